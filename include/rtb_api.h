@@ -1,0 +1,212 @@
+/*
+ * rtb_api.h -- C-ABI of the B200-native ray-tracing hot path.
+ *
+ * Two layers are exported by libraytracing_b200.so:
+ *
+ *  (1) launchKernel(...)  -- the legacy drop-in.  Exactly the symbol the
+ *      reference's scene.cpp declares (reference scene.cpp:79-85) and calls
+ *      once per frame (reference scene.cpp:823-824); defined by the reference
+ *      in kernel.cu:406-462.  `result` is a DEVICE pointer, everything else is
+ *      host memory; sky textures are read on the first call only; errors print
+ *      to stderr and exit(1) like the reference's getLastCudaError
+ *      (reference common/inc/helper_cuda.h:584-596).
+ *
+ *  (2) rt_*  -- a handle API for what the legacy form cannot express: any number
+ *      of primitives (LBVH in HBM instead of 133 objects in __constant__),
+ *      explicit lifetime, several devices (one context per device), screen-tile
+ *      shards, hit-id / counter read-back, status codes instead of exit().
+ *      launchKernel is a thin shim over one process-global rt_context.
+ *
+ *  (3) rtb_scene_* -- the host-side scene layer (reference scene.cpp) restated
+ *      with explicit state instead of globals; produces the Object/Light/Camera
+ *      inputs of the boundary for any view, time of day and sea level.
+ *
+ * No torch types, no C++ types: plain pointers, ints and the PODs of
+ * rtb_structs.h.
+ */
+#ifndef RTB_API_H
+#define RTB_API_H
+
+#include "rtb_structs.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ legacy */
+
+#if defined(__cplusplus) && !defined(RTB_NO_LEGACY_DECL)
+/* replaces reference kernel.cu:406-411 */
+void launchKernel(unsigned int* result, int imgw, int imgh, rtb_Camera cam,
+                  rtb_Object* objects, rtb_Light* lights, rtb_float3 ambient,
+                  float* h_skyVars,
+                  unsigned char* h_tex1, unsigned char* h_tex2,
+                  unsigned char* h_tex3, unsigned char* h_tex4, int w, int h,
+                  float h_dayTime, bool alias);
+#endif
+
+/* ------------------------------------------------------------ handle API */
+
+typedef struct rt_context rt_context;
+
+enum {
+    RT_OK = 0,
+    RT_ERR_CUDA = 1,       /* a CUDA runtime/driver call failed; see rt_last_error */
+    RT_ERR_ARG = 2,        /* bad argument */
+    RT_ERR_STATE = 3,      /* call order (e.g. render before set_scene/set_sky) */
+    RT_ERR_UNSUPPORTED = 4
+};
+
+/* rt_set_option keys */
+enum {
+    RT_OPT_TRAVERSAL = 0,   /* 0 = LBVH (default), 1 = brute force over all primitives (GPU cross-check) */
+    RT_OPT_COUNTERS  = 1,   /* 1 = instrumented kernels: count rays / node / primitive tests */
+    RT_OPT_FXAA_IMPL = 2,   /* 0 = TMA-staged (default when width%4==0), 1 = plain shared-memory */
+    RT_OPT_TIMING    = 3,   /* 1 = record CUDA events around trace and fxaa */
+    RT_OPT_SKY_ALL4  = 4,   /* 1 = fetch all four sky maps like the reference (default 0: only non-zero weights; bit-identical) */
+    RT_OPT_TRACE_IMPL = 5,  /* 0 = default tracer, other values select experimental variants */
+    RT_OPT_FORCE_RADIX = 7  /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
+};
+
+/* One frame's uniforms: what launchKernel receives by value / as small host arrays. */
+typedef struct rt_frame {
+    rtb_Camera cam;
+    float      ambient[3];
+    float      skyVars[4];
+    float      dayTime;      /* dayNightTime / 24 (reference scene.cpp:822) */
+    int        alias;        /* FXAA on/off */
+    int        imgw, imgh;
+} rt_frame;
+
+/* Interleaved screen-tile shard: tile (i,j) belongs to shard (i + j*stride) % n_shards.
+ * A shard traces its tiles plus a 1-pixel apron so FXAA needs no halo exchange. */
+typedef struct rt_shard {
+    int tile_w, tile_h;
+    int n_shards, shard_id;
+    int stride;
+} rt_shard;
+
+/* counters returned by rt_get_counters (RT_OPT_COUNTERS=1) */
+enum {
+    RT_CNT_RAYS_PRIMARY = 0, RT_CNT_RAYS_SHADOW = 1, RT_CNT_RAYS_MIRROR = 2,
+    RT_CNT_NODE_TESTS = 3, RT_CNT_TRI_TESTS = 4, RT_CNT_SPHERE_TESTS = 5,
+    RT_CNT_PLANE_TESTS = 6, RT_CNT_SKY_LOOKUPS = 7, RT_CNT_SHADOW_SKIPPED = 8,
+    RT_CNT_COUNT = 16
+};
+
+int  rt_create(int device, rt_context** out);
+int  rt_destroy(rt_context* ctx);
+const char* rt_last_error(rt_context* ctx);
+int  rt_set_option(rt_context* ctx, int key, int value);
+/* cudaStream_t to launch on (default: the legacy default stream) */
+int  rt_set_stream(rt_context* ctx, void* cuda_stream);
+
+/* Four equirectangular RGBA8 sky maps, HOST memory, w*h*4 bytes each
+ * (reference kernel.cu:418-436).  Copied to device once. */
+int  rt_set_sky(rt_context* ctx, const unsigned char* const tex[4], int w, int h);
+
+/* Upload primitives + lights (HOST memory) and build / refit the LBVH.
+ * Classifies the change against the previous call: identical geometry ->
+ * materials only; same topology with moved primitives -> refit; else rebuild. */
+int  rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects,
+                  const rtb_Light* lights, int n_lights);
+
+/* Render one frame into a DEVICE buffer of imgw*imgh uint32 (0x00BBGGRR).
+ * shard may be NULL (whole frame).  hit_ids_dev may be NULL; else imgw*imgh int32
+ * primary hit object index (-1 = sky).  Asynchronous on the context's stream. */
+int  rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard,
+               unsigned int* out_dev, int* hit_ids_dev);
+/* Same, result copied to HOST memory (pinned or pageable); synchronous. */
+int  rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* shard,
+                       unsigned int* out_host, int* hit_ids_host);
+/* The pre-FXAA image of the last rt_render (device pointer owned by ctx). */
+int  rt_get_base_image(rt_context* ctx, unsigned int** base_dev);
+/* FXAA alone: in_dev -> out_dev (reference kernel.cu:262-403 with alias=true). */
+int  rt_fxaa(rt_context* ctx, const unsigned int* in_dev, unsigned int* out_dev,
+             int imgw, int imgh, const rt_shard* shard);
+
+/* Tile gather helpers for multi-GPU compositing: pack the tiles a shard owns
+ * into a dense [n_tiles][tile_h][tile_w] buffer / scatter them back. */
+int  rt_shard_tile_count(const rt_shard* shard, int imgw, int imgh);
+int  rt_pack_tiles(rt_context* ctx, const unsigned int* frame_dev, int imgw, int imgh,
+                   const rt_shard* shard, unsigned int* packed_dev);
+int  rt_unpack_tiles(rt_context* ctx, const unsigned int* packed_dev, int imgw, int imgh,
+                     const rt_shard* shard, unsigned int* frame_dev);
+
+int  rt_synchronize(rt_context* ctx);
+int  rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]);
+/* ms of the last frame's kernels (RT_OPT_TIMING=1): [0]=trace [1]=fxaa [2]=bvh build/refit */
+int  rt_get_timings(rt_context* ctx, float out_ms[3]);
+
+/* LBVH introspection (tests): copies to HOST.  nodes: 16 floats per node. */
+int  rt_bvh_info(rt_context* ctx, int* n_prims_in_bvh, int* n_nodes, int* n_planes);
+int  rt_bvh_download(rt_context* ctx, float* nodes16, int* sorted_prim_ids,
+                     unsigned int* morton_sorted);
+/* Stand-alone key sort used by the builder (tests compare it with CUB):
+ * sorts (key,val) pairs in DEVICE memory, stable, ascending. */
+int  rt_sort_pairs(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n);
+int  rt_sort_pairs_cub(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n);
+
+/* ----------------------------------------------------- host scene layer */
+
+typedef struct rtb_scene rtb_scene;
+
+/* initCamera + initLights + initObjects (reference scene.cpp:165-173, 634-652, 444-488) */
+rtb_scene*  rtb_scene_create(void);
+void        rtb_scene_destroy(rtb_scene* s);
+rtb_Object* rtb_scene_objects(rtb_scene* s, int* n);
+rtb_Light*  rtb_scene_lights(rtb_scene* s, int* n);
+rtb_Camera* rtb_scene_camera(rtb_scene* s);
+float*      rtb_scene_sky_vars(rtb_scene* s);      /* 4 floats */
+float*      rtb_scene_ambient(rtb_scene* s);       /* 3 floats */
+float       rtb_scene_time(rtb_scene* s);          /* dayNightTime, hours */
+/* Steady state of animate() at a fixed hour: calcSkyVars -> recolorObjects ->
+ * moveLights (reference scene.cpp:778-804, 674-687, 758-776; order per SURVEY 3.2). */
+void        rtb_scene_set_time(rtb_scene* s, float hours);
+/* key '5' (island) / '6' (mountains) presets (reference scene.cpp:736-747) */
+int         rtb_scene_set_view(rtb_scene* s, int key);
+void        rtb_scene_set_pose(rtb_scene* s, float px, float py, float pz, float horAngle, float verAngle);
+/* aspect = (1.0f*w)/h then cameraHelperAngles (reference scene.cpp:821, 100-126) */
+void        rtb_scene_update_camera(rtb_scene* s, int imgw, int imgh);
+void        rtb_scene_set_sea_level(rtb_scene* s, float y);   /* objects[0].pos.y, reference scene.cpp:709 */
+void        rtb_scene_set_antialiasing(rtb_scene* s, int on);
+/* Headless stand-in for one animate() tick (reference scene.cpp:806-816) with the
+ * key state given explicitly.  keys: bitmask of RTB_KEY_* */
+void        rtb_scene_animate(rtb_scene* s, float deltaTime, unsigned int keys);
+/* reference mouseMotion (scene.cpp:128-140) with explicit deltas */
+void        rtb_scene_mouse(rtb_scene* s, int deltaX, int deltaY);
+const char* rtb_scene_clock(rtb_scene* s);                    /* getTime(), reference scene.cpp:93-96 */
+/* Fill an rt_frame from the scene state (what launch() passes, reference scene.cpp:820-824) */
+void        rtb_scene_frame(rtb_scene* s, int imgw, int imgh, rt_frame* out);
+/* launch(): update aspect, call the legacy boundary, synchronise (reference scene.cpp:820-826).
+ * tex pointers as loaded by the caller. */
+void        rtb_scene_launch(rtb_scene* s, unsigned int* out_dev, int imgw, int imgh,
+                             unsigned char* tex[4], int texw, int texh);
+
+enum {
+    RTB_KEY_W = 1u << 0, RTB_KEY_S = 1u << 1, RTB_KEY_A = 1u << 2, RTB_KEY_D = 1u << 3,
+    RTB_KEY_Q = 1u << 4, RTB_KEY_E = 1u << 5, RTB_KEY_SHIFT = 1u << 6,
+    RTB_KEY_LEFT = 1u << 7, RTB_KEY_RIGHT = 1u << 8, RTB_KEY_UP = 1u << 9, RTB_KEY_DOWN = 1u << 10,
+    RTB_KEY_1 = 1u << 11, RTB_KEY_2 = 1u << 12, RTB_KEY_3 = 1u << 13, RTB_KEY_4 = 1u << 14,
+    RTB_KEY_5 = 1u << 15, RTB_KEY_6 = 1u << 16, RTB_KEY_P = 1u << 17, RTB_KEY_O = 1u << 18,
+    RTB_KEY_B = 1u << 19, RTB_KEY_V = 1u << 20
+};
+
+/* Synthetic inputs (no reference counterpart; BASELINE.json config 4 and the
+ * asset-free sky used on the GPU box). */
+/* Tessellated terrain: cells x cells grid, 2 triangles per cell, fBm heights, plus the
+ * water plane at index 0 and sun/moon spheres as the last two.  Returns object count
+ * (2*cells*cells + 3); out may be NULL to query. */
+int  rtb_terrain_build(int cells, unsigned int seed, rtb_Object* out, int capacity);
+/* Procedural equirectangular sky map `which` (0 morning,1 day,2 evening,3 night), RGBA8. */
+void rtb_sky_synthetic(int which, int w, int h, unsigned char* out);
+
+/* Image output (replaces the GL blit, reference main.cpp:141-165): packed 0x00BBGGRR
+ * host pixels -> binary PPM / PNG.  Return 0 on success. */
+int  rtb_write_ppm(const char* path, const unsigned int* pixels, int w, int h);
+int  rtb_write_png(const char* path, const unsigned int* pixels, int w, int h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB_API_H */

@@ -1,0 +1,235 @@
+#!/usr/bin/env python3
+"""Build the oracle and, when the reference tree is present, the reference builds.
+
+TEST INFRASTRUCTURE.  Nothing here is part of the product path.
+
+Outputs
+-------
+oracle/liboracle.so                    rt_oracle.cpp (own CPU restatement), g++ -O2 -fopenmp
+oracle/_ref/libref_scene.so            the reference's scene.cpp as it lies under /root/reference,
+                                       + ref_shims/windows.h + ref_scene_wrap.cpp
+oracle/_ref/libref_trace_cpu.so        the reference's kernel.cu:9-403 (device functions and both
+                                       kernels) compiled for the HOST under ref_shims/cpu_cuda_shim.h,
+                                       + ref_trace_cpu_wrap.inc
+oracle/_ref/libref_kernel_sm100.so     the reference's kernel.cu rebuilt for sm_100 with the minimum
+                                       patch CUDA 12.9 needs (texture references -> texture objects,
+                                       explicit float casts at kernel.cu:163) and a primary hit-id tap;
+                                       flags as the reference's vcxproj:66-67 (--use_fast_math)
+
+Reference sources are read where they lie and are never copied into the repo: the
+concatenated / patched translation units are written to a temporary directory and
+deleted; only the .so files stay, under git-ignored oracle/_ref/.  On the GPU box
+/root/reference does not exist and the prebuilt .so files (shipped with the snapshot)
+are used as they are.
+"""
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("RTB_REFERENCE_DIR", "/root/reference")
+OUT = os.path.join(HERE, "_ref")
+CUDA = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+HOST_FLAGS = ["-O2", "-fopenmp", "-ffp-contract=off", "-fPIC", "-shared", "-std=c++17"]
+
+
+def run(cmd):
+    print("+", " ".join(cmd), flush=True)
+    subprocess.check_call(cmd)
+
+
+def newer(target, sources):
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.exists(s) and os.path.getmtime(s) <= t for s in sources)
+
+
+def build_oracle(force=False):
+    src = os.path.join(HERE, "rt_oracle.cpp")
+    out = os.path.join(HERE, "liboracle.so")
+    if not force and newer(out, [src, os.path.join(HERE, "..", "include", "rtb_structs.h")]):
+        return out
+    run(["g++"] + HOST_FLAGS + ["-o", out, src])
+    return out
+
+
+def have_reference():
+    return os.path.isfile(os.path.join(REF, "kernel.cu")) and os.path.isfile(os.path.join(REF, "scene.cpp"))
+
+
+def build_ref_scene(force=False):
+    out = os.path.join(OUT, "libref_scene.so")
+    wrap = os.path.join(HERE, "ref_scene_wrap.cpp")
+    if not force and newer(out, [wrap, os.path.join(REF, "scene.cpp")]):
+        return out
+    run(["g++"] + HOST_FLAGS + ["-w", "-I", os.path.join(HERE, "ref_shims"), "-I", REF,
+                                "-I", os.path.join(REF, "common", "inc"), "-I", os.path.join(CUDA, "include"),
+                                "-o", out, os.path.join(REF, "scene.cpp"), wrap,
+                                "-L", os.path.join(CUDA, "lib64"), "-lcudart",
+                                "-Wl,-rpath," + os.path.join(CUDA, "lib64")])
+    return out
+
+
+def _kernel_text():
+    with open(os.path.join(REF, "kernel.cu"), "r", encoding="utf-8", errors="replace") as f:
+        return f.read().replace("\r\n", "\n")
+
+
+def _insert_hit_tap(text, tap):
+    """Insert `tap` right after the closest-hit loop of trace<depth> (reference kernel.cu:153)."""
+    marker = "    // calculate pixel color\n"
+    assert text.count(marker) == 1, "closest-hit marker not found exactly once"
+    return text.replace(marker, tap + marker)
+
+
+def _brace_case_bodies(text):
+    """g++ rejects jumps over initialisations between the case labels of checkHit
+    (reference kernel.cu:45-126; nvcc only warns): give every case body its own scope and
+    hoist `float t`, which the triangle case borrows from the plane case (kernel.cu:76,115)."""
+    def once(t, old, new):
+        assert t.count(old) == 1, old
+        return t.replace(old, new)
+    text = once(text, "    case Primitive::SPHERE:\n", "    case Primitive::SPHERE: {\n")
+    text = once(text, "    case Primitive::PLANE:\n", "    }\n    case Primitive::PLANE: {\n")
+    text = once(text, "    case Primitive::TRIANGLE:\n", "    }\n    case Primitive::TRIANGLE: {\n        float t;\n")
+    text = once(text, "        return true;\n    }\n\n    return false;\n}",
+                "        return true;\n    }\n    }\n\n    return false;\n}")
+    return text
+
+
+def build_ref_trace_cpu(force=False):
+    out = os.path.join(OUT, "libref_trace_cpu.so")
+    deps = [os.path.join(REF, "kernel.cu"), os.path.join(HERE, "ref_trace_cpu_wrap.inc"),
+            os.path.join(HERE, "ref_shims", "cpu_cuda_shim.h")]
+    if not force and newer(out, deps):
+        return out
+    text = _kernel_text()
+    start = text.index("#define MAX_DEPTH")
+    end = text.index("// Main Kernel")
+    body = text[start:end]
+    body = _insert_hit_tap(body, "    if (depth == 0) g_ref_hit = index;\n")
+    body = _brace_case_bodies(body)
+    tmp = tempfile.mkdtemp(prefix="rtb_ref_")
+    try:
+        tu = os.path.join(tmp, "ref_trace_cpu.cpp")
+        with open(tu, "w") as f:
+            f.write('#include "cpu_cuda_shim.h"\n#include <scene.h>\n#include <structs.h>\n')
+            f.write("typedef unsigned char GLubyte;\nstatic thread_local int g_ref_hit = -1;\n")
+            f.write(body)
+            f.write('\n#include "ref_trace_cpu_wrap.inc"\n')
+        run(["g++"] + HOST_FLAGS + ["-w", "-fpermissive", "-Wno-narrowing",
+                                    "-I", os.path.join(HERE, "ref_shims"), "-I", HERE, "-I", REF,
+                                    "-I", os.path.join(CUDA, "include"), "-o", out, tu])
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return out
+
+
+GPU_TEX_INIT = r"""
+        {
+            const unsigned char* h_texN[4] = {h_tex1, h_tex2, h_tex3, h_tex4};
+            cudaTextureObject_t objs[4];
+            for (int t = 0; t < 4; t++) {
+                cudaChannelFormatDesc desc = cudaCreateChannelDesc<uchar4>();
+                cudaArray_t arr;
+                cudaMallocArray(&arr, &desc, w, h);
+                cudaMemcpy2DToArray(arr, 0, 0, h_texN[t], (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyHostToDevice);
+                cudaResourceDesc rd; memset(&rd, 0, sizeof(rd));
+                rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+                cudaTextureDesc td; memset(&td, 0, sizeof(td));
+                td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+                td.filterMode = cudaFilterModePoint;
+                td.readMode = cudaReadModeElementType;
+                td.normalizedCoords = 1;
+                cudaCreateTextureObject(&objs[t], &rd, &td, NULL);
+            }
+            cudaMemcpyToSymbol(tex1, &objs[0], sizeof(cudaTextureObject_t));
+            cudaMemcpyToSymbol(tex2, &objs[1], sizeof(cudaTextureObject_t));
+            cudaMemcpyToSymbol(tex3, &objs[2], sizeof(cudaTextureObject_t));
+            cudaMemcpyToSymbol(tex4, &objs[3], sizeof(cudaTextureObject_t));
+        }
+"""
+
+GPU_TAIL = r"""
+// ---- appended by oracle/build_ref.py (test infrastructure) ----
+extern "C" void ref_set_hit_buffer(int* dev, int w) {
+    cudaMemcpyToSymbol(g_hitIds, &dev, sizeof(int*));
+    cudaMemcpyToSymbol(g_hitW, &w, sizeof(int));
+}
+extern "C" unsigned int* ref_get_base_image() { return baseImage; }
+// time `iters` back-to-back frames of the two reference kernels (inputs already uploaded by a
+// previous launchKernel call); returns ms per frame
+extern "C" float ref_time_kernels(unsigned int* result, int imgw, int imgh, Camera cam, bool alias, int iters) {
+    dim3 block(BLOCK_SIZE, BLOCK_SIZE, 1);
+    dim3 grid((imgw + block.x - 1) / block.x, (imgh + block.y - 1) / block.y, 1);
+    cudaEvent_t a, b; cudaEventCreate(&a); cudaEventCreate(&b);
+    cudaEventRecord(a);
+    for (int i = 0; i < iters; i++) {
+        raytracing<<< grid, block >>>(baseImage, imgw, imgh, cam);
+        antialiasing<<< grid, block >>>(baseImage, result, imgw, imgh, alias);
+    }
+    cudaEventRecord(b); cudaEventSynchronize(b);
+    float ms = 0; cudaEventElapsedTime(&ms, a, b);
+    cudaEventDestroy(a); cudaEventDestroy(b);
+    return ms / iters;
+}
+"""
+
+
+def build_ref_kernel_gpu(force=False):
+    out = os.path.join(OUT, "libref_kernel_sm100.so")
+    if not force and newer(out, [os.path.join(REF, "kernel.cu"), os.path.abspath(__file__)]):
+        return out
+    text = _kernel_text()
+    # (i) texture references -> texture objects held in __constant__ (reference kernel.cu:19-22)
+    text, n = re.subn(r"texture<uchar4, 2, cudaReadModeElementType> (tex[1-4]);",
+                      r"__constant__ cudaTextureObject_t \1;", text)
+    assert n == 4
+    text, n = re.subn(r"tex2D\((tex[1-4]), x, y\)", r"tex2D<uchar4>(\1, x, y)", text)
+    assert n == 4
+    # (ii) narrowing brace-init (reference kernel.cu:163)
+    old = "float3{ v.x, v.y, v.z }"
+    assert text.count(old) == 1
+    text = text.replace(old, "float3{ (float)v.x, (float)v.y, (float)v.z }")
+    # (iii) texture setup block (reference kernel.cu:418-436)
+    a = text.index("        int mem_size = sizeof(uchar4) * w * h;")
+    b = text.index('        getLastCudaError("Error texture\\n");')
+    text = text[:a] + GPU_TEX_INIT + text[b:]
+    # (iv) primary hit-id tap
+    text = text.replace("bool init = false;",
+                        "bool init = false;\n__constant__ int* g_hitIds;\n__constant__ int g_hitW;", 1)
+    tap = ("    if (depth == 0 && g_hitIds) g_hitIds[(blockIdx.y * blockDim.y + threadIdx.y) * g_hitW + "
+           "blockIdx.x * blockDim.x + threadIdx.x] = index;\n")
+    text = _insert_hit_tap(text, tap)
+    text += GPU_TAIL
+    tmp = tempfile.mkdtemp(prefix="rtb_ref_")
+    try:
+        tu = os.path.join(tmp, "ref_kernel_sm100.cu")
+        with open(tu, "w") as f:
+            f.write("#include <cstring>\n" + text)
+        run([os.path.join(CUDA, "bin", "nvcc"), "-gencode", "arch=compute_100,code=sm_100",
+             "--use_fast_math", "-O3", "-w", "-shared", "-Xcompiler", "-fPIC", "-lineinfo",
+             "-I", REF, "-I", os.path.join(REF, "common", "inc"), "-o", out, tu])
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+    return out
+
+
+def build_all(force=False, gpu_ref=True):
+    built = {"oracle": build_oracle(force)}
+    if have_reference():
+        os.makedirs(OUT, exist_ok=True)
+        built["ref_scene"] = build_ref_scene(force)
+        built["ref_trace_cpu"] = build_ref_trace_cpu(force)
+        if gpu_ref:
+            built["ref_kernel_gpu"] = build_ref_kernel_gpu(force)
+    return built
+
+
+if __name__ == "__main__":
+    for k, v in build_all(force="--force" in sys.argv).items():
+        print(k, "->", v)

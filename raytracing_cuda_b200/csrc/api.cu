@@ -1,0 +1,600 @@
+/*
+ * api.cu -- host side of the drop-in boundary: the rt_* handle API and the legacy
+ * launchKernel() shim over it (replaces the reference's host wrapper,
+ * reference kernel.cu:406-462).
+ *
+ * Differences from the reference wrapper, by design:
+ *   - scene data lives in HBM as an LBVH + SoA records (rt_device.h) instead of
+ *     133 Objects in __constant__ memory; per-frame uniforms travel as one kernel
+ *     parameter block instead of five cudaMemcpyToSymbol calls (kernel.cu:447-451);
+ *   - sky maps are texture OBJECTS (point filter, clamp, normalised coordinates --
+ *     the defaults the reference's texture references end up with, kernel.cu:19-22,
+ *     429-436); legacy texture references no longer exist in CUDA 12;
+ *   - rt_set_scene classifies the change against the previous upload (nothing /
+ *     materials and planes only / moved primitives -> refit / topology -> rebuild).
+ */
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "rt_device.h"
+
+
+extern "C" {
+cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, cudaStream_t stream);
+cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned int* tmp_keys, unsigned int* tmp_vals,
+                                unsigned int* hist, int n, int force_radix, cudaStream_t stream);
+int rt_radix_hist_entries(int n);
+cudaError_t rt_cub_sort_pairs(unsigned int* keys, unsigned int* vals, int n, cudaStream_t stream);
+cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
+                            RtCountersDev* counters, int brute, int count, cudaStream_t stream);
+cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
+                                cudaStream_t stream);
+cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out, int w, int h,
+                               const rt_shard* sh, int n_sm, cudaStream_t stream);
+cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
+                           cudaStream_t stream);
+cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned int* packed, int w, int h, const rt_shard* sh,
+                                 int unpack, cudaStream_t stream);
+}
+
+struct rt_context {
+    int device = 0;
+    int n_sm = 148;
+    cudaStream_t stream = 0;
+    std::string err;
+    int opt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    /* sky */
+    cudaArray_t sky_arr[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaTextureObject_t sky_tex[4] = {0, 0, 0, 0};
+    bool have_sky = false;
+
+    /* scene */
+    std::vector<rtb_Object> host_objs;      /* last upload, for change classification */
+    std::vector<int> host_planes;
+    rtb_Light lights[RT_MAX_LIGHTS];
+    int n_lights = 0;
+    bool have_scene = false;
+    int cap_objects = 0, cap_bvh = 0, cap_planes = 0;
+    float* d_objs = nullptr;
+    int* d_plane_idx = nullptr;
+    RtBuildBuffers bb;
+    RtSceneDev scene;
+
+    /* frame buffers */
+    unsigned int* d_base = nullptr;
+    size_t cap_base = 0;
+    unsigned int* d_stage_out = nullptr;    /* for rt_render_to_host */
+    int* d_stage_ids = nullptr;
+    size_t cap_stage = 0;
+    RtCountersDev* d_counters = nullptr;
+
+    /* TMA descriptor cache */
+    CUtensorMap tmap;
+    const void* tmap_ptr = nullptr;
+    int tmap_w = 0, tmap_h = 0;
+
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool timing_valid = false, build_timed = false;
+};
+
+namespace {
+
+#define RT_CHECK(ctx, call)                                                                     \
+    do {                                                                                        \
+        cudaError_t e_ = (call);                                                                \
+        if (e_ != cudaSuccess) {                                                                \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                    \
+            return RT_ERR_CUDA;                                                                 \
+        }                                                                                       \
+    } while (0)
+
+int fail(rt_context* ctx, int code, const char* msg) {
+    ctx->err = msg;
+    return code;
+}
+
+template <class T>
+cudaError_t regrow(T** p, size_t count) {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    if (count == 0) return cudaSuccess;
+    return cudaMalloc((void**)p, sizeof(T) * count);
+}
+
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_tiled_fn get_encode_tiled() {
+    static encode_tiled_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (encode_tiled_fn)p;
+    }
+    return fn;
+}
+
+/* 2-D uint32 image [h][w] -> 68x34 boxes (FXAA tile + halo) */
+bool make_fxaa_tmap(rt_context* ctx, const unsigned int* img, int w, int h) {
+    if (ctx->tmap_ptr == img && ctx->tmap_w == w && ctx->tmap_h == h) return true;
+    encode_tiled_fn enc = get_encode_tiled();
+    if (!enc) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)w, (cuuint64_t)h};
+    cuuint64_t strides[1] = {(cuuint64_t)w * 4};
+    cuuint32_t box[2] = {68, 34};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&ctx->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, (void*)img, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return false;
+    ctx->tmap_ptr = img;
+    ctx->tmap_w = w;
+    ctx->tmap_h = h;
+    return true;
+}
+
+int run_fxaa(rt_context* ctx, const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh) {
+    const bool shard_ok = !sh || sh->n_shards <= 1 || (sh->tile_w == 64 && sh->tile_h == 32);
+    const bool tma_ok = ctx->opt[RT_OPT_FXAA_IMPL] == 0 && (w % 4 == 0) && (((uintptr_t)in) % 16 == 0) && shard_ok &&
+                        make_fxaa_tmap(ctx, in, w, h);
+    if (tma_ok) RT_CHECK(ctx, rt_launch_fxaa_tma(&ctx->tmap, in, out, w, h, sh, ctx->n_sm, ctx->stream));
+    else        RT_CHECK(ctx, rt_launch_fxaa_smem(in, out, w, h, sh, ctx->stream));
+    return RT_OK;
+}
+
+bool geometry_equal(const rtb_Object& a, const rtb_Object& b) {
+    return a.type == b.type && memcmp(&a.pos, &b.pos, 36) == 0;   /* pos, size, third are contiguous */
+}
+
+}  // namespace
+
+extern "C" {
+
+int rt_create(int device, rt_context** out) {
+    if (!out) return RT_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return RT_ERR_CUDA;
+    rt_context* ctx = new rt_context();
+    ctx->device = device;
+    memset(&ctx->bb, 0, sizeof(ctx->bb));
+    memset(&ctx->scene, 0, sizeof(ctx->scene));
+    ctx->scene.root = RT_NODE_SENTINEL;
+    if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
+    cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
+    if (cudaMalloc((void**)&ctx->d_counters, sizeof(RtCountersDev)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
+    cudaMemset(ctx->d_counters, 0, sizeof(RtCountersDev));
+    for (int i = 0; i < 6; i++) cudaEventCreate(&ctx->ev[i]);
+    *out = ctx;
+    return RT_OK;
+}
+
+int rt_destroy(rt_context* ctx) {
+    if (!ctx) return RT_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < 4; i++) {
+        if (ctx->sky_tex[i]) cudaDestroyTextureObject(ctx->sky_tex[i]);
+        if (ctx->sky_arr[i]) cudaFreeArray(ctx->sky_arr[i]);
+    }
+    RtBuildBuffers& b = ctx->bb;
+    void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
+                    b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.flags,
+                    b.nodes, b.prims, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    delete ctx;
+    return RT_OK;
+}
+
+const char* rt_last_error(rt_context* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int rt_set_option(rt_context* ctx, int key, int value) {
+    if (!ctx || key < 0 || key >= 8) return RT_ERR_ARG;
+    ctx->opt[key] = value;
+    return RT_OK;
+}
+
+int rt_set_stream(rt_context* ctx, void* cuda_stream) {
+    if (!ctx) return RT_ERR_ARG;
+    ctx->stream = (cudaStream_t)cuda_stream;
+    return RT_OK;
+}
+
+int rt_set_sky(rt_context* ctx, const unsigned char* const tex[4], int w, int h) {
+    if (!ctx || !tex || w <= 0 || h <= 0) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    for (int i = 0; i < 4; i++) {
+        if (!tex[i]) return fail(ctx, RT_ERR_ARG, "null sky map");
+        if (ctx->sky_tex[i]) { cudaDestroyTextureObject(ctx->sky_tex[i]); ctx->sky_tex[i] = 0; }
+        if (ctx->sky_arr[i]) { cudaFreeArray(ctx->sky_arr[i]); ctx->sky_arr[i] = nullptr; }
+        cudaChannelFormatDesc desc = cudaCreateChannelDesc<uchar4>();
+        RT_CHECK(ctx, cudaMallocArray(&ctx->sky_arr[i], &desc, w, h));
+        RT_CHECK(ctx, cudaMemcpy2DToArray(ctx->sky_arr[i], 0, 0, tex[i], (size_t)w * 4, (size_t)w * 4, h,
+                                          cudaMemcpyHostToDevice));
+        cudaResourceDesc rd;
+        memset(&rd, 0, sizeof(rd));
+        rd.resType = cudaResourceTypeArray;
+        rd.res.array.array = ctx->sky_arr[i];
+        cudaTextureDesc td;
+        memset(&td, 0, sizeof(td));
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModePoint;
+        td.readMode = cudaReadModeElementType;
+        td.normalizedCoords = 1;
+        RT_CHECK(ctx, cudaCreateTextureObject(&ctx->sky_tex[i], &rd, &td, nullptr));
+    }
+    ctx->have_sky = true;
+    return RT_OK;
+}
+
+int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, const rtb_Light* lights, int n_lights) {
+    if (!ctx || n_objects < 0 || (n_objects > 0 && !objects) || n_lights < 0 || n_lights > RT_MAX_LIGHTS ||
+        (n_lights > 0 && !lights) || (unsigned int)n_objects > RT_TAG_INDEX)
+        return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    for (int i = 0; i < n_lights; i++) ctx->lights[i] = lights[i];
+    ctx->n_lights = n_lights;
+
+    /* classify the change */
+    int mode;   /* -1 nothing to upload, 1 refit (also covers material-only), 0 rebuild */
+    if (!ctx->have_scene || (int)ctx->host_objs.size() != n_objects) {
+        mode = 0;
+    } else if (n_objects == 0 || memcmp(ctx->host_objs.data(), objects, sizeof(rtb_Object) * (size_t)n_objects) == 0) {
+        mode = -1;
+    } else {
+        mode = 1;
+        for (int i = 0; i < n_objects; i++)
+            if (objects[i].type != ctx->host_objs[i].type) { mode = 0; break; }
+    }
+    if (mode < 0) return RT_OK;
+
+    bool bvh_geometry_changed = (mode == 0);
+    if (mode == 1) {
+        for (int i = 0; i < n_objects && !bvh_geometry_changed; i++)
+            if (objects[i].type != RTB_PLANE && !geometry_equal(objects[i], ctx->host_objs[i])) bvh_geometry_changed = true;
+    }
+
+    if (mode == 0) {
+        ctx->host_planes.clear();
+        for (int i = 0; i < n_objects; i++)
+            if (objects[i].type != RTB_SPHERE && objects[i].type != RTB_TRIANGLE) ctx->host_planes.push_back(i);
+    }
+    const int n_planes = (int)ctx->host_planes.size();
+    const int n_bvh = n_objects - n_planes;
+    RtBuildBuffers& b = ctx->bb;
+
+    if (n_objects > ctx->cap_objects) {
+        const size_t c = (size_t)n_objects;
+        RT_CHECK(ctx, regrow(&ctx->d_objs, c * 17));
+        RT_CHECK(ctx, regrow(&b.mats, c * 2));
+        RT_CHECK(ctx, regrow(&b.recs, c * 3));
+        ctx->cap_objects = n_objects;
+    }
+    if (n_planes > ctx->cap_planes || !ctx->d_plane_idx) {
+        const size_t c = (size_t)(n_planes > 0 ? n_planes : 1);
+        RT_CHECK(ctx, regrow(&ctx->d_plane_idx, c));
+        RT_CHECK(ctx, regrow(&b.planes, c * 2));
+        ctx->cap_planes = (int)c;
+    }
+    if (!b.bounds) RT_CHECK(ctx, regrow(&b.bounds, (size_t)8));
+    if (n_bvh > ctx->cap_bvh) {
+        const size_t c = (size_t)n_bvh;
+        RT_CHECK(ctx, regrow(&b.bvh_src, c));
+        RT_CHECK(ctx, regrow(&b.prim_lo, c));
+        RT_CHECK(ctx, regrow(&b.prim_hi, c));
+        RT_CHECK(ctx, regrow(&b.keys, c));
+        RT_CHECK(ctx, regrow(&b.vals, c));
+        RT_CHECK(ctx, regrow(&b.tmp_keys, c));
+        RT_CHECK(ctx, regrow(&b.tmp_vals, c));
+        RT_CHECK(ctx, regrow(&b.hist, (size_t)rt_radix_hist_entries(n_bvh)));
+        RT_CHECK(ctx, regrow(&b.children, c));
+        RT_CHECK(ctx, regrow(&b.node_parent, c));
+        RT_CHECK(ctx, regrow(&b.leaf_parent, c));
+        RT_CHECK(ctx, regrow(&b.flags, c));
+        RT_CHECK(ctx, regrow(&b.nodes, c * 16));
+        RT_CHECK(ctx, regrow(&b.prims, c * 3));
+        ctx->cap_bvh = n_bvh;
+    }
+
+    ctx->host_objs.assign(objects, objects + n_objects);
+    if (n_objects > 0)
+        RT_CHECK(ctx, cudaMemcpyAsync(ctx->d_objs, ctx->host_objs.data(), sizeof(rtb_Object) * (size_t)n_objects, cudaMemcpyHostToDevice,
+                                      ctx->stream));
+    if (mode == 0 && n_planes > 0)
+        RT_CHECK(ctx, cudaMemcpyAsync(ctx->d_plane_idx, ctx->host_planes.data(), sizeof(int) * (size_t)n_planes,
+                                      cudaMemcpyHostToDevice, ctx->stream));
+    /* host_objs is the staging source of the async copies above: it is only rewritten by the next
+     * rt_set_scene, and pageable cudaMemcpyAsync returns after the source has been staged */
+
+    b.objs = ctx->d_objs;
+    b.n_objects = n_objects;
+    b.plane_idx = ctx->d_plane_idx;
+    b.n_planes = n_planes;
+    b.n_bvh = n_bvh;
+    const bool timing = ctx->opt[RT_OPT_TIMING] != 0;
+    if (timing) cudaEventRecord(ctx->ev[4], ctx->stream);
+    /* material / plane-only changes still run the (cheap) setup + refit: one code path */
+    RT_CHECK(ctx, rt_build_bvh(&b, mode == 0 ? 0 : 1, ctx->opt[RT_OPT_FORCE_RADIX], ctx->stream));
+    if (timing) { cudaEventRecord(ctx->ev[5], ctx->stream); ctx->build_timed = true; }
+    (void)bvh_geometry_changed;
+
+    ctx->scene.nodes = (const float4*)b.nodes;
+    ctx->scene.prims = b.prims;
+    ctx->scene.planes = b.planes;
+    ctx->scene.mats = b.mats;
+    ctx->scene.recs = b.recs;
+    ctx->scene.n_bvh_prims = n_bvh;
+    ctx->scene.n_planes = n_planes;
+    ctx->scene.n_objects = n_objects;
+    ctx->scene.root = n_bvh == 0 ? RT_NODE_SENTINEL : (n_bvh == 1 ? ~0 : 0);
+    ctx->have_scene = true;
+    return RT_OK;
+}
+
+static int fill_frame(rt_context* ctx, const rt_frame* fr, const rt_shard* sh, RtFrameDev* f) {
+    memset(f, 0, sizeof(*f));
+    memcpy(f->pos, &fr->cam.pos, 12);
+    memcpy(f->LD, &fr->cam.LD, 12);
+    memcpy(f->LU, &fr->cam.LU, 12);
+    memcpy(f->RD, &fr->cam.RD, 12);
+    memcpy(f->RU, &fr->cam.RU, 12);
+    memcpy(f->ambient, fr->ambient, 12);
+    memcpy(f->skyVars, fr->skyVars, 16);
+    f->dayTime = fr->dayTime;
+    f->imgw = fr->imgw;
+    f->imgh = fr->imgh;
+    f->n_lights = ctx->n_lights;
+    for (int i = 0; i < ctx->n_lights; i++) {
+        const rtb_Light& l = ctx->lights[i];
+        f->lights[i].px = l.pos.x; f->lights[i].py = l.pos.y; f->lights[i].pz = l.pos.z;
+        f->lights[i].intensity = l.intensity;
+        f->lights[i].cr = l.color.x; f->lights[i].cg = l.color.y; f->lights[i].cb = l.color.z;
+    }
+    for (int i = 0; i < 4; i++) f->sky[i] = ctx->sky_tex[i];
+    f->sky_all4 = ctx->opt[RT_OPT_SKY_ALL4];
+    if (sh && sh->n_shards > 1) {
+        if (sh->tile_w < 1 || sh->tile_h < 1 || sh->shard_id < 0 || sh->shard_id >= sh->n_shards) return RT_ERR_ARG;
+        f->tile_w = sh->tile_w; f->tile_h = sh->tile_h;
+        f->n_shards = sh->n_shards; f->shard_id = sh->shard_id; f->stride = sh->stride;
+    } else {
+        f->tile_w = f->tile_h = 1; f->n_shards = 1;
+    }
+    return RT_OK;
+}
+
+int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_dev, int* hit_ids_dev) {
+    if (!ctx || !frame || !out_dev || frame->imgw < 2 || frame->imgh < 2) return RT_ERR_ARG;
+    if (!ctx->have_scene) return fail(ctx, RT_ERR_STATE, "rt_render before rt_set_scene");
+    if (!ctx->have_sky) return fail(ctx, RT_ERR_STATE, "rt_render before rt_set_sky");
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const size_t npx = (size_t)frame->imgw * frame->imgh;
+    if (npx > ctx->cap_base) {
+        RT_CHECK(ctx, regrow(&ctx->d_base, npx));
+        ctx->cap_base = npx;
+        ctx->tmap_ptr = nullptr;
+    }
+    RtFrameDev f;
+    if (fill_frame(ctx, frame, shard, &f) != RT_OK) return fail(ctx, RT_ERR_ARG, "bad shard");
+    const bool timing = ctx->opt[RT_OPT_TIMING] != 0;
+    const int count = ctx->opt[RT_OPT_COUNTERS] != 0;
+    if (count) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(RtCountersDev), ctx->stream));
+    if (timing) cudaEventRecord(ctx->ev[0], ctx->stream);
+    RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
+                                  ctx->opt[RT_OPT_TRAVERSAL] == 1, count, ctx->stream));
+    if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }
+    int rc = RT_OK;
+    if (frame->alias) rc = run_fxaa(ctx, ctx->d_base, out_dev, frame->imgw, frame->imgh, shard);
+    else RT_CHECK(ctx, rt_launch_copy(ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, ctx->stream));
+    if (rc != RT_OK) return rc;
+    if (timing) { cudaEventRecord(ctx->ev[3], ctx->stream); ctx->timing_valid = true; }
+    return RT_OK;
+}
+
+int rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_host,
+                      int* hit_ids_host) {
+    if (!ctx || !frame || !out_host) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const size_t npx = (size_t)frame->imgw * frame->imgh;
+    if (npx > ctx->cap_stage) {
+        RT_CHECK(ctx, regrow(&ctx->d_stage_out, npx));
+        RT_CHECK(ctx, regrow(&ctx->d_stage_ids, npx));
+        ctx->cap_stage = npx;
+    }
+    if (shard && shard->n_shards > 1) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_stage_out, 0, npx * 4, ctx->stream));
+    int rc = rt_render(ctx, frame, shard, ctx->d_stage_out, hit_ids_host ? ctx->d_stage_ids : nullptr);
+    if (rc != RT_OK) return rc;
+    RT_CHECK(ctx, cudaMemcpyAsync(out_host, ctx->d_stage_out, npx * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (hit_ids_host)
+        RT_CHECK(ctx, cudaMemcpyAsync(hit_ids_host, ctx->d_stage_ids, npx * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_get_base_image(rt_context* ctx, unsigned int** base_dev) {
+    if (!ctx || !base_dev) return RT_ERR_ARG;
+    *base_dev = ctx->d_base;
+    return RT_OK;
+}
+
+int rt_fxaa(rt_context* ctx, const unsigned int* in_dev, unsigned int* out_dev, int imgw, int imgh,
+            const rt_shard* shard) {
+    if (!ctx || !in_dev || !out_dev || imgw < 1 || imgh < 1) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    return run_fxaa(ctx, in_dev, out_dev, imgw, imgh, shard);
+}
+
+int rt_shard_tile_count(const rt_shard* sh, int imgw, int imgh) {
+    if (!sh || sh->n_shards < 1 || sh->tile_w < 1 || sh->tile_h < 1) return -1;
+    const int tiles_x = (imgw + sh->tile_w - 1) / sh->tile_w, tiles_y = (imgh + sh->tile_h - 1) / sh->tile_h;
+    return ((tiles_x + sh->n_shards - 1) / sh->n_shards) * tiles_y;   /* slots, some may be empty */
+}
+
+int rt_pack_tiles(rt_context* ctx, const unsigned int* frame_dev, int imgw, int imgh, const rt_shard* sh,
+                  unsigned int* packed_dev) {
+    if (!ctx || !frame_dev || !packed_dev || !sh) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_pack_tiles(frame_dev, packed_dev, imgw, imgh, sh, 0, ctx->stream));
+    return RT_OK;
+}
+
+int rt_unpack_tiles(rt_context* ctx, const unsigned int* packed_dev, int imgw, int imgh, const rt_shard* sh,
+                    unsigned int* frame_dev) {
+    if (!ctx || !frame_dev || !packed_dev || !sh) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_pack_tiles(frame_dev, (unsigned int*)packed_dev, imgw, imgh, sh, 1, ctx->stream));
+    return RT_OK;
+}
+
+int rt_synchronize(rt_context* ctx) {
+    if (!ctx) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+int rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]) {
+    if (!ctx || !out) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    RT_CHECK(ctx, cudaMemcpy(out, ctx->d_counters, sizeof(RtCountersDev), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+int rt_get_timings(rt_context* ctx, float out_ms[3]) {
+    if (!ctx || !out_ms) return RT_ERR_ARG;
+    out_ms[0] = out_ms[1] = out_ms[2] = 0.0f;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->timing_valid) {
+        cudaEventElapsedTime(&out_ms[0], ctx->ev[0], ctx->ev[1]);
+        cudaEventElapsedTime(&out_ms[1], ctx->ev[2], ctx->ev[3]);
+    }
+    if (ctx->build_timed) cudaEventElapsedTime(&out_ms[2], ctx->ev[4], ctx->ev[5]);
+    return RT_OK;
+}
+
+int rt_bvh_info(rt_context* ctx, int* n_prims_in_bvh, int* n_nodes, int* n_planes) {
+    if (!ctx) return RT_ERR_ARG;
+    if (n_prims_in_bvh) *n_prims_in_bvh = ctx->scene.n_bvh_prims;
+    if (n_nodes) *n_nodes = ctx->scene.n_bvh_prims > 1 ? ctx->scene.n_bvh_prims - 1 : 0;
+    if (n_planes) *n_planes = ctx->scene.n_planes;
+    return RT_OK;
+}
+
+int rt_bvh_download(rt_context* ctx, float* nodes16, int* sorted_prim_ids, unsigned int* morton_sorted) {
+    if (!ctx || !ctx->have_scene) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    const int n = ctx->scene.n_bvh_prims;
+    if (nodes16 && n > 1) RT_CHECK(ctx, cudaMemcpy(nodes16, ctx->bb.nodes, sizeof(float) * 16 * (size_t)(n - 1), cudaMemcpyDeviceToHost));
+    if (sorted_prim_ids && n > 0) {
+        std::vector<float4> prims((size_t)n * 3);
+        RT_CHECK(ctx, cudaMemcpy(prims.data(), ctx->bb.prims, sizeof(float4) * 3 * (size_t)n, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < n; i++) {
+            unsigned int tag;
+            memcpy(&tag, &prims[3 * (size_t)i].w, 4);
+            sorted_prim_ids[i] = (int)(tag & RT_TAG_INDEX);
+        }
+    }
+    if (morton_sorted && n > 0) RT_CHECK(ctx, cudaMemcpy(morton_sorted, ctx->bb.keys, sizeof(unsigned int) * (size_t)n, cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+int rt_sort_pairs(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n) {
+    if (!ctx || n < 0) return RT_ERR_ARG;
+    if (n <= 1) return RT_OK;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    unsigned int *tk = nullptr, *tv = nullptr, *hist = nullptr;
+    RT_CHECK(ctx, cudaMalloc((void**)&tk, sizeof(unsigned int) * (size_t)n));
+    RT_CHECK(ctx, cudaMalloc((void**)&tv, sizeof(unsigned int) * (size_t)n));
+    RT_CHECK(ctx, cudaMalloc((void**)&hist, sizeof(unsigned int) * (size_t)rt_radix_hist_entries(n)));
+    cudaError_t e = rt_radix_sort_pairs(keys_dev, vals_dev, tk, tv, hist, n, 1, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(tk); cudaFree(tv); cudaFree(hist);
+    RT_CHECK(ctx, e);
+    return RT_OK;
+}
+
+int rt_sort_pairs_cub(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n) {
+    if (!ctx || n < 0) return RT_ERR_ARG;
+    if (n <= 1) return RT_OK;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_cub_sort_pairs(keys_dev, vals_dev, n, ctx->stream));
+    return RT_OK;
+}
+
+/* ------------------------------------------------------------------ legacy drop-in */
+
+static rt_context* g_legacy = nullptr;
+static bool g_legacy_sky = false;
+
+static void legacy_die(const char* what, rt_context* ctx, int rc) {
+    /* the reference's getLastCudaError: print and exit (common/inc/helper_cuda.h:584-596) */
+    fprintf(stderr, "launchKernel: %s failed (%d): %s\n", what, rc, ctx ? rt_last_error(ctx) : "no context");
+    exit(EXIT_FAILURE);
+}
+
+void launchKernel(unsigned int* result, int imgw, int imgh, rtb_Camera cam, rtb_Object* objects, rtb_Light* lights,
+                  rtb_float3 ambient, float* h_skyVars, unsigned char* h_tex1, unsigned char* h_tex2,
+                  unsigned char* h_tex3, unsigned char* h_tex4, int w, int h, float h_dayTime, bool alias) {
+    int rc;
+    if (!g_legacy) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        rc = rt_create(dev, &g_legacy);
+        if (rc != RT_OK) legacy_die("rt_create", g_legacy, rc);
+    }
+    if (!g_legacy_sky) {   /* textures are read on the first call only (reference kernel.cu:414-442) */
+        const unsigned char* tex[4] = {h_tex1, h_tex2, h_tex3, h_tex4};
+        rc = rt_set_sky(g_legacy, tex, w, h);
+        if (rc != RT_OK) legacy_die("rt_set_sky", g_legacy, rc);
+        g_legacy_sky = true;
+    }
+    rc = rt_set_scene(g_legacy, objects, RTB_OBJECTS_NUMBER, lights, RTB_LIGHTS_NUMBER);
+    if (rc != RT_OK) legacy_die("rt_set_scene", g_legacy, rc);
+    rt_frame fr;
+    memset(&fr, 0, sizeof(fr));
+    fr.cam = cam;
+    fr.ambient[0] = ambient.x; fr.ambient[1] = ambient.y; fr.ambient[2] = ambient.z;
+    memcpy(fr.skyVars, h_skyVars, 16);
+    fr.dayTime = h_dayTime;
+    fr.alias = alias ? 1 : 0;
+    fr.imgw = imgw;
+    fr.imgh = imgh;
+    rc = rt_render(g_legacy, &fr, nullptr, result, nullptr);
+    if (rc != RT_OK) legacy_die("rt_render", g_legacy, rc);
+    /* asynchronous like the reference; the caller synchronises (reference scene.cpp:825) */
+}
+
+/* the context behind launchKernel (tests: options, counters) */
+rt_context* rt_legacy_context(void) { return g_legacy; }
+
+void rtb_scene_launch(rtb_scene* s, unsigned int* out_dev, int imgw, int imgh, unsigned char* tex[4], int texw,
+                      int texh) {
+    rtb_scene_update_camera(s, imgw, imgh);
+    rt_frame fr;
+    rtb_scene_frame(s, imgw, imgh, &fr);
+    int n = 0, nl = 0;
+    rtb_Object* objs = rtb_scene_objects(s, &n);
+    rtb_Light* lights = rtb_scene_lights(s, &nl);
+    rtb_float3 amb;
+    amb.x = fr.ambient[0]; amb.y = fr.ambient[1]; amb.z = fr.ambient[2];
+    launchKernel(out_dev, imgw, imgh, fr.cam, objs, lights, amb, fr.skyVars, tex[0], tex[1], tex[2], tex[3], texw, texh,
+                 fr.dayTime, fr.alias != 0);
+    cudaDeviceSynchronize();
+}
+
+}  // extern "C"

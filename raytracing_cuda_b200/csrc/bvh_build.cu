@@ -1,0 +1,452 @@
+/*
+ * bvh_build.cu -- GPU LBVH build for the tracer (no counterpart in the reference,
+ * which loops linearly over 133 objects held in __constant__ memory,
+ * reference kernel.cu:14, 144-151).
+ *
+ * Pipeline (all on the context's stream, no host round trip):
+ *   rt_setup_kernel    Object AoS (68 B, reference structs.h:27-38) -> leaf records, materials,
+ *                      per-primitive AABB, centroid bounds (atomic min/max on ordered ints)
+ *   rt_morton_kernel   30-bit Morton code of the AABB centroid in the centroid bounds
+ *   sort               stable LSD radix sort of (code, id): 4 passes x 8 bits, per pass
+ *                      histogram -> scan -> ranked scatter (warp match/ballot ranking);
+ *                      scenes <= 2048 primitives use a single-CTA bitonic sort instead
+ *   rt_karras_kernel   Karras 2012 hierarchy: one thread per internal node, common-prefix
+ *                      length via clz, index as tie-breaker for equal codes
+ *   rt_refit_kernel    bottom-up: leaves write their padded box into the parent's record and
+ *                      the second arrival at each node (atomic counter) carries the union up
+ *
+ * Node / leaf-record layout: see rt_device.h.  Refit alone (same topology, moved
+ * primitives) re-runs rt_setup_kernel + rt_refit_kernel.
+ *
+ * Leaf boxes are padded by 2^-15 of their largest |coordinate| plus 2^-20 of the scene
+ * extent, which is >100x the rounding slack of the slab test and of the Moller-Trumbore
+ * acceptance region, so the hierarchy never culls a primitive the leaf test would accept.
+ */
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_device.h"
+
+#define RT_BUILD_THREADS 256
+
+/* order-preserving float <-> uint mapping for atomicMin/Max */
+__device__ __forceinline__ unsigned int f2ord(float f) {
+    unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned int u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u);
+}
+
+/* bounds[0..2] = min centroid, [3..5] = max centroid, [6] = max |coordinate| (all ordered-uint) */
+extern "C" __global__ void rt_bounds_init_kernel(unsigned int* bounds) {
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0xFFFFFFFFu;
+    else if (threadIdx.x < 7) bounds[threadIdx.x] = 0u;
+}
+
+__global__ void rt_setup_kernel(const float* __restrict__ objs, int n_objects, const int* __restrict__ plane_idx,
+                                int n_planes, float4* __restrict__ mats, float4* __restrict__ recs,
+                                float4* __restrict__ planes, int* __restrict__ bvh_src,
+                                float4* __restrict__ prim_lo, float4* __restrict__ prim_hi,
+                                unsigned int* __restrict__ bounds) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    /* neutral elements for the warp-level bounds reduction at the end */
+    unsigned int bmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, bmax[4] = {0u, 0u, 0u, 0u};
+    if (i < n_objects) {
+    const float* o = objs + (size_t)i * 17;
+    const int type = __float_as_int(o[0]);
+    const float shine = o[1], specular = o[2], mirror = o[3];
+    const float3 color = make_float3(o[4], o[5], o[6]);
+    const float3 pos = make_float3(o[7], o[8], o[9]);
+    const float3 size = make_float3(o[10], o[11], o[12]);
+    const float3 third = make_float3(o[13], o[14], o[15]);
+    const bool emissive = (__float_as_uint(o[16]) & 0xFFu) != 0;
+
+    unsigned int tag = (unsigned int)i | (emissive ? RT_TAG_EMISSIVE : 0u);
+    mats[2 * i] = make_float4(color.x, color.y, color.z, mirror);
+    mats[2 * i + 1] = make_float4(shine, specular, emissive ? 1.0f : 0.0f, (float)type);
+
+    int planes_before = 0, my_plane = -1;
+    for (int p = 0; p < n_planes; p++) {
+        const int pi = plane_idx[p];
+        if (pi < i) planes_before++;
+        if (pi == i) my_plane = p;
+    }
+    if (my_plane >= 0) {
+        tag |= RT_TAG_PLANE;
+        /* unknown primitive types never hit in the reference (kernel.cu:128): zero normal */
+        const float3 nrm = (type == RTB_PLANE) ? size : make_float3(0.f, 0.f, 0.f);
+        const float4 q0 = make_float4(pos.x, pos.y, pos.z, __uint_as_float(tag));
+        const float4 q1 = make_float4(nrm.x, nrm.y, nrm.z, 0.f);
+        recs[3 * i] = q0; recs[3 * i + 1] = q1; recs[3 * i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        planes[2 * my_plane] = q0;
+        planes[2 * my_plane + 1] = q1;
+    } else {
+    const int k = i - planes_before;
+    bvh_src[k] = i;
+    float3 lo, hi;
+    if (type == RTB_SPHERE) {
+        tag |= RT_TAG_SPHERE;
+        const float r = size.x;
+        recs[3 * i] = make_float4(pos.x, pos.y, pos.z, __uint_as_float(tag));
+        recs[3 * i + 1] = make_float4(r, __fmul_rn(r, r), 0.f, 0.f);
+        recs[3 * i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float ar = fabsf(r);
+        lo = make_float3(pos.x - ar, pos.y - ar, pos.z - ar);
+        hi = make_float3(pos.x + ar, pos.y + ar, pos.z + ar);
+    } else {
+        /* e1 = v1 - v0, e2 = v2 - v0: the same FADDs the reference does per test (kernel.cu:100-101) */
+        recs[3 * i] = make_float4(pos.x, pos.y, pos.z, __uint_as_float(tag));
+        recs[3 * i + 1] = make_float4(__fadd_rn(size.x, -pos.x), __fadd_rn(size.y, -pos.y), __fadd_rn(size.z, -pos.z), 0.f);
+        recs[3 * i + 2] = make_float4(__fadd_rn(third.x, -pos.x), __fadd_rn(third.y, -pos.y), __fadd_rn(third.z, -pos.z), 0.f);
+        lo = make_float3(fminf(pos.x, fminf(size.x, third.x)), fminf(pos.y, fminf(size.y, third.y)),
+                         fminf(pos.z, fminf(size.z, third.z)));
+        hi = make_float3(fmaxf(pos.x, fmaxf(size.x, third.x)), fmaxf(pos.y, fmaxf(size.y, third.y)),
+                         fmaxf(pos.z, fmaxf(size.z, third.z)));
+    }
+    prim_lo[k] = make_float4(lo.x, lo.y, lo.z, 0.f);
+    prim_hi[k] = make_float4(hi.x, hi.y, hi.z, 0.f);
+    const float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
+    const float ma = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))),
+                           fmaxf(fabsf(lo.z), fabsf(hi.z)));
+    bmin[0] = f2ord(cx); bmin[1] = f2ord(cy); bmin[2] = f2ord(cz);
+    bmax[0] = f2ord(cx); bmax[1] = f2ord(cy); bmax[2] = f2ord(cz); bmax[3] = f2ord(ma);
+    }   /* non-plane */
+    }   /* i < n_objects */
+    /* one atomic per warp and bound instead of one per primitive */
+#pragma unroll
+    for (int a = 0; a < 3; a++) bmin[a] = __reduce_min_sync(0xFFFFFFFFu, bmin[a]);
+#pragma unroll
+    for (int a = 0; a < 4; a++) bmax[a] = __reduce_max_sync(0xFFFFFFFFu, bmax[a]);
+    if ((threadIdx.x & 31) == 0) {
+        if (bmin[0] != 0xFFFFFFFFu) {
+            atomicMin(&bounds[0], bmin[0]); atomicMin(&bounds[1], bmin[1]); atomicMin(&bounds[2], bmin[2]);
+            atomicMax(&bounds[3], bmax[0]); atomicMax(&bounds[4], bmax[1]); atomicMax(&bounds[5], bmax[2]);
+            atomicMax(&bounds[6], bmax[3]);
+        }
+    }
+}
+
+__device__ __forceinline__ unsigned int expand10(unsigned int v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+__global__ void rt_morton_kernel(const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, int n,
+                                 const unsigned int* __restrict__ bounds, unsigned int* __restrict__ keys,
+                                 unsigned int* __restrict__ vals) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const float4 lo = prim_lo[k], hi = prim_hi[k];
+    const float mnx = ord2f(bounds[0]), mny = ord2f(bounds[1]), mnz = ord2f(bounds[2]);
+    const float ex = ord2f(bounds[3]) - mnx, ey = ord2f(bounds[4]) - mny, ez = ord2f(bounds[5]) - mnz;
+    const float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
+    const float ux = ex > 0.f ? (cx - mnx) / ex : 0.f;
+    const float uy = ey > 0.f ? (cy - mny) / ey : 0.f;
+    const float uz = ez > 0.f ? (cz - mnz) / ez : 0.f;
+    const unsigned int qx = (unsigned int)fminf(fmaxf(ux * 1024.f, 0.f), 1023.f);
+    const unsigned int qy = (unsigned int)fminf(fmaxf(uy * 1024.f, 0.f), 1023.f);
+    const unsigned int qz = (unsigned int)fminf(fmaxf(uz * 1024.f, 0.f), 1023.f);
+    keys[k] = (expand10(qx) << 2) | (expand10(qy) << 1) | expand10(qz);
+    vals[k] = (unsigned int)k;
+}
+
+/* ------------------------------------------------------------------ sort */
+
+#define RS_THREADS 256
+#define RS_KEYS_PER_THREAD 16
+#define RS_TILE (RS_THREADS * RS_KEYS_PER_THREAD)   /* 4096 keys per block */
+#define RS_WARPS (RS_THREADS / 32)
+
+/* per-block digit histogram -> hist[digit * n_blocks + block] */
+__global__ void __launch_bounds__(RS_THREADS)
+rs_hist_kernel(const unsigned int* __restrict__ keys, int n, int shift, unsigned int* __restrict__ hist, int n_blocks) {
+    __shared__ unsigned int s_h[256];
+    s_h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * RS_TILE;
+    for (int i = threadIdx.x; i < RS_TILE; i += RS_THREADS) {
+        const int g = base + i;
+        if (g < n) atomicAdd(&s_h[(keys[g] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * n_blocks + blockIdx.x] = s_h[threadIdx.x];
+}
+
+/* exclusive scan of hist[256 * n_blocks] in place, one block */
+__global__ void __launch_bounds__(1024) rs_scan_kernel(unsigned int* __restrict__ hist, int total) {
+    __shared__ unsigned int s_w[32];
+    __shared__ unsigned int s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < total; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned int v = i < total ? hist[i] : 0u;
+        unsigned int s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane == 31) s_w[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int ws = s_w[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, ws, o);
+                if (lane >= o) ws += t;
+            }
+            s_w[lane] = ws;
+        }
+        __syncthreads();
+        const unsigned int carry = s_carry;
+        const unsigned int excl = carry + (warp ? s_w[warp - 1] : 0u) + s - v;
+        if (i < total) hist[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = carry + s_w[31];
+        __syncthreads();
+    }
+}
+
+/* stable ranked scatter.  Warp w owns the contiguous chunk [w*512, (w+1)*512) of the block's
+ * tile and walks it in 16 steps of 32 keys, so rank order == memory order. */
+__global__ void __launch_bounds__(RS_THREADS)
+rs_scatter_kernel(const unsigned int* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
+                  unsigned int* __restrict__ keys_out, unsigned int* __restrict__ vals_out, int n, int shift,
+                  const unsigned int* __restrict__ hist, int n_blocks) {
+    __shared__ unsigned int s_cnt[RS_WARPS][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&s_cnt[0][0])[i] = 0;
+    __syncthreads();
+
+    const int chunk = blockIdx.x * RS_TILE + warp * (32 * RS_KEYS_PER_THREAD);
+    unsigned int key[RS_KEYS_PER_THREAD], val[RS_KEYS_PER_THREAD], rank[RS_KEYS_PER_THREAD];
+#pragma unroll
+    for (int s = 0; s < RS_KEYS_PER_THREAD; s++) {
+        const int g = chunk + s * 32 + lane;
+        const bool valid = g < n;
+        key[s] = valid ? keys_in[g] : 0xFFFFFFFFu;
+        val[s] = valid ? vals_in[g] : 0u;
+        const unsigned int digit = (key[s] >> shift) & 255u;
+        const unsigned int vmask = __ballot_sync(0xFFFFFFFFu, valid);
+        const unsigned int peers = __match_any_sync(0xFFFFFFFFu, digit) & vmask;
+        const unsigned int below = peers & ((1u << lane) - 1u);
+        unsigned int base = 0;
+        const int leader = __ffs(peers) - 1;
+        if (valid && lane == leader) {
+            base = s_cnt[warp][digit];
+            s_cnt[warp][digit] = base + __popc(peers);
+        }
+        base = __shfl_sync(0xFFFFFFFFu, base, leader < 0 ? 0 : leader);
+        rank[s] = base + __popc(below);
+        __syncwarp();
+    }
+    __syncthreads();
+    /* digit d = threadIdx.x: exclusive prefix over warps + global base */
+    {
+        const unsigned int d = threadIdx.x;
+        unsigned int run = hist[d * n_blocks + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) {
+            const unsigned int c = s_cnt[w][d];
+            s_cnt[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < RS_KEYS_PER_THREAD; s++) {
+        const int g = chunk + s * 32 + lane;
+        if (g < n) {
+            const unsigned int digit = (key[s] >> shift) & 255u;
+            const unsigned int dst = s_cnt[warp][digit] + rank[s];
+            keys_out[dst] = key[s];
+            vals_out[dst] = val[s];
+        }
+    }
+}
+
+/* single-CTA bitonic sort of (key,val) for small scenes; 64-bit composite keeps it stable */
+#define SS_MAX 2048
+__global__ void __launch_bounds__(1024) rs_small_sort_kernel(unsigned int* __restrict__ keys,
+                                                             unsigned int* __restrict__ vals, int n) {
+    __shared__ unsigned long long s[SS_MAX];
+    int m = 1;
+    while (m < n) m <<= 1;
+    for (int i = threadIdx.x; i < m; i += blockDim.x)
+        s[i] = i < n ? (((unsigned long long)keys[i] << 32) | vals[i]) : 0xFFFFFFFFFFFFFFFFull;
+    __syncthreads();
+    for (int k = 2; k <= m; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < m; i += blockDim.x) {
+                const int ixj = i ^ j;
+                if (ixj > i) {
+                    const unsigned long long a = s[i], b = s[ixj];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up) { s[i] = b; s[ixj] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        keys[i] = (unsigned int)(s[i] >> 32);
+        vals[i] = (unsigned int)(s[i] & 0xFFFFFFFFull);
+    }
+}
+
+/* sorts in place (result ends in keys/vals); tmp_* and hist are scratch */
+extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned int* tmp_keys,
+                                           unsigned int* tmp_vals, unsigned int* hist, int n, int force_radix,
+                                           cudaStream_t stream) {
+    if (n <= 1) return cudaSuccess;
+    if (n <= SS_MAX && !force_radix) {
+        rs_small_sort_kernel<<<1, 1024, 0, stream>>>(keys, vals, n);
+        return cudaGetLastError();
+    }
+    const int n_blocks = (n + RS_TILE - 1) / RS_TILE;
+    unsigned int *ki = keys, *vi = vals, *ko = tmp_keys, *vo = tmp_vals;
+    for (int pass = 0; pass < 4; pass++) {
+        const int shift = pass * 8;
+        rs_hist_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, n, shift, hist, n_blocks);
+        rs_scan_kernel<<<1, 1024, 0, stream>>>(hist, 256 * n_blocks);
+        rs_scatter_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, vi, ko, vo, n, shift, hist, n_blocks);
+        unsigned int* t = ki; ki = ko; ko = t;
+        t = vi; vi = vo; vo = t;
+    }
+    return cudaGetLastError();   /* 4 passes: result is back in keys/vals */
+}
+
+extern "C" int rt_radix_hist_entries(int n) { return 256 * ((n + RS_TILE - 1) / RS_TILE); }
+
+/* ------------------------------------------------------------------ hierarchy */
+
+/* common-prefix length of sorted keys i and j; index breaks ties between equal codes */
+__device__ __forceinline__ int rt_delta(const unsigned int* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const unsigned int a = keys[i], b = keys[j];
+    if (a == b) return 32 + __clz((unsigned int)i ^ (unsigned int)j);
+    return __clz(a ^ b);
+}
+
+/* children: >=0 internal node, <0 leaf slot (~c).  parent of internal node i in node_parent[i],
+ * of leaf slot j in leaf_parent[j].  Root is internal node 0. */
+__global__ void rt_karras_kernel(const unsigned int* __restrict__ keys, int n, int2* __restrict__ children,
+                                 int* __restrict__ node_parent, int* __restrict__ leaf_parent) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    if (i == 0) node_parent[0] = -1;
+    const int d = (rt_delta(keys, n, i, i + 1) - rt_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = rt_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (rt_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (rt_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = rt_delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (rt_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    int c0, c1;
+    if (lo == gamma) { c0 = ~gamma; leaf_parent[gamma] = i; }
+    else             { c0 = gamma; node_parent[gamma] = i; }
+    if (hi == gamma + 1) { c1 = ~(gamma + 1); leaf_parent[gamma + 1] = i; }
+    else                 { c1 = gamma + 1; node_parent[gamma + 1] = i; }
+    children[i] = make_int2(c0, c1);
+}
+
+__device__ __forceinline__ void rt_store_child_box(float* __restrict__ node, int which, const float3& lo,
+                                                   const float3& hi) {
+    /* node = 16 floats: n0 (c0 x/y), n1 (c1 x/y), n2 (c0 z, c1 z), n3 (children) */
+    float* xy = node + 4 * which;
+    __stcg(xy + 0, lo.x); __stcg(xy + 1, hi.x); __stcg(xy + 2, lo.y); __stcg(xy + 3, hi.y);
+    __stcg(node + 8 + 2 * which, lo.z);
+    __stcg(node + 9 + 2 * which, hi.z);
+}
+
+__global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
+                                const int* __restrict__ bvh_src, const float4* __restrict__ recs,
+                                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
+                                const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
+                                const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
+                                unsigned int* __restrict__ flags, float* __restrict__ nodes,
+                                float4* __restrict__ prims) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const int k = (int)sorted_vals[j];
+    const int obj = bvh_src[k];
+    prims[3 * j] = recs[3 * obj];
+    prims[3 * j + 1] = recs[3 * obj + 1];
+    prims[3 * j + 2] = recs[3 * obj + 2];
+    if (n < 2) return;
+
+    const float4 plo = prim_lo[k], phi = prim_hi[k];
+    const float extent = fmaxf(fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), ord2f(bounds[4]) - ord2f(bounds[1])),
+                               ord2f(bounds[5]) - ord2f(bounds[2]));
+    const float global_pad = 9.5367431640625e-07f * fmaxf(extent, ord2f(bounds[6]));   /* 2^-20 */
+    const float kRel = 3.0517578125e-05f;                                               /* 2^-15 */
+    float3 lo, hi;
+    {
+        const float px = kRel * fmaxf(fabsf(plo.x), fabsf(phi.x)) + global_pad;
+        const float py = kRel * fmaxf(fabsf(plo.y), fabsf(phi.y)) + global_pad;
+        const float pz = kRel * fmaxf(fabsf(plo.z), fabsf(phi.z)) + global_pad;
+        lo = make_float3(plo.x - px, plo.y - py, plo.z - pz);
+        hi = make_float3(phi.x + px, phi.y + py, phi.z + pz);
+    }
+    int child = ~j;
+    int node = leaf_parent[j];
+    while (node >= 0) {
+        const int2 ch = children[node];
+        const int which = (ch.x == child) ? 0 : 1;
+        float* rec = nodes + 16 * (size_t)node;
+        rt_store_child_box(rec, which, lo, hi);
+        if (which == 0) __stcg(rec + 12, __int_as_float(ch.x));
+        else            __stcg(rec + 13, __int_as_float(ch.y));
+        __threadfence();
+        if (atomicAdd(&flags[node], 1u) == 0u) return;   /* first arrival: the sibling will carry on */
+        /* second arrival: the sibling's box is visible (written before its fence + atomic) */
+        const int other = which ^ 1;
+        const float* xy = rec + 4 * other;
+        const float olx = __ldcg(xy + 0), ohx = __ldcg(xy + 1), oly = __ldcg(xy + 2), ohy = __ldcg(xy + 3);
+        const float olz = __ldcg(rec + 8 + 2 * other), ohz = __ldcg(rec + 9 + 2 * other);
+        lo = make_float3(fminf(lo.x, olx), fminf(lo.y, oly), fminf(lo.z, olz));
+        hi = make_float3(fmaxf(hi.x, ohx), fmaxf(hi.y, ohy), fmaxf(hi.z, ohz));
+        child = node;
+        node = node_parent[node];
+    }
+}
+
+
+/* mode 0: full build; mode 1: refit only (topology from the previous build) */
+extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, cudaStream_t stream) {
+    const int T = RT_BUILD_THREADS;
+    rt_bounds_init_kernel<<<1, 32, 0, stream>>>(b->bounds);
+    if (b->n_objects > 0)
+        rt_setup_kernel<<<(b->n_objects + T - 1) / T, T, 0, stream>>>(b->objs, b->n_objects, b->plane_idx, b->n_planes,
+                                                                      b->mats, b->recs, b->planes, b->bvh_src,
+                                                                      b->prim_lo, b->prim_hi, b->bounds);
+    const int n = b->n_bvh;
+    if (n <= 0) return cudaGetLastError();
+    if (mode == 0) {
+        rt_morton_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->prim_lo, b->prim_hi, n, b->bounds, b->keys, b->vals);
+        cudaError_t e = rt_radix_sort_pairs(b->keys, b->vals, b->tmp_keys, b->tmp_vals, b->hist, n, force_radix, stream);
+        if (e != cudaSuccess) return e;
+        if (n >= 2)
+            rt_karras_kernel<<<(n - 1 + T - 1) / T, T, 0, stream>>>(b->keys, n, b->children, b->node_parent, b->leaf_parent);
+    }
+    if (n >= 2) cudaMemsetAsync(b->flags, 0, sizeof(unsigned int) * (size_t)(n - 1), stream);
+    rt_refit_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
+                                                      b->children, b->node_parent, b->leaf_parent, b->flags, b->nodes,
+                                                      b->prims);
+    return cudaGetLastError();
+}

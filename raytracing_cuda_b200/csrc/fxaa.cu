@@ -1,0 +1,325 @@
+/*
+ * fxaa.cu -- the FXAA post-pass (replaces the reference's `antialiasing` kernel,
+ * reference kernel.cu:262-403).
+ *
+ * The filter is a pure function of each interior pixel's 3x3 neighbourhood in the
+ * pre-FXAA image; border pixels pass through (kernel.cu:330, 399-402).  The
+ * reference's out-of-bounds halo loads (operator-precedence slip at
+ * kernel.cu:318-319) only ever feed border pixels, so a clean version needs none.
+ *
+ * HBM-bound: 4 B read + 4 B written per pixel.  Two implementations:
+ *   rt_fxaa_tma_kernel  : persistent CTAs, 64x32-pixel tiles (+1 halo) staged into shared
+ *                         memory by TMA (cp.async.bulk.tensor.2d, 68x34 box, zero OOB fill),
+ *                         double-buffered on two mbarriers; luminance computed once per
+ *                         staged texel; coalesced 128-byte row stores.
+ *   rt_fxaa_smem_kernel : plain shared-memory tile, any width, any shard tile size.
+ *
+ * Arithmetic is spelled with explicit rounding intrinsics in the fused shape the
+ * rebuilt reference has in SASS (luminance = min(255, fma(b,c3, fma(r,c1, g*c2))) * (1/255)f,
+ * blend = fma(1-b, centre, b*neighbour), smoothstep = (3-(f+f))*(f*f), ...), so the two
+ * kernels and the reference agree bit for bit on identical input.
+ */
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_device.h"
+
+__device__ __forceinline__ float fx_lum(unsigned int c) {
+    const float r = (float)(c & 255u), g = (float)((c >> 8) & 255u), b = (float)((c >> 16) & 255u);
+    float l = __fmaf_rn(b, 0.0721750f, __fmaf_rn(r, 0.2126729f, __fmul_rn(g, 0.7151522f)));
+    return __fmul_rn(fminf(l, 255.0f), 0.0039215688593685626984f);
+}
+
+__device__ __forceinline__ unsigned int fx_pack(float r, float g, float b) {
+    r = fmaxf(0.0f, fminf(r, 255.0f));
+    g = fmaxf(0.0f, fminf(g, 255.0f));
+    b = fmaxf(0.0f, fminf(b, 255.0f));
+    return (unsigned int)(((int)b << 16) | ((int)g << 8) | (int)r);
+}
+
+/* Decide from the nine luminances.  Returns false when the pixel passes through
+ * (kernel.cu:349-354); else the blend factor and the neighbour offset (kernel.cu:369-392). */
+__device__ __forceinline__ bool fx_decide(float M, float E, float W, float N, float S, float NE, float NW,
+                                          float SE, float SW, float& b, int& dx, int& dy) {
+    const float high = fmaxf(fmaxf(fmaxf(fmaxf(E, W), N), S), M);
+    const float low = fminf(fminf(fminf(fminf(E, W), N), S), M);
+    const float contrast = __fadd_rn(high, -low);
+    const float threshold = fmaxf(0.0312f, __fmul_rn(0.063f, high));
+    if (contrast < threshold) return false;
+
+    float sum = __fadd_rn(__fadd_rn(__fadd_rn(E, W), S), N);
+    sum = __fadd_rn(__fadd_rn(__fadd_rn(__fmaf_rn(sum, 2.0f, NE), NW), SE), SW);
+    float filter = (float)((double)sum / 12.0);
+    float rc;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(contrast));
+    filter = fminf(__fmul_rn(fabsf(__fadd_rn(filter, -M)), rc), 1.0f);
+    b = __fmul_rn(__fadd_rn(3.0f, -__fadd_rn(filter, filter)), __fmul_rn(filter, filter));
+
+    const float hor = __fadd_rn(__fmaf_rn(fabsf(__fadd_rn(__fadd_rn(N, S), -__fadd_rn(M, M))), 2.0f,
+                                          fabsf(__fadd_rn(__fadd_rn(NE, SE), -__fadd_rn(E, E)))),
+                                fabsf(__fadd_rn(__fadd_rn(NW, SW), -__fadd_rn(W, W))));
+    const float ver = __fadd_rn(__fmaf_rn(fabsf(__fadd_rn(__fadd_rn(E, W), -__fadd_rn(M, M))), 2.0f,
+                                          fabsf(__fadd_rn(__fadd_rn(NE, NW), -__fadd_rn(N, N)))),
+                                fabsf(__fadd_rn(__fadd_rn(SE, SW), -__fadd_rn(S, S))));
+    dx = 0;
+    dy = 0;
+    if (hor >= ver) dy = fabsf(__fadd_rn(N, -M)) >= fabsf(__fadd_rn(S, -M)) ? -1 : 1;
+    else            dx = fabsf(__fadd_rn(E, -M)) >= fabsf(__fadd_rn(W, -M)) ? 1 : -1;
+    return true;
+}
+
+__device__ __forceinline__ unsigned int fx_blend(unsigned int centre, unsigned int nb, float b) {
+    const float omb = __fadd_rn(1.0f, -b);
+    const float r = __fmaf_rn(omb, (float)(centre & 255u), __fmul_rn(b, (float)(nb & 255u)));
+    const float g = __fmaf_rn(omb, (float)((centre >> 8) & 255u), __fmul_rn(b, (float)((nb >> 8) & 255u)));
+    const float bl = __fmaf_rn(omb, (float)((centre >> 16) & 255u), __fmul_rn(b, (float)((nb >> 16) & 255u)));
+    return fx_pack(r, g, bl);
+}
+
+/* ------------------------------------------------------------------ plain shared-memory kernel */
+
+#define FX_BW 32
+#define FX_BH 8
+
+__global__ void __launch_bounds__(FX_BW * FX_BH)
+rt_fxaa_smem_kernel(const unsigned int* __restrict__ in, unsigned int* __restrict__ out, int w, int h,
+                    int tile_w, int tile_h, int n_shards, int shard_id, int stride) {
+    __shared__ unsigned int s_px[FX_BH + 2][FX_BW + 2];
+    __shared__ float s_lum[FX_BH + 2][FX_BW + 2];
+    const int x0 = blockIdx.x * FX_BW - 1, y0 = blockIdx.y * FX_BH - 1;
+    for (int i = threadIdx.y * FX_BW + threadIdx.x; i < (FX_BH + 2) * (FX_BW + 2); i += FX_BW * FX_BH) {
+        const int ly = i / (FX_BW + 2), lx = i % (FX_BW + 2);
+        const int gx = x0 + lx, gy = y0 + ly;
+        unsigned int c = 0;
+        if (gx >= 0 && gx < w && gy >= 0 && gy < h) c = __ldg(in + (size_t)gy * w + gx);
+        s_px[ly][lx] = c;
+        s_lum[ly][lx] = fx_lum(c);
+    }
+    __syncthreads();
+    const int x = blockIdx.x * FX_BW + threadIdx.x, y = blockIdx.y * FX_BH + threadIdx.y;
+    if (x >= w || y >= h) return;
+    if (n_shards > 1 && rt_tile_owner(x, y, tile_w, tile_h, n_shards, stride) != shard_id) return;
+    const int lx = threadIdx.x + 1, ly = threadIdx.y + 1;
+    const unsigned int centre = s_px[ly][lx];
+    unsigned int result = centre;
+    if (x > 0 && y > 0 && x + 1 < w && y + 1 < h) {
+        float b;
+        int dx, dy;
+        if (fx_decide(s_lum[ly][lx], s_lum[ly][lx + 1], s_lum[ly][lx - 1], s_lum[ly - 1][lx], s_lum[ly + 1][lx],
+                      s_lum[ly - 1][lx + 1], s_lum[ly - 1][lx - 1], s_lum[ly + 1][lx + 1], s_lum[ly + 1][lx - 1],
+                      b, dx, dy))
+            result = fx_blend(centre, s_px[ly + dy][lx + dx], b);
+    }
+    out[(size_t)y * w + x] = result;
+}
+
+/* ------------------------------------------------------------------ TMA-staged persistent kernel */
+
+#define FX_TW 64
+#define FX_TH 32
+#define FX_BOXW 68            /* 64 + 2 halo, rounded up to a 16-byte multiple */
+#define FX_BOXH 34
+#define FX_STAGE_BYTES (FX_BOXW * FX_BOXH * 4)
+#define FX_THREADS 256
+
+__device__ __forceinline__ uint32_t fx_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void fx_mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(fx_smem_addr(bar)), "r"(count));
+}
+__device__ __forceinline__ void fx_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fx_smem_addr(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void fx_mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(fx_smem_addr(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void fx_tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::
+            "r"(fx_smem_addr(dst)),
+        "l"(map), "r"(c0), "r"(c1), "r"(fx_smem_addr(bar))
+        : "memory");
+}
+
+/* tile k of this shard -> pixel origin.  Whole frame: row-major over tiles. */
+__device__ __forceinline__ bool fx_tile_origin(int k, int tiles_x, int tiles_y, int n_shards, int shard_id,
+                                               int stride, int& tx, int& ty) {
+    if (n_shards <= 1) {
+        if (k >= tiles_x * tiles_y) return false;
+        tx = k % tiles_x;
+        ty = k / tiles_x;
+        return true;
+    }
+    /* slots: per tile row, ceil(tiles_x / n) candidates i = i0 + m*n with i0 = (shard - j*stride) mod n */
+    const int per_row = (tiles_x + n_shards - 1) / n_shards;
+    if (k >= per_row * tiles_y) return false;
+    ty = k / per_row;
+    const int m = k % per_row;
+    int i0 = (shard_id - ty * stride) % n_shards;
+    if (i0 < 0) i0 += n_shards;
+    tx = i0 + m * n_shards;
+    return true;   /* caller checks tx < tiles_x */
+}
+
+__global__ void __launch_bounds__(FX_THREADS)
+rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned int* __restrict__ in,
+                   unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride) {
+    __shared__ __align__(128) unsigned int s_px[2][FX_BOXH][FX_BOXW];
+    __shared__ float s_lum[FX_BOXH][FX_BOXW];
+    __shared__ __align__(8) uint64_t s_bar[2];
+
+    const int tiles_x = (w + FX_TW - 1) / FX_TW, tiles_y = (h + FX_TH - 1) / FX_TH;
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        fx_mbar_init(&s_bar[0], 1);
+        fx_mbar_init(&s_bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    int k = blockIdx.x;
+    int tx, ty;
+    bool have = fx_tile_origin(k, tiles_x, tiles_y, n_shards, shard_id, stride, tx, ty);
+    if (tid == 0 && have && tx < tiles_x) {
+        fx_mbar_expect_tx(&s_bar[0], FX_STAGE_BYTES);
+        fx_tma_load_2d(&s_px[0][0][0], &in_map, tx * FX_TW - 1, ty * FX_TH - 1, &s_bar[0]);
+    }
+    uint32_t phases = 0;   /* bit s = parity to wait for on stage s */
+    int stage = 0;
+    while (have) {
+        const int kn = k + gridDim.x;
+        int ntx, nty;
+        const bool have_next = fx_tile_origin(kn, tiles_x, tiles_y, n_shards, shard_id, stride, ntx, nty);
+        if (tid == 0 && have_next && ntx < tiles_x) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            fx_mbar_expect_tx(&s_bar[stage ^ 1], FX_STAGE_BYTES);
+            fx_tma_load_2d(&s_px[stage ^ 1][0][0], &in_map, ntx * FX_TW - 1, nty * FX_TH - 1, &s_bar[stage ^ 1]);
+        }
+        if (tx < tiles_x) {
+            fx_mbar_wait(&s_bar[stage], (phases >> stage) & 1u);
+            phases ^= 1u << stage;
+            for (int i = tid; i < FX_BOXH * FX_BOXW; i += FX_THREADS)
+                (&s_lum[0][0])[i] = fx_lum((&s_px[stage][0][0])[i]);
+            __syncthreads();
+            const int cx = tid & 63, ry = tid >> 6;
+            const int x = tx * FX_TW + cx;
+#pragma unroll 2
+            for (int pass = 0; pass < FX_TH / 4; pass++) {
+                const int row = pass * 4 + ry;
+                const int y = ty * FX_TH + row;
+                if (x < w && y < h) {
+                    const int lx = cx + 1, ly = row + 1;
+                    const unsigned int centre = s_px[stage][ly][lx];
+                    unsigned int result = centre;
+                    if (x > 0 && y > 0 && x + 1 < w && y + 1 < h) {
+                        float b;
+                        int dx, dy;
+                        if (fx_decide(s_lum[ly][lx], s_lum[ly][lx + 1], s_lum[ly][lx - 1], s_lum[ly - 1][lx],
+                                      s_lum[ly + 1][lx], s_lum[ly - 1][lx + 1], s_lum[ly - 1][lx - 1],
+                                      s_lum[ly + 1][lx + 1], s_lum[ly + 1][lx - 1], b, dx, dy))
+                            result = fx_blend(centre, s_px[stage][ly + dy][lx + dx], b);
+                    }
+                    out[(size_t)y * w + x] = result;
+                }
+            }
+        }
+        __syncthreads();   /* everyone is done with s_px[stage] and s_lum before they are refilled */
+        k = kn;
+        tx = ntx;
+        ty = nty;
+        have = have_next;
+        stage ^= 1;
+    }
+}
+
+/* pass-through when AA is off (reference kernel.cu:275-278), shard-aware */
+__global__ void rt_copy_kernel(const unsigned int* __restrict__ in, unsigned int* __restrict__ out, int w, int h,
+                               int tile_w, int tile_h, int n_shards, int shard_id, int stride) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= w || y >= h) return;
+    if (n_shards > 1 && rt_tile_owner(x, y, tile_w, tile_h, n_shards, stride) != shard_id) return;
+    out[(size_t)y * w + x] = in[(size_t)y * w + x];
+}
+
+/* gather / scatter of the tiles a shard owns (multi-GPU compositing) */
+__global__ void rt_pack_tiles_kernel(const unsigned int* __restrict__ frame, unsigned int* __restrict__ packed,
+                                     int w, int h, int tile_w, int tile_h, int n_shards, int shard_id, int stride,
+                                     int unpack) {
+    const int tiles_x = (w + tile_w - 1) / tile_w, tiles_y = (h + tile_h - 1) / tile_h;
+    const int per_row = (tiles_x + n_shards - 1) / n_shards;
+    const int slot = blockIdx.x;
+    const int ty = slot / per_row, m = slot % per_row;
+    if (ty >= tiles_y) return;
+    int i0 = (shard_id - ty * stride) % n_shards;
+    if (i0 < 0) i0 += n_shards;
+    const int tx = i0 + m * n_shards;
+    if (tx >= tiles_x) return;
+    unsigned int* dst = packed + (size_t)slot * tile_w * tile_h;
+    for (int i = threadIdx.x; i < tile_w * tile_h; i += blockDim.x) {
+        const int lx = i % tile_w, ly = i / tile_w;
+        const int x = tx * tile_w + lx, y = ty * tile_h + ly;
+        if (x < w && y < h) {
+            if (unpack) ((unsigned int*)frame)[(size_t)y * w + x] = dst[i];
+            else        dst[i] = frame[(size_t)y * w + x];
+        }
+    }
+}
+
+extern "C" cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h,
+                                           const rt_shard* sh, cudaStream_t stream) {
+    dim3 block(FX_BW, FX_BH, 1), grid((w + FX_BW - 1) / FX_BW, (h + FX_BH - 1) / FX_BH, 1);
+    if (sh && sh->n_shards > 1)
+        rt_fxaa_smem_kernel<<<grid, block, 0, stream>>>(in, out, w, h, sh->tile_w, sh->tile_h, sh->n_shards,
+                                                        sh->shard_id, sh->stride);
+    else
+        rt_fxaa_smem_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0);
+    return cudaGetLastError();
+}
+
+extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out,
+                                          int w, int h, const rt_shard* sh, int n_sm, cudaStream_t stream) {
+    const int tiles_x = (w + FX_TW - 1) / FX_TW, tiles_y = (h + FX_TH - 1) / FX_TH;
+    int n = 1, id = 0, st = 0;
+    int slots = tiles_x * tiles_y;
+    if (sh && sh->n_shards > 1) {
+        n = sh->n_shards; id = sh->shard_id; st = sh->stride;
+        slots = ((tiles_x + n - 1) / n) * tiles_y;
+    }
+    int grid = n_sm * 4;
+    if (grid > slots) grid = slots;
+    if (grid < 1) grid = 1;
+    rt_fxaa_tma_kernel<<<grid, FX_THREADS, 0, stream>>>(*map, in, out, w, h, n, id, st);
+    return cudaGetLastError();
+}
+
+extern "C" cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
+                                      cudaStream_t stream) {
+    dim3 block(32, 8, 1), grid((w + 31) / 32, (h + 7) / 8, 1);
+    if (sh && sh->n_shards > 1)
+        rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, sh->tile_w, sh->tile_h, sh->n_shards, sh->shard_id,
+                                                   sh->stride);
+    else
+        rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0);
+    return cudaGetLastError();
+}
+
+extern "C" cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned int* packed, int w, int h,
+                                            const rt_shard* sh, int unpack, cudaStream_t stream) {
+    const int tiles_x = (w + sh->tile_w - 1) / sh->tile_w, tiles_y = (h + sh->tile_h - 1) / sh->tile_h;
+    const int per_row = (tiles_x + sh->n_shards - 1) / sh->n_shards;
+    rt_pack_tiles_kernel<<<per_row * tiles_y, 256, 0, stream>>>(frame, packed, w, h, sh->tile_w, sh->tile_h,
+                                                                sh->n_shards, sh->shard_id, sh->stride, unpack);
+    return cudaGetLastError();
+}

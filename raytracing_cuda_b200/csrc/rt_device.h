@@ -1,0 +1,100 @@
+/*
+ * rt_device.h -- device-side data layout shared by the builder, the tracer and
+ * the host wrapper.
+ *
+ * HBM layout (all 16-byte aligned, float4 granularity):
+ *
+ *   nodes   [n_nodes][4] float4   LBVH internal nodes, children's boxes embedded
+ *        n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)
+ *        n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
+ *        n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)
+ *        n3 = (child0, child1, -, -) as int bits; child >= 0: internal node,
+ *             child < 0: leaf, slot = ~child into `prims`
+ *   prims   [n_bvh_prims][3] float4   leaf records in Morton order
+ *        triangle: q0 = (v0.xyz, tag)  q1 = (e1.xyz, 0)  q2 = (e2.xyz, 0)     e1 = v1-v0, e2 = v2-v0
+ *        sphere  : q0 = (c.xyz,  tag)  q1 = (r, r*r, 0, 0)
+ *        tag = original object index | RT_TAG_SPHERE | RT_TAG_EMISSIVE
+ *   planes  [n_planes][2] float4  (point.xyz, tag) (normal.xyz, 0) -- infinite planes are
+ *                                  tested analytically, outside the BVH
+ *   mats    [n_objects][2] float4 (color.rgb, mirror) (shine, specular, emissive, type)
+ *   recs    [n_objects][3] float4 leaf records in ORIGINAL order (brute-force mode, build input)
+ *
+ * The reference keeps all of this as 133 x 68-byte AoS Objects in __constant__
+ * memory (reference kernel.cu:14) and loops over them linearly per ray
+ * (reference kernel.cu:144-151, 188-193).
+ */
+#ifndef RTB_RT_DEVICE_H
+#define RTB_RT_DEVICE_H
+
+#include <cuda_runtime.h>
+#include "../../include/rtb_api.h"
+
+#define RT_TAG_SPHERE   0x80000000u
+#define RT_TAG_EMISSIVE 0x40000000u
+#define RT_TAG_PLANE    0x20000000u
+#define RT_TAG_INDEX    0x1FFFFFFFu
+
+#define RT_MAX_LIGHTS 8
+#define RT_NODE_SENTINEL 0x7FFFFFFF   /* empty-stack marker / empty tree */
+#define RT_STACK_SIZE 64
+
+struct RtSceneDev {
+    const float4* nodes;
+    const float4* prims;
+    const float4* planes;
+    const float4* mats;
+    const float4* recs;
+    int root;          /* encoded child: >=0 node, <0 leaf, RT_NODE_SENTINEL = empty */
+    int n_bvh_prims;
+    int n_planes;
+    int n_objects;
+};
+
+struct RtLightDev {
+    float px, py, pz, intensity;
+    float cr, cg, cb, _pad;
+};
+
+/* Per-frame uniforms, passed by value as a kernel parameter (the reference uploads the
+ * same data with five cudaMemcpyToSymbol calls per frame, reference kernel.cu:447-451). */
+struct RtFrameDev {
+    float pos[3];
+    float LD[3], LU[3], RD[3], RU[3];
+    float ambient[3];
+    float skyVars[4];
+    float dayTime;
+    int imgw, imgh;
+    int n_lights;
+    RtLightDev lights[RT_MAX_LIGHTS];
+    cudaTextureObject_t sky[4];
+    int sky_all4;
+    /* shard: n_shards <= 1 means whole frame */
+    int tile_w, tile_h, n_shards, shard_id, stride;
+};
+
+struct RtCountersDev {
+    unsigned long long v[RT_CNT_COUNT];
+};
+
+/* scratch + outputs of the LBVH build (bvh_build.cu) */
+struct RtBuildBuffers {
+    const float* objs; int n_objects;
+    const int* plane_idx; int n_planes;
+    float4 *mats, *recs, *planes;
+    int* bvh_src;
+    float4 *prim_lo, *prim_hi;
+    unsigned int* bounds;
+    unsigned int *keys, *vals, *tmp_keys, *tmp_vals, *hist;
+    int2* children; int *node_parent, *leaf_parent;
+    unsigned int* flags;
+    float* nodes; float4* prims;
+    int n_bvh;
+};
+
+/* owner of the tile containing pixel (x,y) */
+__host__ __device__ inline int rt_tile_owner(int x, int y, int tile_w, int tile_h, int n_shards, int stride) {
+    int i = x / tile_w, j = y / tile_h;
+    return (i + j * stride) % n_shards;
+}
+
+#endif

@@ -1,0 +1,240 @@
+/*
+ * trace_common.cuh -- per-ray device routines shared by the tracer kernels:
+ * closest hit / any hit over the LBVH (or brute force), sky lookup, Phong
+ * shading with hard shadows, pixel packing.  Restates reference
+ * kernel.cu:131-225 (trace<depth>) with the linear object loops
+ * (kernel.cu:144-151, 188-193) replaced by LBVH traversal.
+ *
+ * Closest hit keeps the reference's tie rule: strict '<' over increasing object
+ * index (kernel.cu:145) == lexicographic minimum of (t, index); traversal order
+ * therefore cannot change the winner.
+ */
+#ifndef RTB_TRACE_COMMON_CUH
+#define RTB_TRACE_COMMON_CUH
+
+#include "intersect.cuh"
+
+struct RtHit {
+    float t;
+    unsigned int tag;   /* original index | flags; 0xFFFFFFFF = miss */
+    int slot;           /* >=0: BVH slot / record index; <0: ~plane list index */
+};
+
+struct RtLocalCounters {
+    unsigned int node_tests, tri_tests, sphere_tests, plane_tests;
+};
+
+#define RT_MISS 0xFFFFFFFFu
+
+__device__ __forceinline__ vec3 f4xyz(const float4& q) { return v3(q.x, q.y, q.z); }
+
+__device__ __forceinline__ void rt_consider(RtHit& best, float t, unsigned int tag, int slot) {
+    unsigned int idx = tag & RT_TAG_INDEX;
+    if (t < best.t || (t == best.t && idx < (best.tag & RT_TAG_INDEX))) {
+        best.t = t;
+        best.tag = tag;
+        best.slot = slot;
+    }
+}
+
+/* one leaf record (3 float4 at `rec`) against the ray; returns hit and t */
+template <bool COUNT>
+__device__ __forceinline__ bool rt_test_record(const float4* __restrict__ rec, const vec3& o, const vec3& d,
+                                               float& t, unsigned int& tag, RtLocalCounters& cnt) {
+    const float4 q0 = __ldg(rec);
+    const float4 q1 = __ldg(rec + 1);
+    tag = __float_as_uint(q0.w);
+    if (tag & RT_TAG_SPHERE) {
+        if (COUNT) cnt.sphere_tests++;
+        return rt_hit_sphere(o, d, f4xyz(q0), q1.y, t);
+    }
+    if (tag & RT_TAG_PLANE) {
+        if (COUNT) cnt.plane_tests++;
+        return rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t);
+    }
+    const float4 q2 = __ldg(rec + 2);
+    if (COUNT) cnt.tri_tests++;
+    return rt_hit_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t);
+}
+
+/*
+ * ANY = false: closest hit into `best` (planes already folded in by the caller).
+ * ANY = true : returns true at the first non-emissive primitive with t < tmax
+ *              (reference kernel.cu:188-193; negative t counts, as in the reference).
+ */
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o, const vec3& d, RtHit& best,
+                                            float tmax, RtLocalCounters& cnt) {
+    int node = sc.root;
+    if (node == RT_NODE_SENTINEL) return false;
+    const RtRayBox rb = rt_ray_box(o, d);
+    int stack[RT_STACK_SIZE];
+    int sp = 0;
+    const float4* __restrict__ nodes = sc.nodes;
+    while (true) {
+        if (node >= 0) {
+            const float4 n0 = __ldg(nodes + 4 * node);
+            const float4 n1 = __ldg(nodes + 4 * node + 1);
+            const float4 n2 = __ldg(nodes + 4 * node + 2);
+            const float4 n3 = __ldg(nodes + 4 * node + 3);
+            const float lim = ANY ? tmax : fmaxf(best.t, 0.0f);
+            float t0, t1;
+            const bool h0 = rt_slab(rb, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, lim, t0);
+            const bool h1 = rt_slab(rb, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, lim, t1);
+            if (COUNT) cnt.node_tests += 2;
+            int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            if (h0 && h1) {
+                if (t1 < t0) { int tmp = c0; c0 = c1; c1 = tmp; }
+                if (sp < RT_STACK_SIZE) stack[sp++] = c1;
+                node = c0;
+                continue;
+            }
+            if (h0) { node = c0; continue; }
+            if (h1) { node = c1; continue; }
+        } else {
+            const int slot = ~node;
+            float t;
+            unsigned int tag;
+            if (rt_test_record<COUNT>(sc.prims + 3 * slot, o, d, t, tag, cnt)) {
+                if (ANY) {
+                    if (!(tag & RT_TAG_EMISSIVE) && t < tmax) return true;
+                } else {
+                    rt_consider(best, t, tag, slot);
+                }
+            }
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+    return false;
+}
+
+/* closest hit over planes + BVH (BRUTE: over all records in original order) */
+template <bool BRUTE, bool COUNT>
+__device__ __forceinline__ RtHit rt_closest(const RtSceneDev& sc, const vec3& o, const vec3& d,
+                                            RtLocalCounters& cnt) {
+    RtHit best;
+    best.t = __int_as_float(0x7f800000);
+    best.tag = RT_MISS;
+    best.slot = 0;
+    if (BRUTE) {
+        for (int i = 0; i < sc.n_objects; i++) {
+            float t;
+            unsigned int tag;
+            if (rt_test_record<COUNT>(sc.recs + 3 * i, o, d, t, tag, cnt) && t < best.t) {
+                best.t = t;
+                best.tag = tag;
+                best.slot = i;
+            }
+        }
+        return best;
+    }
+    for (int p = 0; p < sc.n_planes; p++) {
+        const float4 q0 = __ldg(sc.planes + 2 * p), q1 = __ldg(sc.planes + 2 * p + 1);
+        float t;
+        if (COUNT) cnt.plane_tests++;
+        if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t)) rt_consider(best, t, __float_as_uint(q0.w), ~p);
+    }
+    rt_traverse<false, COUNT>(sc, o, d, best, 0.0f, cnt);
+    return best;
+}
+
+/* reference kernel.cu:188-193 */
+template <bool BRUTE, bool COUNT>
+__device__ __forceinline__ bool rt_occluded(const RtSceneDev& sc, const vec3& o, const vec3& d, float tmax,
+                                            RtLocalCounters& cnt) {
+    if (BRUTE) {
+        for (int i = 0; i < sc.n_objects; i++) {
+            float t;
+            unsigned int tag;
+            if (__float_as_uint(__ldg(&sc.recs[3 * i].w)) & RT_TAG_EMISSIVE) continue;
+            if (rt_test_record<COUNT>(sc.recs + 3 * i, o, d, t, tag, cnt) && t < tmax) return true;
+        }
+        return false;
+    }
+    for (int p = 0; p < sc.n_planes; p++) {
+        const float4 q0 = __ldg(sc.planes + 2 * p), q1 = __ldg(sc.planes + 2 * p + 1);
+        float t;
+        if (COUNT) cnt.plane_tests++;
+        if (__float_as_uint(q0.w) & RT_TAG_EMISSIVE) continue;
+        if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t) && t < tmax) return true;
+    }
+    RtHit dummy;
+    return rt_traverse<true, COUNT>(sc, o, d, dummy, tmax, cnt);
+}
+
+/* surface normal at the hit (reference kernel.cu:66, 87, 123) */
+template <bool BRUTE>
+__device__ __forceinline__ vec3 rt_hit_normal(const RtSceneDev& sc, const RtHit& h, const vec3& P) {
+    if (!BRUTE && h.slot < 0) return f4xyz(__ldg(sc.planes + 2 * (~h.slot) + 1));
+    const float4* rec = (BRUTE ? sc.recs : sc.prims) + 3 * h.slot;
+    if (h.tag & RT_TAG_PLANE) return f4xyz(__ldg(rec + 1));
+    if (h.tag & RT_TAG_SPHERE) return rt_normalize(rt_sub(P, f4xyz(__ldg(rec))));
+    return rt_normalize(rt_cross(f4xyz(__ldg(rec + 1)), f4xyz(__ldg(rec + 2))));
+}
+
+/* reference kernel.cu:154-164 with the truncating / wrapping uchar4 operators of structs.h:86-91.
+ * Maps with weight 0 contribute (uchar)(v*0.0f) = 0, so skipping them is bit-identical. */
+__device__ __forceinline__ vec3 rt_sky(const RtFrameDev& f, const vec3& d) {
+    const double PI = RTB_PI;
+    float y = (float)(1 - (asinf(d.y) + PI / 2.0f) / PI);
+    float x = fmodf((float)((atan2f(d.x, d.z) + PI) / (2.0f * PI) + f.dayTime), 1);
+    unsigned char r = 0, g = 0, b = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float w = f.skyVars[k];
+        if (w != 0.0f || f.sky_all4) {
+            const uchar4 v = tex2D<uchar4>(f.sky[k], x, y);
+            r = (unsigned char)(r + (unsigned char)(v.x * w));
+            g = (unsigned char)(g + (unsigned char)(v.y * w));
+            b = (unsigned char)(b + (unsigned char)(v.z * w));
+        }
+    }
+    return vscale(v3((float)r, (float)g, (float)b), 1.0f / 255.0f);
+}
+
+/* reference kernel.cu:26-32 */
+__device__ __forceinline__ unsigned int rt_pack(float r, float g, float b) {
+    r = clampf(r, 0.0f, 255.0f);
+    g = clampf(g, 0.0f, 255.0f);
+    b = clampf(b, 0.0f, 255.0f);
+    return (unsigned int)(((int)b << 16) | ((int)g << 8) | (int)r);
+}
+
+/* reference kernel.cu:244-253, in the fused shape of the rebuilt reference's SASS */
+__device__ __forceinline__ vec3 rt_primary_dir(const RtFrameDev& f, int x, int y) {
+    const float partX = __fmul_rn((float)x, rt_rcp_approx((float)(f.imgw - 1)));
+    const float partY = __fmul_rn((float)y, rt_rcp_approx((float)(f.imgh - 1)));
+    vec3 t;
+    {
+        float vd = __fmaf_rn(partX, __fadd_rn(f.RD[0], -f.LD[0]), f.LD[0]);
+        float vu = __fmaf_rn(partX, __fadd_rn(f.RU[0], -f.LU[0]), f.LU[0]);
+        t.x = __fmaf_rn(-partY, __fadd_rn(vu, -vd), vu);
+    }
+    {
+        float vd = __fmaf_rn(partX, __fadd_rn(f.RD[1], -f.LD[1]), f.LD[1]);
+        float vu = __fmaf_rn(partX, __fadd_rn(f.RU[1], -f.LU[1]), f.LU[1]);
+        t.y = __fmaf_rn(-partY, __fadd_rn(vu, -vd), vu);
+    }
+    {
+        float vd = __fmaf_rn(partX, __fadd_rn(f.RD[2], -f.LD[2]), f.LD[2]);
+        float vu = __fmaf_rn(partX, __fadd_rn(f.RU[2], -f.LU[2]), f.LU[2]);
+        t.z = __fmaf_rn(-partY, __fadd_rn(vu, -vd), vu);
+    }
+    return rt_normalize(t);
+}
+
+/* does this shard have to trace pixel (x,y)?  own tile, or 1-pixel apron of an own tile */
+__device__ __forceinline__ bool rt_shard_owns(const RtFrameDev& f, int x, int y) {
+    return rt_tile_owner(x, y, f.tile_w, f.tile_h, f.n_shards, f.stride) == f.shard_id;
+}
+__device__ __forceinline__ bool rt_shard_needs(const RtFrameDev& f, int x, int y) {
+    if (f.n_shards <= 1) return true;
+    const int x0 = max(x - 1, 0), x1 = min(x + 1, f.imgw - 1);
+    const int y0 = max(y - 1, 0), y1 = min(y + 1, f.imgh - 1);
+    /* the 3x3 neighbourhood spans at most 2x2 tiles: test its corners */
+    return rt_shard_owns(f, x0, y0) || rt_shard_owns(f, x1, y0) || rt_shard_owns(f, x0, y1) ||
+           rt_shard_owns(f, x1, y1) || rt_shard_owns(f, x, y);
+}
+
+#endif
