@@ -104,6 +104,9 @@ int  rt_set_stream(rt_context* ctx, void* cuda_stream);
 /* Four equirectangular RGBA8 sky maps, HOST memory, w*h*4 bytes each
  * (reference kernel.cu:418-436).  Copied to device once. */
 int  rt_set_sky(rt_context* ctx, const unsigned char* const tex[4], int w, int h);
+/* Let `ctx` sample the sky maps `owner` uploaded (same device; 512 MiB is uploaded once, `owner` must
+ * outlive `ctx`). */
+int  rt_share_sky(rt_context* ctx, rt_context* owner);
 
 /* Upload primitives + lights (HOST memory) and build / refit the LBVH.
  * Classifies the change against the previous call: identical geometry ->
@@ -137,6 +140,9 @@ int  rt_synchronize(rt_context* ctx);
 int  rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]);
 /* ms of the last frame's kernels (RT_OPT_TIMING=1): [0]=trace [1]=fxaa [2]=bvh build/refit */
 int  rt_get_timings(rt_context* ctx, float out_ms[3]);
+/* FP32 FFMA throughput of the device in TFLOP/s (2 flops per FFMA), measured with a register-resident
+ * FMA chain kernel: the denominator of the tracer's FP32 roofline fraction. */
+int  rt_measure_fp32_peak(rt_context* ctx, float* tflops);
 
 /* LBVH introspection (tests): copies to HOST.  nodes: 16 floats per node. */
 int  rt_bvh_info(rt_context* ctx, int* n_prims_in_bvh, int* n_nodes, int* n_planes);

@@ -41,6 +41,7 @@ cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int
                            cudaStream_t stream);
 cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned int* packed, int w, int h, const rt_shard* sh,
                                  int unpack, cudaStream_t stream);
+cudaError_t rt_launch_ffma_peak(int n_sm, cudaStream_t stream, float* ms, double* flops);
 }
 
 struct rt_context {
@@ -53,7 +54,7 @@ struct rt_context {
     /* sky */
     cudaArray_t sky_arr[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaTextureObject_t sky_tex[4] = {0, 0, 0, 0};
-    bool have_sky = false;
+    bool have_sky = false, own_sky = true;
 
     /* scene */
     std::vector<rtb_Object> host_objs;      /* last upload, for change classification */
@@ -185,7 +186,7 @@ int rt_destroy(rt_context* ctx) {
     if (!ctx) return RT_ERR_ARG;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
-    for (int i = 0; i < 4; i++) {
+    for (int i = 0; i < 4 && ctx->own_sky; i++) {
         if (ctx->sky_tex[i]) cudaDestroyTextureObject(ctx->sky_tex[i]);
         if (ctx->sky_arr[i]) cudaFreeArray(ctx->sky_arr[i]);
     }
@@ -216,6 +217,10 @@ int rt_set_stream(rt_context* ctx, void* cuda_stream) {
 int rt_set_sky(rt_context* ctx, const unsigned char* const tex[4], int w, int h) {
     if (!ctx || !tex || w <= 0 || h <= 0) return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->own_sky) {
+        for (int i = 0; i < 4; i++) { ctx->sky_tex[i] = 0; ctx->sky_arr[i] = nullptr; }
+        ctx->own_sky = true;
+    }
     for (int i = 0; i < 4; i++) {
         if (!tex[i]) return fail(ctx, RT_ERR_ARG, "null sky map");
         if (ctx->sky_tex[i]) { cudaDestroyTextureObject(ctx->sky_tex[i]); ctx->sky_tex[i] = 0; }
@@ -237,6 +242,30 @@ int rt_set_sky(rt_context* ctx, const unsigned char* const tex[4], int w, int h)
         RT_CHECK(ctx, cudaCreateTextureObject(&ctx->sky_tex[i], &rd, &td, nullptr));
     }
     ctx->have_sky = true;
+    return RT_OK;
+}
+
+int rt_share_sky(rt_context* ctx, rt_context* owner) {
+    if (!ctx || !owner || ctx == owner) return RT_ERR_ARG;
+    if (!owner->have_sky) return fail(ctx, RT_ERR_STATE, "owner has no sky maps");
+    if (owner->device != ctx->device) return fail(ctx, RT_ERR_ARG, "sky maps live on another device");
+    for (int i = 0; i < 4 && ctx->own_sky; i++) {
+        if (ctx->sky_tex[i]) cudaDestroyTextureObject(ctx->sky_tex[i]);
+        if (ctx->sky_arr[i]) cudaFreeArray(ctx->sky_arr[i]);
+    }
+    for (int i = 0; i < 4; i++) { ctx->sky_tex[i] = owner->sky_tex[i]; ctx->sky_arr[i] = nullptr; }
+    ctx->own_sky = false;
+    ctx->have_sky = true;
+    return RT_OK;
+}
+
+int rt_measure_fp32_peak(rt_context* ctx, float* tflops) {
+    if (!ctx || !tflops) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    float ms = 0.f;
+    double flops = 0.0;
+    RT_CHECK(ctx, rt_launch_ffma_peak(ctx->n_sm, ctx->stream, &ms, &flops));
+    *tflops = ms > 0.f ? (float)(flops / (ms * 1e-3) / 1e12) : 0.f;
     return RT_OK;
 }
 

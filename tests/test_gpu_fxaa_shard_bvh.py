@@ -1,0 +1,189 @@
+"""GPU tests of the FXAA kernels, the screen-tile shards and the LBVH builder (all through the C-ABI)."""
+import os
+
+import numpy as np
+import pytest
+
+import gpu_util as gu
+import oracle_util as ou
+import raytracing_cuda_b200 as rt
+from raytracing_cuda_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+
+
+# ---------------------------------------------------------------- FXAA (reference kernel.cu:262-403)
+
+def _fxaa(r, img, impl, shard=None):
+    import torch
+    h, w = img.shape
+    src = gu.to_dev(img)
+    dst = torch.zeros_like(src)
+    r.set_option(_lib.RT_OPT_FXAA_IMPL, impl)
+    r.fxaa(src, dst, w, h, shard)
+    r.synchronize()
+    return gu.to_host_u32(dst, (h, w))
+
+
+@pytest.mark.parametrize("impl", [0, 1])
+def test_fxaa_matches_reference_goldens_bit_exact(impl):
+    """Identical input -> the FXAA result must equal the reference kernel text's, bit for bit."""
+    FX = np.load(os.path.join(ou.GOLDEN, "fxaa.npz"))
+    r = gu.renderer()
+    for name in ("noise", "edges"):
+        got = _fxaa(r, FX[name + "_in"], impl)
+        want = FX[name + "_out"]
+        assert (got == want).mean() > 0.9999, (name, impl, float((got == want).mean()))
+        assert ou.compare_images(got, want)["max_abs"] <= 1
+
+
+@pytest.mark.parametrize("shape", [(2, 4), (3, 8), (33, 64), (34, 68), (97, 131), (108, 192), (720, 1280), (1080, 1920)])
+def test_fxaa_tma_equals_smem_equals_oracle(shape):
+    """Ragged sizes: tiny images, sizes around the 64x32 tile, widths not divisible by 4 (TMA falls back)."""
+    rng = np.random.default_rng(shape[0] * 7919 + shape[1])
+    h, w = shape
+    img = rng.integers(0, 1 << 24, size=(h, w), dtype=np.uint32)
+    img[h // 3: h // 2, w // 4: w // 2] = 0x00203040          # a flat patch: pass-through region
+    r = gu.renderer()
+    a = _fxaa(r, img, 0)
+    b = _fxaa(r, img, 1)
+    assert (a == b).all()
+    want = ou.oracle_fxaa(img)
+    assert (a == want).mean() > 0.9999 and ou.compare_images(a, want)["max_abs"] <= 1
+    # borders pass through
+    assert (a[0] == img[0]).all() and (a[-1] == img[-1]).all() and (a[:, 0] == img[:, 0]).all() and (a[:, -1] == img[:, -1]).all()
+
+
+# ---------------------------------------------------------------- shards (multi-GPU partition on one GPU)
+
+@pytest.mark.parametrize("n", [2, 3, 4, 8])
+@pytest.mark.parametrize("tile", [(64, 32), (48, 24)])
+def test_shard_count_invariance(n, tile):
+    """N logical shards on one GPU: every pixel owned exactly once and the composite equals the
+    unsharded frame bit for bit (1-pixel apron -> no halo exchange)."""
+    import torch
+    r = gu.renderer()
+    s = rt.Scene()
+    w, h = 640, 360
+    f = s.configure(view=5, hours=18.0, imgw=w, imgh=h, alias=True)
+    full, _ = gu.render(r, s, f, want_ids=False), None
+    full = full[0] if isinstance(full, tuple) else full
+    comp = np.zeros((h, w), dtype=np.uint32)
+    owned = np.zeros((h, w), dtype=np.int32)
+    frame_dev = torch.zeros(h * w, dtype=torch.int32, device="cuda")
+    for k in range(n):
+        sh = rt.make_shard(n, k, tile[0], tile[1])
+        part = r.render_to_host(f, shard=sh)
+        yy, xx = np.mgrid[0:h, 0:w]
+        mine = ((xx // tile[0]) + (yy // tile[1]) * sh.stride) % n == k
+        owned += mine
+        comp[mine] = part[mine]
+        assert (part[~mine] == 0).all()      # a shard writes only what it owns
+        # pack -> unpack reproduces the owned pixels (the gather path of bench.py --mode tiles)
+        slots = r.tile_slots(sh, w, h)
+        packed = torch.zeros(slots * tile[0] * tile[1], dtype=torch.int32, device="cuda")
+        part_dev = gu.to_dev(part)
+        r.pack_tiles(part_dev, w, h, sh, packed)
+        r.unpack_tiles(packed, w, h, sh, frame_dev)
+    r.synchronize()
+    assert (owned == 1).all()
+    assert (comp == full).all()
+    assert (gu.to_host_u32(frame_dev, (h, w)) == full).all()
+
+
+# ---------------------------------------------------------------- LBVH builder
+
+def _check_bvh(r, n_prims):
+    nodes, ids, keys = r.bvh_download()
+    assert len(ids) == n_prims and sorted(ids.tolist()) == sorted(set(ids.tolist()))
+    assert (np.diff(keys.astype(np.int64)) >= 0).all()
+    if n_prims < 2:
+        return
+    assert nodes.shape == (n_prims - 1, 16)
+    children = nodes[:, 12:14].copy().view(np.int32)
+    seen_leaf = np.zeros(n_prims, dtype=np.int32)
+    seen_node = np.zeros(n_prims - 1, dtype=np.int32)
+    seen_node[0] = 1
+    lo = np.stack([nodes[:, [0, 2, 8]], nodes[:, [4, 6, 10]]], 1)    # [node][child][xyz]
+    hi = np.stack([nodes[:, [1, 3, 9]], nodes[:, [5, 7, 11]]], 1)
+    assert (lo <= hi).all()
+    for i in range(n_prims - 1):
+        for c in range(2):
+            ch = int(children[i, c])
+            if ch < 0:
+                seen_leaf[~ch] += 1
+            else:
+                seen_node[ch] += 1
+                # a child's box (as stored in its parent) contains its own children's boxes
+                assert (lo[i, c] <= lo[ch].min(0) + 1e-6).all() and (hi[i, c] >= hi[ch].max(0) - 1e-6).all()
+    assert (seen_leaf == 1).all() and (seen_node == 1).all()
+
+
+def test_bvh_structure_builtin_scene_both_sorts():
+    r = gu.renderer()
+    s = rt.Scene()
+    s.set_time(14.0)
+    r.set_scene(s.objects, s.lights)
+    assert r.bvh_info() == {"prims": 132, "nodes": 131, "planes": 1}
+    _check_bvh(r, 132)
+    a = r.bvh_download()
+    r.set_option(_lib.RT_OPT_FORCE_RADIX, 1)           # multi-pass radix instead of the single-CTA bitonic sort
+    r.set_scene(s.objects[:50], s.lights)              # topology change -> rebuild
+    r.set_scene(s.objects, s.lights)
+    b = r.bvh_download()
+    assert (a[1] == b[1]).all() and (a[2] == b[2]).all() and (a[0] == b[0]).all()
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 257, 4096, 4097, 100_003, 1_000_000])
+def test_radix_sort_matches_cub(n):
+    import torch
+    r = gu.renderer()
+    g = torch.Generator(device="cuda").manual_seed(n)
+    bits = 30 if n % 2 else 6                           # many duplicates on even n: stability matters
+    keys = torch.randint(0, 1 << bits, (n,), generator=g, device="cuda", dtype=torch.int32)
+    vals = torch.arange(n, device="cuda", dtype=torch.int32)
+    k1, v1, k2, v2 = keys.clone(), vals.clone(), keys.clone(), vals.clone()
+    r.sort_pairs(k1, v1, n)
+    r.sort_pairs(k2, v2, n, use_cub=True)
+    torch.cuda.synchronize()
+    assert torch.equal(k1, k2) and torch.equal(v1, v2)
+    ks, order = torch.sort(keys.long(), stable=True)
+    assert torch.equal(k1.long(), ks) and torch.equal(v1.long(), order)
+
+
+def test_refit_after_motion_equals_rebuild():
+    """Sun/moon spheres and the sea level move every frame (reference scene.cpp:758-776, 709): the refit
+    path must render exactly what a fresh build renders."""
+    r = gu.renderer()
+    s = rt.Scene()
+    f = s.configure(view=6, hours=14.0, imgw=320, imgh=180, alias=True)
+    gu.render(r, s, f)
+    s.set_sea_level(2.0)
+    f = s.configure(view=6, hours=16.5, imgw=320, imgh=180, alias=True)
+    a, ida = gu.render(r, s, f)                         # same topology -> refit
+    r2 = rt.Renderer(0)
+    r2.set_sky(gu.sky_small())
+    b, idb = gu.render(r2, s, f)                        # fresh context -> full build
+    r2.close()
+    assert (a == b).all() and (ida == idb).all()
+
+
+def test_terrain_bvh_equals_bruteforce():
+    """Config 4's generator at a size the brute-force kernel finishes quickly: 2*96*96+3 objects."""
+    r = gu.renderer()
+    objs = rt.terrain_objects(96)
+    s = rt.Scene()
+    s.set_pose((324.4, 330.0, -84.0), 141.2, -35.0)
+    s.set_time(14.0)
+    f = s.frame(320, 180)
+    f.alias = 1
+    r.set_scene(objs, s.lights)
+    _check_bvh(r, len(objs) - 1)
+    a, ida = r.render_to_host(f, want_ids=True)
+    r.set_option(_lib.RT_OPT_TRAVERSAL, 1)
+    b, idb = r.render_to_host(f, want_ids=True)
+    assert (ida == idb).all() and (a == b).all()
+    assert (ida > 0).mean() > 0.5                        # the terrain fills most of the view
+    o = ou.oracle_render(objs, s.lights, f, gu.sky_small(), x_step=4, y_step=4, want_out=False)
+    m = o["ids"][::4, ::4] != ida[::4, ::4]
+    assert m.mean() <= 1e-3

@@ -1,0 +1,52 @@
+"""Exactness claims the CUDA kernels rely on (csrc/intersect.cuh, csrc/vecmath.h), proved on the CPU."""
+import numpy as np
+
+
+def _neighbours(x32):
+    x = np.float32(x32)
+    return [np.nextafter(x, np.float32(-np.inf), dtype=np.float32), x, np.nextafter(x, np.float32(np.inf), dtype=np.float32)]
+
+
+def test_double_literal_compares_equal_float_compares():
+    """(double)x < 0.001 <=> x < 0.001f, (double)x <= -0.01 <=> x < -0.01f, (double)x > 0.00001 <=> x > 0.00001f
+    for EVERY float x: it is enough to check the floats around the literal."""
+    for lit, dbl_op, flt_op in ((0.001, lambda x: float(x) < 0.001, lambda x: x < np.float32(0.001)),
+                                (-0.01, lambda x: float(x) <= -0.01, lambda x: x < np.float32(-0.01)),
+                                (0.00001, lambda x: float(x) > 0.00001, lambda x: x > np.float32(0.00001))):
+        centre = np.float32(lit)
+        cands = []
+        for c in _neighbours(centre):
+            cands += _neighbours(c)
+        for x in cands:
+            assert dbl_op(x) == bool(flt_op(x)), (lit, x)
+        # monotone predicates: agreement around the threshold implies agreement everywhere
+        assert float(cands[0]) < lit < float(cands[-1])
+
+
+def test_fp64_reciprocal_rounded_equals_fp32_reciprocal():
+    """(float)(1.0/(double)n) == correctly rounded 1.0f/n: structs.h:82-84's FP64 divide can be a
+    single-precision __frcp_rn on the device."""
+    rng = np.random.default_rng(5)
+    bits = rng.integers(0x00800000, 0x7F000000, size=4_000_000, dtype=np.uint32)
+    n = bits.view(np.float32)
+    a = (1.0 / n.astype(np.float64)).astype(np.float32)
+    b = np.float32(1.0) / n
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+    # exhaustive over one binade (the mantissa pattern is all that matters)
+    m = (np.arange(1 << 23, dtype=np.uint32) | np.uint32(0x3F800000)).view(np.float32)
+    a = (1.0 / m.astype(np.float64)).astype(np.float32)
+    b = np.float32(1.0) / m
+    assert (a.view(np.uint32) == b.view(np.uint32)).all()
+
+
+def test_max_double_zero_equals_fmaxf():
+    x = np.array([-1.5, -0.0, 0.0, 1e-30, 0.25, 3.0], dtype=np.float32)
+    assert (np.maximum(0.0, x.astype(np.float64)).astype(np.float32) == np.maximum(np.float32(0), x)).all()
+
+
+def test_pack_roundtrip_all_bytes():
+    """v/255*255 truncates back to v for all 256 values when done as two FP32 multiplies (sky texels,
+    reference kernel.cu:163, 256-257)."""
+    v = np.arange(256, dtype=np.float32)
+    back = (v * np.float32(1.0 / 255.0)) * np.float32(255.0)
+    assert (np.clip(back, 0, 255).astype(np.int32) == np.arange(256)).all()

@@ -1,0 +1,150 @@
+"""The oracle (oracle/rt_oracle.cpp) pinned against the reference:
+  - golden frames rendered by the reference's own kernel.cu text compiled for the host
+    (tests/golden/frames.npz, fxaa.npz; generator tests/gen_golden.py) -- bit-exact;
+  - the live reference build under oracle/_ref when present -- bit-exact;
+  - hand-derived known answers for reference kernel.cu:41-129 (checkHit)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_util as ou
+import raytracing_cuda_b200 as rt
+from raytracing_cuda_b200.structs import OBJECT_DTYPE, PLANE, SPHERE, TRIANGLE
+
+FR = np.load(os.path.join(ou.GOLDEN, "frames.npz"))
+FX = np.load(os.path.join(ou.GOLDEN, "fxaa.npz"))
+W, H = 192, 108
+
+
+def _obj(type_, pos=(0, 0, 0), size=(0, 0, 0), third=(0, 0, 0)):
+    o = np.zeros(1, dtype=OBJECT_DTYPE)
+    o["type"], o["pos"], o["size"], o["third"] = type_, pos, size, third
+    return o
+
+
+@pytest.fixture(scope="module")
+def sky():
+    return rt.synthetic_sky(512, 256)
+
+
+@pytest.mark.parametrize("view", [5, 6])
+@pytest.mark.parametrize("tod", list(rt.TIME_PRESETS))
+def test_oracle_matches_reference_golden_frames(view, tod, sky):
+    s = rt.Scene()
+    f = s.configure(view=view, hours=rt.TIME_PRESETS[tod], imgw=W, imgh=H, alias=True)
+    r = ou.oracle_render(s.objects, s.lights, f, sky)
+    key = "v%d_%s" % (view, tod)
+    assert (r["base"] == FR[key + "_base"]).all()
+    assert (r["ids"] == FR[key + "_ids"].astype(np.int32)).all()
+    assert (r["out"] == FR[key + "_out"]).all()
+    # workload shape of SURVEY 3.3: rays per pixel
+    c = r["counters"]
+    rpp = (c["rays_primary"] + c["rays_shadow"] + c["rays_mirror"]) / (W * H)
+    assert (3.1 < rpp < 3.4) if view == 5 else (2.1 < rpp < 2.35)
+
+
+def test_oracle_fxaa_matches_reference_goldens():
+    for name in ("noise", "edges"):
+        assert (ou.oracle_fxaa(FX[name + "_in"]) == FX[name + "_out"]).all()
+    # AA off = pass-through; borders pass through (reference kernel.cu:275-278, 399-402)
+    out = ou.oracle_fxaa(FX["noise_in"])
+    src = FX["noise_in"]
+    assert (out[0] == src[0]).all() and (out[-1] == src[-1]).all() and (out[:, 0] == src[:, 0]).all() and (out[:, -1] == src[:, -1]).all()
+    assert (out[1:-1, 1:-1] != src[1:-1, 1:-1]).mean() > 0.5
+
+
+@pytest.mark.skipif(ou.ref_lib("trace_cpu") is None, reason="oracle/_ref/libref_trace_cpu.so not built (needs /root/reference)")
+def test_oracle_matches_live_reference(sky):
+    s = rt.Scene()
+    for view, hours, sea, w, h in ((5, 9.3, -4.5, 97, 61), (6, 17.5, 3.5, 128, 40), (5, 21.0, 11.5, 64, 64)):
+        s.set_sea_level(sea)
+        f = s.configure(view=view, hours=hours, imgw=w, imgh=h, alias=True)
+        a = ou.oracle_render(s.objects, s.lights, f, sky)
+        b = ou.ref_cpu_render(s.objects, s.lights, f, sky)
+        for k in ("out", "base", "ids"):
+            assert (a[k] == b[k]).all(), (view, hours, k)
+
+
+@pytest.mark.skipif(ou.ref_lib("trace_cpu") is None, reason="needs oracle/_ref/libref_trace_cpu.so")
+def test_check_hit_random_vs_live_reference():
+    rng = np.random.default_rng(11)
+    n_hit = 0
+    for _ in range(3000):
+        kind = int(rng.integers(0, 3))
+        o = _obj(kind, rng.uniform(-5, 5, 3), rng.uniform(-5, 5, 3) if kind != SPHERE else (rng.uniform(0.5, 4),) * 3,
+                 rng.uniform(-5, 5, 3))
+        org = rng.uniform(-6, 6, 3).astype(np.float32)
+        d = rng.normal(size=3)
+        d = (d / np.linalg.norm(d)).astype(np.float32)
+        a, b = ou.oracle_check_hit(o, org, d), ou.ref_check_hit(o, org, d)
+        assert a[0] == b[0]
+        if a[0]:
+            n_hit += 1
+            assert np.float32(a[1]).tobytes() == np.float32(b[1]).tobytes()
+            assert np.array(a[2:], np.float32).tobytes() == np.array(b[2:], np.float32).tobytes()
+    assert n_hit > 300
+
+
+def test_check_hit_known_answers():
+    # unit sphere at z=5 seen from the origin along +z: near root t=4, normal (0,0,-1)
+    hit, t, pos, nrm = ou.oracle_check_hit(_obj(SPHERE, (0, 0, 5), (1, 1, 1)), (0, 0, 0), (0, 0, 1))
+    assert hit and t == 4.0 and pos == (0, 0, 4) and nrm == (0, 0, -1)
+    # centre behind the ray: rejected by tca <= 0 (kernel.cu:55)
+    assert not ou.oracle_check_hit(_obj(SPHERE, (0, 0, -5), (1, 1, 1)), (0, 0, 0), (0, 0, 1))[0]
+    # origin inside, centre ahead: NEAR root is returned and is negative (kernel.cu:62)
+    hit, t, _, _ = ou.oracle_check_hit(_obj(SPHERE, (0, 0, 0.5), (2, 2, 2)), (0, 0, 0), (0, 0, 1))
+    assert hit and t == -1.5
+    # grazing: d2 >= r^2 misses
+    assert not ou.oracle_check_hit(_obj(SPHERE, (1, 0, 5), (1, 1, 1)), (0, 0, 0), (0, 0, 1))[0]
+
+    # plane y=0, two-sided (kernel.cu:71-94)
+    plane = _obj(PLANE, (0, 0, 0), (0, 1, 0))
+    hit, t, pos, nrm = ou.oracle_check_hit(plane, (0, 2, 0), (0, -1, 0))
+    assert hit and t == 2.0 and nrm == (0, 1, 0)
+    hit, t, _, nrm = ou.oracle_check_hit(plane, (0, -2, 0), (0, 1, 0))
+    assert hit and t == 2.0 and nrm == (0, 1, 0)            # normal is never flipped
+    assert not ou.oracle_check_hit(plane, (0, 2, 0), (0, 1, 0))[0]     # t < 0
+    assert not ou.oracle_check_hit(plane, (0, 2, 0), (1, 0, 0))[0]     # parallel: denom^2 <= 1e-5
+    assert not ou.oracle_check_hit(plane, (0, 2, 0), (1, 0.003, 0))[0] # still under the 1e-5 threshold
+
+    # triangle: CCW seen from the ray origin hits, CW is culled (det < 0.001, kernel.cu:104)
+    ccw = _obj(TRIANGLE, (0, 0, 5), (0, 1, 5), (1, 0, 5))
+    cw = _obj(TRIANGLE, (0, 0, 5), (1, 0, 5), (0, 1, 5))
+    hit, t, pos, nrm = ou.oracle_check_hit(ccw, (0.25, 0.25, 0), (0, 0, 1))
+    assert hit and t == 5.0 and nrm == (0, 0, -1)
+    assert not ou.oracle_check_hit(cw, (0.25, 0.25, 0), (0, 0, 1))[0]
+    assert not ou.oracle_check_hit(ccw, (0.75, 0.75, 0), (0, 0, 1))[0]   # u+v > 1
+    assert not ou.oracle_check_hit(ccw, (0.25, 0.25, 10), (0, 0, 1))[0]  # t < 0
+    # edges are inclusive: u = 0 and u + v = 1 hit
+    assert ou.oracle_check_hit(ccw, (0.0, 0.5, 0), (0, 0, 1))[0]
+    assert ou.oracle_check_hit(ccw, (0.5, 0.5, 0), (0, 0, 1))[0]
+
+
+def test_closest_hit_tie_goes_to_lowest_index(sky):
+    """Two coplanar triangles at the same t: strict '<' keeps the first (reference kernel.cu:145)."""
+    s = rt.Scene()
+    objs = s.objects.copy()
+    f = s.configure(view=5, hours=14, imgw=8, imgh=8, alias=False)
+    objs["type"] = TRIANGLE
+    objs["pos"], objs["size"], objs["third"] = (0, 0, 1e6), (0, 1, 1e6), (1, 0, 1e6)   # park everything far away, culled
+    objs["light"] = 0
+    cam = f.cam
+    # a big triangle facing the camera, duplicated at indices 7 and 3
+    c = np.array([cam.pos.x, cam.pos.y, cam.pos.z]) + 50 * np.array([(cam.LD.x + cam.RU.x) / 2, (cam.LD.y + cam.RU.y) / 2,
+                                                                   (cam.LD.z + cam.RU.z) / 2])
+    fwd = np.array([(cam.LD.x + cam.RU.x), (cam.LD.y + cam.RU.y), (cam.LD.z + cam.RU.z)])
+    fwd /= np.linalg.norm(fwd)
+    up = np.array([0, 1, 0.0])
+    right = np.cross(fwd, up)
+    right /= np.linalg.norm(right)
+    up = np.cross(right, fwd)
+    v0, v1, v2 = c - 500 * right - 500 * up, c + 500 * up, c + 500 * right - 500 * up
+    for idx in (7, 3):
+        objs["pos"][idx], objs["size"][idx], objs["third"][idx] = v0, v1, v2
+    r = ou.oracle_render(objs, s.lights, f, sky)
+    if (r["ids"] == -1).all():   # wound away from the camera: flip
+        for idx in (7, 3):
+            objs["size"][idx], objs["third"][idx] = v2, v1
+        r = ou.oracle_render(objs, s.lights, f, sky)
+    assert (r["ids"] == 3).all()
