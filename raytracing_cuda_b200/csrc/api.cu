@@ -127,14 +127,14 @@ encode_tiled_fn get_encode_tiled() {
     return fn;
 }
 
-/* 2-D uint32 image [h][w] -> 68x34 boxes (FXAA tile + halo) */
+/* 2-D uint32 image [h][w] -> 72x34 boxes (64x32 FXAA tile + halo; see FX_HALO_X in fxaa.cu) */
 bool make_fxaa_tmap(rt_context* ctx, const unsigned int* img, int w, int h) {
     if (ctx->tmap_ptr == img && ctx->tmap_w == w && ctx->tmap_h == h) return true;
     encode_tiled_fn enc = get_encode_tiled();
     if (!enc) return false;
     cuuint64_t dims[2] = {(cuuint64_t)w, (cuuint64_t)h};
     cuuint64_t strides[1] = {(cuuint64_t)w * 4};
-    cuuint32_t box[2] = {68, 34};
+    cuuint32_t box[2] = {72, 34};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(&ctx->tmap, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, (void*)img, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,

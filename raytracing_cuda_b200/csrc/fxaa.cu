@@ -9,7 +9,7 @@
  *
  * HBM-bound: 4 B read + 4 B written per pixel.  Two implementations:
  *   rt_fxaa_tma_kernel  : persistent CTAs, 64x32-pixel tiles (+1 halo) staged into shared
- *                         memory by TMA (cp.async.bulk.tensor.2d, 68x34 box, zero OOB fill),
+ *                         memory by TMA (cp.async.bulk.tensor.2d, 72x34 box, zero OOB fill),
  *                         double-buffered on two mbarriers; luminance computed once per
  *                         staged texel; coalesced 128-byte row stores.
  *   rt_fxaa_smem_kernel : plain shared-memory tile, any width, any shard tile size.
@@ -118,9 +118,14 @@ rt_fxaa_smem_kernel(const unsigned int* __restrict__ in, unsigned int* __restric
 
 #define FX_TW 64
 #define FX_TH 32
-#define FX_BOXW 68            /* 64 + 2 halo, rounded up to a 16-byte multiple */
+/* TMA needs the box's inner start coordinate at a 16-byte boundary (measured on this B200: a start at
+ * x0-1 raises "illegal instruction", x0-4 works; negative / past-the-end coordinates are zero-filled), so
+ * the halo column is fetched as a 4-pixel group on each side: 4 + 64 + 4 = 72 pixels per row. */
+#define FX_HALO_X 4
+#define FX_BOXW (FX_TW + 2 * FX_HALO_X)
 #define FX_BOXH 34
 #define FX_STAGE_BYTES (FX_BOXW * FX_BOXH * 4)
+#define FX_STAGE_WORDS 2464   /* 9792 B rounded up to a multiple of 128 B: every TMA destination is 128-byte aligned */
 #define FX_THREADS 256
 
 __device__ __forceinline__ uint32_t fx_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -176,7 +181,7 @@ __device__ __forceinline__ bool fx_tile_origin(int k, int tiles_x, int tiles_y, 
 __global__ void __launch_bounds__(FX_THREADS)
 rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned int* __restrict__ in,
                    unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride) {
-    __shared__ __align__(128) unsigned int s_px[2][FX_BOXH][FX_BOXW];
+    __shared__ __align__(128) unsigned int s_px[2][FX_STAGE_WORDS];
     __shared__ float s_lum[FX_BOXH][FX_BOXW];
     __shared__ __align__(8) uint64_t s_bar[2];
 
@@ -194,7 +199,7 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
     bool have = fx_tile_origin(k, tiles_x, tiles_y, n_shards, shard_id, stride, tx, ty);
     if (tid == 0 && have && tx < tiles_x) {
         fx_mbar_expect_tx(&s_bar[0], FX_STAGE_BYTES);
-        fx_tma_load_2d(&s_px[0][0][0], &in_map, tx * FX_TW - 1, ty * FX_TH - 1, &s_bar[0]);
+        fx_tma_load_2d(&s_px[0][0], &in_map, tx * FX_TW - FX_HALO_X, ty * FX_TH - 1, &s_bar[0]);
     }
     uint32_t phases = 0;   /* bit s = parity to wait for on stage s */
     int stage = 0;
@@ -205,13 +210,13 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         if (tid == 0 && have_next && ntx < tiles_x) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             fx_mbar_expect_tx(&s_bar[stage ^ 1], FX_STAGE_BYTES);
-            fx_tma_load_2d(&s_px[stage ^ 1][0][0], &in_map, ntx * FX_TW - 1, nty * FX_TH - 1, &s_bar[stage ^ 1]);
+            fx_tma_load_2d(&s_px[stage ^ 1][0], &in_map, ntx * FX_TW - FX_HALO_X, nty * FX_TH - 1, &s_bar[stage ^ 1]);
         }
         if (tx < tiles_x) {
             fx_mbar_wait(&s_bar[stage], (phases >> stage) & 1u);
             phases ^= 1u << stage;
             for (int i = tid; i < FX_BOXH * FX_BOXW; i += FX_THREADS)
-                (&s_lum[0][0])[i] = fx_lum((&s_px[stage][0][0])[i]);
+                (&s_lum[0][0])[i] = fx_lum(s_px[stage][i]);
             __syncthreads();
             const int cx = tid & 63, ry = tid >> 6;
             const int x = tx * FX_TW + cx;
@@ -220,8 +225,8 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
                 const int row = pass * 4 + ry;
                 const int y = ty * FX_TH + row;
                 if (x < w && y < h) {
-                    const int lx = cx + 1, ly = row + 1;
-                    const unsigned int centre = s_px[stage][ly][lx];
+                    const int lx = cx + FX_HALO_X, ly = row + 1;
+                    const unsigned int centre = s_px[stage][ly * FX_BOXW + lx];
                     unsigned int result = centre;
                     if (x > 0 && y > 0 && x + 1 < w && y + 1 < h) {
                         float b;
@@ -229,7 +234,7 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
                         if (fx_decide(s_lum[ly][lx], s_lum[ly][lx + 1], s_lum[ly][lx - 1], s_lum[ly - 1][lx],
                                       s_lum[ly + 1][lx], s_lum[ly - 1][lx + 1], s_lum[ly - 1][lx - 1],
                                       s_lum[ly + 1][lx + 1], s_lum[ly + 1][lx - 1], b, dx, dy))
-                            result = fx_blend(centre, s_px[stage][ly + dy][lx + dx], b);
+                            result = fx_blend(centre, s_px[stage][(ly + dy) * FX_BOXW + lx + dx], b);
                     }
                     out[(size_t)y * w + x] = result;
                 }
