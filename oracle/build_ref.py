@@ -164,6 +164,12 @@ extern "C" void ref_set_hit_buffer(int* dev, int w) {
     cudaMemcpyToSymbol(g_hitW, &w, sizeof(int));
 }
 extern "C" unsigned int* ref_get_base_image() { return baseImage; }
+// the reference's antialiasing kernel alone on a caller-supplied device image (alias = true)
+extern "C" void ref_fxaa(unsigned int* in, unsigned int* out, int imgw, int imgh) {
+    dim3 block(BLOCK_SIZE, BLOCK_SIZE, 1);
+    dim3 grid((imgw + block.x - 1) / block.x, (imgh + block.y - 1) / block.y, 1);
+    antialiasing<<< grid, block >>>(in, out, imgw, imgh, true);
+}
 // time `iters` back-to-back frames of the two reference kernels (inputs already uploaded by a
 // previous launchKernel call); returns ms per frame
 extern "C" float ref_time_kernels(unsigned int* result, int imgw, int imgh, Camera cam, bool alias, int iters) {
@@ -215,7 +221,10 @@ def build_ref_kernel_gpu(force=False):
         with open(tu, "w") as f:
             f.write("#include <cstring>\n" + text)
         run([os.path.join(CUDA, "bin", "nvcc"), "-gencode", "arch=compute_100,code=sm_100",
-             "--use_fast_math", "-O3", "-w", "-shared", "-Xcompiler", "-fPIC", "-lineinfo",
+             # 32x32 = 1024 threads per block (reference scene.h:13): the kernel must fit 64 registers per
+             # thread or the launch fails with "too many resources"; nvcc 12.9 picks 68 for sm_100 unasked
+             "--use_fast_math", "-O3", "-w", "-shared", "-Xcompiler", "-fPIC", "-lineinfo", "-maxrregcount", "64",
+             "-Xptxas", "-v",
              "-I", REF, "-I", os.path.join(REF, "common", "inc"), "-o", out, tu])
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
