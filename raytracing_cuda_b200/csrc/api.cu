@@ -26,7 +26,7 @@
 
 
 extern "C" {
-cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, cudaStream_t stream);
+cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, int builder, cudaStream_t stream);
 cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned int* tmp_keys, unsigned int* tmp_vals,
                                 unsigned int* hist, int n, int force_radix, cudaStream_t stream);
 int rt_radix_hist_entries(int n);
@@ -192,7 +192,7 @@ int rt_destroy(rt_context* ctx) {
     }
     RtBuildBuffers& b = ctx->bb;
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
-                    b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.flags,
+                    b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.flags, b.node_aux,
                     b.nodes, b.prims, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -204,6 +204,8 @@ const char* rt_last_error(rt_context* ctx) { return ctx ? ctx->err.c_str() : "nu
 
 int rt_set_option(rt_context* ctx, int key, int value) {
     if (!ctx || key < 0 || key >= 8) return RT_ERR_ARG;
+    if ((key == RT_OPT_BUILDER || key == RT_OPT_FORCE_RADIX) && ctx->opt[key] != value)
+        ctx->have_scene = false;   /* the next rt_set_scene rebuilds the hierarchy */
     ctx->opt[key] = value;
     return RT_OK;
 }
@@ -333,6 +335,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
         RT_CHECK(ctx, regrow(&b.node_parent, c));
         RT_CHECK(ctx, regrow(&b.leaf_parent, c));
         RT_CHECK(ctx, regrow(&b.flags, c));
+        RT_CHECK(ctx, regrow(&b.node_aux, c * 12));
         RT_CHECK(ctx, regrow(&b.nodes, c * 16));
         RT_CHECK(ctx, regrow(&b.prims, c * 3));
         ctx->cap_bvh = n_bvh;
@@ -356,7 +359,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
     const bool timing = ctx->opt[RT_OPT_TIMING] != 0;
     if (timing) cudaEventRecord(ctx->ev[4], ctx->stream);
     /* material / plane-only changes still run the (cheap) setup + refit: one code path */
-    RT_CHECK(ctx, rt_build_bvh(&b, mode == 0 ? 0 : 1, ctx->opt[RT_OPT_FORCE_RADIX], ctx->stream));
+    RT_CHECK(ctx, rt_build_bvh(&b, mode == 0 ? 0 : 1, ctx->opt[RT_OPT_FORCE_RADIX], ctx->opt[RT_OPT_BUILDER], ctx->stream));
     if (timing) { cudaEventRecord(ctx->ev[5], ctx->stream); ctx->build_timed = true; }
     (void)bvh_geometry_changed;
 

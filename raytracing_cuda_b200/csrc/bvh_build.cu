@@ -365,13 +365,21 @@ __global__ void rt_karras_kernel(const unsigned int* __restrict__ keys, int n, i
     children[i] = make_int2(c0, c1);
 }
 
-__device__ __forceinline__ void rt_store_child_box(float* __restrict__ node, int which, const float3& lo,
-                                                   const float3& hi) {
-    /* node = 16 floats: n0 (c0 x/y), n1 (c1 x/y), n2 (c0 z, c1 z), n3 (children) */
-    float* xy = node + 4 * which;
-    __stcg(xy + 0, lo.x); __stcg(xy + 1, hi.x); __stcg(xy + 2, lo.y); __stcg(xy + 3, hi.y);
-    __stcg(node + 8 + 2 * which, lo.z);
-    __stcg(node + 9 + 2 * which, hi.z);
+/* A child's box goes to two places: exact (lo,hi) into the build-side `aux` array, from which the sibling
+ * forms the union, and centre / half-extent into the traversal node record (rt_device.h), rounded outward
+ * so that [c-e, c+e] contains [lo,hi]. */
+__device__ __forceinline__ void rt_store_child_box(float* __restrict__ node, float* __restrict__ aux, int which,
+                                                   const float3& lo, const float3& hi) {
+    float* a = aux + 6 * which;
+    __stcg(a + 0, lo.x); __stcg(a + 1, lo.y); __stcg(a + 2, lo.z);
+    __stcg(a + 3, hi.x); __stcg(a + 4, hi.y); __stcg(a + 5, hi.z);
+    const float grow = 1.0f + 4.76837158203125e-07f;   /* 1 + 2^-21 */
+    const float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
+    const float ex = fmaxf(hi.x - cx, cx - lo.x) * grow, ey = fmaxf(hi.y - cy, cy - lo.y) * grow,
+                ez = fmaxf(hi.z - cz, cz - lo.z) * grow;
+    float* r = node + 6 * which;
+    __stcg(r + 0, cx); __stcg(r + 1, cy); __stcg(r + 2, cz);
+    __stcg(r + 3, ex); __stcg(r + 4, ey); __stcg(r + 5, ez);
 }
 
 __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
@@ -380,7 +388,7 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
                                 const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
                                 const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
                                 unsigned int* __restrict__ flags, float* __restrict__ nodes,
-                                float4* __restrict__ prims) {
+                                float* __restrict__ node_aux, float4* __restrict__ prims) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     const int k = (int)sorted_vals[j];
@@ -409,16 +417,16 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
         const int2 ch = children[node];
         const int which = (ch.x == child) ? 0 : 1;
         float* rec = nodes + 16 * (size_t)node;
-        rt_store_child_box(rec, which, lo, hi);
+        float* aux = node_aux + 12 * (size_t)node;
+        rt_store_child_box(rec, aux, which, lo, hi);
         if (which == 0) __stcg(rec + 12, __int_as_float(ch.x));
         else            __stcg(rec + 13, __int_as_float(ch.y));
         __threadfence();
         if (atomicAdd(&flags[node], 1u) == 0u) return;   /* first arrival: the sibling will carry on */
         /* second arrival: the sibling's box is visible (written before its fence + atomic) */
-        const int other = which ^ 1;
-        const float* xy = rec + 4 * other;
-        const float olx = __ldcg(xy + 0), ohx = __ldcg(xy + 1), oly = __ldcg(xy + 2), ohy = __ldcg(xy + 3);
-        const float olz = __ldcg(rec + 8 + 2 * other), ohz = __ldcg(rec + 9 + 2 * other);
+        const float* oa = aux + 6 * (which ^ 1);
+        const float olx = __ldcg(oa + 0), oly = __ldcg(oa + 1), olz = __ldcg(oa + 2);
+        const float ohx = __ldcg(oa + 3), ohy = __ldcg(oa + 4), ohz = __ldcg(oa + 5);
         lo = make_float3(fminf(lo.x, olx), fminf(lo.y, oly), fminf(lo.z, olz));
         hi = make_float3(fmaxf(hi.x, ohx), fmaxf(hi.y, ohy), fmaxf(hi.z, ohz));
         child = node;
@@ -427,8 +435,129 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
 }
 
 
-/* mode 0: full build; mode 1: refit only (topology from the previous build) */
-extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, cudaStream_t stream) {
+/* ------------------------------------------------------------------ PLOC hierarchy (small scenes)
+ *
+ * Parallel locally-ordered clustering (Meister & Bittner 2018) over the Morton-sorted primitives:
+ * every cluster looks RADIUS positions left and right for the neighbour whose union with it has the
+ * smallest surface area; mutual nearest neighbours merge; survivors are compacted; repeat until one
+ * cluster is left.  Unlike the Karras split (which only looks at the Morton keys) the merge order sees
+ * the real boxes, which matters for the built-in scene: 440-unit mountain triangles next to 0.1-unit
+ * spheres.  One CTA, everything in shared memory, deterministic node numbering (ids are handed out by a
+ * prefix sum, descending, so the last merge -- the root -- is node 0).  Emits the same topology arrays
+ * as rt_karras_kernel; rt_refit_kernel then fills the boxes. */
+#define PLOC_MAX 1024
+#define PLOC_RADIUS 16
+
+__device__ __forceinline__ float ploc_area(const float* a, const float* b) {
+    const float dx = fmaxf(a[3], b[3]) - fminf(a[0], b[0]);
+    const float dy = fmaxf(a[4], b[4]) - fminf(a[1], b[1]);
+    const float dz = fmaxf(a[5], b[5]) - fminf(a[2], b[2]);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void __launch_bounds__(PLOC_MAX)
+rt_ploc_small_kernel(const unsigned int* __restrict__ sorted_vals, int n, const float4* __restrict__ prim_lo,
+                     const float4* __restrict__ prim_hi, int2* __restrict__ children, int* __restrict__ node_parent,
+                     int* __restrict__ leaf_parent) {
+    __shared__ float s_box[PLOC_MAX][6];
+    __shared__ int s_cid[PLOC_MAX];
+    __shared__ int s_nn[PLOC_MAX];
+    __shared__ unsigned int s_warp[32];
+    __shared__ unsigned int s_total;
+    const int i = threadIdx.x, lane = i & 31, warp = i >> 5;
+    if (i < n) {
+        const int k = (int)sorted_vals[i];
+        const float4 lo = prim_lo[k], hi = prim_hi[k];
+        s_box[i][0] = lo.x; s_box[i][1] = lo.y; s_box[i][2] = lo.z;
+        s_box[i][3] = hi.x; s_box[i][4] = hi.y; s_box[i][5] = hi.z;
+        s_cid[i] = ~i;
+    }
+    if (i == 0) node_parent[0] = -1;
+    int count = n, next_node = n - 2;
+    __syncthreads();
+    while (count > 1) {
+        /* 1. nearest neighbour within the window */
+        if (i < count) {
+            float best = __int_as_float(0x7f800000);
+            int bj = -1;
+            const int j0 = max(0, i - PLOC_RADIUS), j1 = min(count - 1, i + PLOC_RADIUS);
+            for (int j = j0; j <= j1; j++) {
+                if (j == i) continue;
+                const float a = ploc_area(s_box[i], s_box[j]);
+                if (a < best) { best = a; bj = j; }
+            }
+            s_nn[i] = bj;
+        }
+        __syncthreads();
+        /* 2. mutual pairs merge into the lower position; the upper one dies */
+        bool alive = false, leader = false;
+        int j = -1;
+        if (i < count) {
+            j = s_nn[i];
+            const bool mutual = s_nn[j] == i;
+            leader = mutual && i < j;
+            alive = !mutual || leader;
+        }
+        /* 3. one block scan carries both counts: survivors (low 16 bits) and merges (high 16 bits) */
+        const unsigned int v = (alive ? 1u : 0u) | (leader ? 0x10000u : 0u);
+        unsigned int s = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, s, o);
+            if (lane >= o) s += t;
+        }
+        if (lane == 31) s_warp[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int ws = s_warp[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, ws, o);
+                if (lane >= o) ws += t;
+            }
+            s_warp[lane] = ws;
+            if (lane == 31) s_total = ws;
+        }
+        __syncthreads();
+        const unsigned int excl = (warp ? s_warp[warp - 1] : 0u) + s - v;
+        const unsigned int total = s_total;
+        /* 4. read my (possibly merged) cluster into registers, then write it to its compacted slot */
+        float box[6];
+        int cid = 0;
+        if (alive) {
+#pragma unroll
+            for (int a = 0; a < 6; a++) box[a] = s_box[i][a];
+            cid = s_cid[i];
+            if (leader) {
+                const int id = next_node - (int)(excl >> 16);
+                const int cj = s_cid[j];
+                children[id] = make_int2(cid, cj);
+                if (cid < 0) leaf_parent[~cid] = id; else node_parent[cid] = id;
+                if (cj < 0) leaf_parent[~cj] = id; else node_parent[cj] = id;
+#pragma unroll
+                for (int a = 0; a < 3; a++) {
+                    box[a] = fminf(box[a], s_box[j][a]);
+                    box[a + 3] = fmaxf(box[a + 3], s_box[j][a + 3]);
+                }
+                cid = id;
+            }
+        }
+        __syncthreads();
+        if (alive) {
+            const int dst = (int)(excl & 0xFFFFu);
+#pragma unroll
+            for (int a = 0; a < 6; a++) s_box[dst][a] = box[a];
+            s_cid[dst] = cid;
+        }
+        count = (int)(total & 0xFFFFu);
+        next_node -= (int)(total >> 16);
+        __syncthreads();
+    }
+}
+
+/* mode 0: full build; mode 1: refit only (topology from the previous build).
+ * builder 0: PLOC when n <= PLOC_MAX, else Karras; 1: Karras; 2: PLOC (falls back to Karras above PLOC_MAX) */
+extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, int builder, cudaStream_t stream) {
     const int T = RT_BUILD_THREADS;
     rt_bounds_init_kernel<<<1, 32, 0, stream>>>(b->bounds);
     if (b->n_objects > 0)
@@ -441,12 +570,23 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         rt_morton_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->prim_lo, b->prim_hi, n, b->bounds, b->keys, b->vals);
         cudaError_t e = rt_radix_sort_pairs(b->keys, b->vals, b->tmp_keys, b->tmp_vals, b->hist, n, force_radix, stream);
         if (e != cudaSuccess) return e;
-        if (n >= 2)
-            rt_karras_kernel<<<(n - 1 + T - 1) / T, T, 0, stream>>>(b->keys, n, b->children, b->node_parent, b->leaf_parent);
+        if (n >= 2) {
+            if (builder != 1 && n <= PLOC_MAX)
+                rt_ploc_small_kernel<<<1, PLOC_MAX, 0, stream>>>(b->vals, n, b->prim_lo, b->prim_hi, b->children,
+                                                                 b->node_parent, b->leaf_parent);
+            else
+                rt_karras_kernel<<<(n - 1 + T - 1) / T, T, 0, stream>>>(b->keys, n, b->children, b->node_parent,
+                                                                        b->leaf_parent);
+        }
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
     }
-    if (n >= 2) cudaMemsetAsync(b->flags, 0, sizeof(unsigned int) * (size_t)(n - 1), stream);
+    if (n >= 2) {
+        cudaError_t e = cudaMemsetAsync(b->flags, 0, sizeof(unsigned int) * (size_t)(n - 1), stream);
+        if (e != cudaSuccess) return e;
+    }
     rt_refit_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
                                                       b->children, b->node_parent, b->leaf_parent, b->flags, b->nodes,
-                                                      b->prims);
+                                                      b->node_aux, b->prims);
     return cudaGetLastError();
 }

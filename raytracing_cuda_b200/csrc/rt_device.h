@@ -4,12 +4,13 @@
  *
  * HBM layout (all 16-byte aligned, float4 granularity):
  *
- *   nodes   [n_nodes][4] float4   LBVH internal nodes, children's boxes embedded
- *        n0 = (c0.lo.x, c0.hi.x, c0.lo.y, c0.hi.y)
- *        n1 = (c1.lo.x, c1.hi.x, c1.lo.y, c1.hi.y)
- *        n2 = (c0.lo.z, c0.hi.z, c1.lo.z, c1.hi.z)
- *        n3 = (child0, child1, -, -) as int bits; child >= 0: internal node,
- *             child < 0: leaf, slot = ~child into `prims`
+ *   nodes   [n_nodes][4] float4   LBVH internal nodes, BOTH children's boxes embedded as centre c and
+ *                                  half-extent e (the slab test is then 9 FMAs per box and no per-axis
+ *                                  min/max: t_near/far = (c-o)*inv -/+ e*|inv|)
+ *        words 0..5   child0: c.x c.y c.z e.x e.y e.z
+ *        words 6..11  child1: c.x c.y c.z e.x e.y e.z
+ *        words 12,13  child0, child1 as int bits; child >= 0: internal node,
+ *                     child < 0: leaf, slot = ~child into `prims`;  words 14,15 unused
  *   prims   [n_bvh_prims][3] float4   leaf records in Morton order
  *        triangle: q0 = (v0.xyz, tag)  q1 = (e1.xyz, 0)  q2 = (e2.xyz, 0)     e1 = v1-v0, e2 = v2-v0
  *        sphere  : q0 = (c.xyz,  tag)  q1 = (r, r*r, 0, 0)
@@ -87,7 +88,7 @@ struct RtBuildBuffers {
     unsigned int *keys, *vals, *tmp_keys, *tmp_vals, *hist;
     int2* children; int *node_parent, *leaf_parent;
     unsigned int* flags;
-    float* nodes; float4* prims;
+    float* nodes; float* node_aux; float4* prims;
     int n_bvh;
 };
 

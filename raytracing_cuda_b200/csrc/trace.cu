@@ -115,15 +115,16 @@ rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restric
     image[y * f.imgw + x] = rt_pack(c.x, c.y, c.z);
 
     if (COUNT) {
-        atomicAdd(&counters->v[RT_CNT_RAYS_PRIMARY], 1ull);
-        atomicAdd(&counters->v[RT_CNT_RAYS_SHADOW], (unsigned long long)n_shadow);
-        atomicAdd(&counters->v[RT_CNT_RAYS_MIRROR], (unsigned long long)n_mirror);
-        atomicAdd(&counters->v[RT_CNT_NODE_TESTS], (unsigned long long)cnt.node_tests);
-        atomicAdd(&counters->v[RT_CNT_TRI_TESTS], (unsigned long long)cnt.tri_tests);
-        atomicAdd(&counters->v[RT_CNT_SPHERE_TESTS], (unsigned long long)cnt.sphere_tests);
-        atomicAdd(&counters->v[RT_CNT_PLANE_TESTS], (unsigned long long)cnt.plane_tests);
-        atomicAdd(&counters->v[RT_CNT_SKY_LOOKUPS], (unsigned long long)n_sky);
-        atomicAdd(&counters->v[RT_CNT_SHADOW_SKIPPED], (unsigned long long)n_shadow_skipped);
+        /* one atomic per warp and counter, not per thread */
+        const unsigned int mask = __activemask();
+        const bool leader = (threadIdx.x & 31) == (unsigned int)(__ffs(mask) - 1);
+        const unsigned int vals[9] = {1u, n_shadow, n_mirror, cnt.node_tests, cnt.tri_tests, cnt.sphere_tests,
+                                      cnt.plane_tests, n_sky, n_shadow_skipped};
+#pragma unroll
+        for (int k = 0; k < 9; k++) {
+            const unsigned int s = __reduce_add_sync(mask, vals[k]);
+            if (leader) atomicAdd(&counters->v[k], (unsigned long long)s);
+        }
     }
 }
 

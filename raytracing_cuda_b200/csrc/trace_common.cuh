@@ -79,8 +79,8 @@ __device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o,
             const float4 n3 = __ldg(nodes + 4 * node + 3);
             const float lim = ANY ? tmax : fmaxf(best.t, 0.0f);
             float t0, t1;
-            const bool h0 = rt_slab(rb, n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, lim, t0);
-            const bool h1 = rt_slab(rb, n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, lim, t1);
+            const bool h0 = rt_slab(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0);
+            const bool h1 = rt_slab(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1);
             if (COUNT) cnt.node_tests += 2;
             int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
             if (h0 && h1) {

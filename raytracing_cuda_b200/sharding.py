@@ -1,0 +1,103 @@
+"""Multi-GPU partitioning of the hot path.  Pure index math + torch.distributed plumbing.
+
+Two ways to use N GPUs, one process per GPU:
+
+* frame-parallel (camera-path batches, BASELINE config 5): frame i -> rank i % N, no communication.
+* screen-tile shards of ONE frame (configs 3/4): tile (i, j) of tile_w x tile_h pixels belongs to rank
+  (i + j*stride) % N.  A rank traces its tiles plus a 1-pixel apron (rt_shard_needs in
+  csrc/trace_common.cuh), so FXAA needs no halo exchange; the only collective is the optional gather of
+  finished tiles to rank 0 (`gather_frame`): each rank packs the tiles it owns into a dense buffer
+  (rt_pack_tiles), one `dist.gather` moves them over NVLink (NCCL) and rank 0 scatters them into the frame
+  (rt_unpack_tiles).  Buffers are equally sized on every rank: slots = ceil(tiles_x / N) * tiles_y.
+
+The numpy pack/unpack below restate the CUDA kernels for the CPU (gloo) tests of this logic.
+"""
+import numpy as np
+
+from .renderer import default_stride, make_shard  # noqa: F401
+
+
+def tile_grid(imgw, imgh, tile_w, tile_h):
+    return (imgw + tile_w - 1) // tile_w, (imgh + tile_h - 1) // tile_h
+
+
+def owner_map(imgw, imgh, tile_w, tile_h, n_shards, stride):
+    """[imgh][imgw] int array: which shard owns each pixel (same formula as rt_tile_owner in csrc/rt_device.h)."""
+    yy, xx = np.mgrid[0:imgh, 0:imgw]
+    return ((xx // tile_w) + (yy // tile_h) * stride) % n_shards
+
+
+def needed_map(imgw, imgh, tile_w, tile_h, n_shards, stride, shard_id):
+    """Pixels a shard has to TRACE: its own tiles dilated by one pixel (the FXAA apron)."""
+    own = owner_map(imgw, imgh, tile_w, tile_h, n_shards, stride) == shard_id
+    need = own.copy()
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            shifted = np.zeros_like(own)
+            ys = slice(max(dy, 0), imgh + min(dy, 0))
+            yd = slice(max(-dy, 0), imgh + min(-dy, 0))
+            xs = slice(max(dx, 0), imgw + min(dx, 0))
+            xd = slice(max(-dx, 0), imgw + min(-dx, 0))
+            shifted[yd, xd] = own[ys, xs]
+            need |= shifted
+    return need
+
+
+def tile_slots(imgw, imgh, shard):
+    """Slot s of a shard -> (tx, ty) or None for an empty slot.  Mirrors rt_pack_tiles_kernel."""
+    tiles_x, tiles_y = tile_grid(imgw, imgh, shard.tile_w, shard.tile_h)
+    per_row = (tiles_x + shard.n_shards - 1) // shard.n_shards
+    out = []
+    for s in range(per_row * tiles_y):
+        ty, m = divmod(s, per_row)
+        i0 = (shard.shard_id - ty * shard.stride) % shard.n_shards
+        tx = i0 + m * shard.n_shards
+        out.append((tx, ty) if tx < tiles_x else None)
+    return out
+
+
+def pack_tiles_host(frame, shard):
+    imgh, imgw = frame.shape
+    slots = tile_slots(imgw, imgh, shard)
+    packed = np.zeros((len(slots), shard.tile_h, shard.tile_w), dtype=frame.dtype)
+    for s, t in enumerate(slots):
+        if t is None:
+            continue
+        x0, y0 = t[0] * shard.tile_w, t[1] * shard.tile_h
+        blk = frame[y0:y0 + shard.tile_h, x0:x0 + shard.tile_w]
+        packed[s, :blk.shape[0], :blk.shape[1]] = blk
+    return packed
+
+
+def unpack_tiles_host(packed, frame, shard):
+    imgh, imgw = frame.shape
+    for s, t in enumerate(tile_slots(imgw, imgh, shard)):
+        if t is None:
+            continue
+        x0, y0 = t[0] * shard.tile_w, t[1] * shard.tile_h
+        h = min(shard.tile_h, imgh - y0)
+        w = min(shard.tile_w, imgw - x0)
+        frame[y0:y0 + h, x0:x0 + w] = packed[s, :h, :w]
+    return frame
+
+
+def frames_of_rank(n_frames, rank, world):
+    """Frame-parallel batches: frame i -> rank i % world."""
+    return list(range(rank, n_frames, world))
+
+
+def gather_frame(dist, rank, world, packed_local, make_like, unpack, dst=0):
+    """Gather every rank's packed tiles to `dst` and scatter them into the frame there.
+
+    packed_local : this rank's packed tiles (torch tensor; CUDA for NCCL, CPU for gloo)
+    make_like    : () -> empty tensor shaped like packed_local (receive buffers on dst)
+    unpack       : (packed_tensor, shard_id) -> None, writes the tiles of shard_id into the frame
+    """
+    if world == 1:
+        unpack(packed_local, 0)
+        return
+    bufs = [make_like() for _ in range(world)] if rank == dst else None
+    dist.gather(packed_local, gather_list=bufs, dst=dst)
+    if rank == dst:
+        for k in range(world):
+            unpack(bufs[k], k)

@@ -209,9 +209,12 @@ def test_against_rebuilt_reference_kernel():
     import torch
     ref = _ref_gpu()
     ref.ref_set_hit_buffer.argtypes = [C.c_void_p, C.c_int]
-    r = gu.renderer()
     s = rt.Scene()
-    sky = gu.sky_small()
+    # the reference sizes its scratch image by the TEXTURE dimensions (kernel.cu:441): the sky maps must
+    # have at least as many texels as the frame has pixels, or its own kernel writes out of bounds
+    sky = rt.synthetic_sky(2048, 1024)
+    r = rt.Renderer(0)
+    r.set_sky(sky)
     w, h = 1280, 720
     out = torch.zeros(w * h, dtype=torch.int32, device="cuda")
     hit = torch.full((w * h,), -2, dtype=torch.int32, device="cuda")
@@ -228,6 +231,7 @@ def test_against_rebuilt_reference_kernel():
             m = _gate(img, ref_img, ids, ref_ids, "ref kernel v%d %s" % (view, tod))
             m["id_mismatch"] = int((ids != ref_ids).sum())
             stats.append((view, tod, m))
+    r.close()
     os.makedirs(os.path.join(ou.ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ou.ROOT, "gpurun_out", "parity_vs_reference_kernel.txt"), "w") as fh:
         for view, tod, m in stats:
