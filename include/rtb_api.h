@@ -64,7 +64,7 @@ enum {
     RT_OPT_FXAA_IMPL = 2,   /* 0 = TMA-staged (default when width%4==0), 1 = plain shared-memory */
     RT_OPT_TIMING    = 3,   /* 1 = record CUDA events around trace and fxaa */
     RT_OPT_SKY_ALL4  = 4,   /* 1 = fetch all four sky maps like the reference (default 0: only non-zero weights; bit-identical) */
-    RT_OPT_TRACE_IMPL = 5,  /* 0 = default tracer, other values select experimental variants */
+    RT_OPT_TRACE_IMPL = 5,  /* 0 = auto: shared-memory tracer when the scene fits (<= ~165 primitives), else the HBM-resident LBVH tracer; 1 = always the HBM tracer; 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests) */
     RT_OPT_BUILDER = 6,     /* hierarchy over the Morton-sorted primitives: 0 = auto (PLOC up to 1024 primitives, Karras above), 1 = Karras, 2 = PLOC */
     RT_OPT_FORCE_RADIX = 7  /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
 };

@@ -10,7 +10,7 @@ import os
 from .structs import Camera, Float3, Frame, Light, Object, Shard
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libraytracing_b200.so")
+LIB_PATH = os.environ.get("RTB_LIB_PATH") or os.path.join(_HERE, "libraytracing_b200.so")   # override: kernel experiments
 
 RT_OK, RT_ERR_CUDA, RT_ERR_ARG, RT_ERR_STATE, RT_ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 (RT_OPT_TRAVERSAL, RT_OPT_COUNTERS, RT_OPT_FXAA_IMPL, RT_OPT_TIMING, RT_OPT_SKY_ALL4, RT_OPT_TRACE_IMPL) = range(6)

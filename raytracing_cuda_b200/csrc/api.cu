@@ -33,6 +33,12 @@ int rt_radix_hist_entries(int n);
 cudaError_t rt_cub_sort_pairs(unsigned int* keys, unsigned int* vals, int n, cudaStream_t stream);
 cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                             RtCountersDev* counters, int brute, int count, cudaStream_t stream);
+cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
+                                  RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
+                                  int count, int force_linear, int n_sm, cudaStream_t stream);
+size_t rt_trace_small_list_bytes(int imgw, int imgh);
+int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_planes);
+cudaError_t rt_trace_small_init(void);
 cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
                                 cudaStream_t stream);
 cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out, int w, int h,
@@ -75,6 +81,9 @@ struct rt_context {
     int* d_stage_ids = nullptr;
     size_t cap_stage = 0;
     RtCountersDev* d_counters = nullptr;
+    unsigned short* d_tile_lists = nullptr;  /* per-tile primary candidate lists (trace_small.cu) */
+    size_t cap_tile_lists = 0;
+    unsigned int* d_tile_counter = nullptr;  /* [0] next tile, [1] finished CTAs (persistent tracer; self re-arming) */
 
     /* TMA descriptor cache */
     CUtensorMap tmap;
@@ -177,6 +186,9 @@ int rt_create(int device, rt_context** out) {
     cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
     if (cudaMalloc((void**)&ctx->d_counters, sizeof(RtCountersDev)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
     cudaMemset(ctx->d_counters, 0, sizeof(RtCountersDev));
+    if (cudaMalloc((void**)&ctx->d_tile_counter, 4 * sizeof(unsigned int)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
+    cudaMemset(ctx->d_tile_counter, 0, 4 * sizeof(unsigned int));
+    if (rt_trace_small_init() != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
     for (int i = 0; i < 6; i++) cudaEventCreate(&ctx->ev[i]);
     *out = ctx;
     return RT_OK;
@@ -193,7 +205,7 @@ int rt_destroy(rt_context* ctx) {
     RtBuildBuffers& b = ctx->bb;
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
                     b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.flags, b.node_aux,
-                    b.nodes, b.prims, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters};
+                    b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     delete ctx;
@@ -321,6 +333,10 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
         ctx->cap_planes = (int)c;
     }
     if (!b.bounds) RT_CHECK(ctx, regrow(&b.bounds, (size_t)8));
+    if (!b.depth) {
+        RT_CHECK(ctx, regrow(&b.depth, (size_t)1));
+        RT_CHECK(ctx, cudaMemsetAsync(b.depth, 0, sizeof(int), ctx->stream));
+    }
     if (n_bvh > ctx->cap_bvh) {
         const size_t c = (size_t)n_bvh;
         RT_CHECK(ctx, regrow(&b.bvh_src, c));
@@ -368,6 +384,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
     ctx->scene.planes = b.planes;
     ctx->scene.mats = b.mats;
     ctx->scene.recs = b.recs;
+    ctx->scene.depth = b.depth;
     ctx->scene.n_bvh_prims = n_bvh;
     ctx->scene.n_planes = n_planes;
     ctx->scene.n_objects = n_objects;
@@ -424,8 +441,25 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
     const int count = ctx->opt[RT_OPT_COUNTERS] != 0;
     if (count) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(RtCountersDev), ctx->stream));
     if (timing) cudaEventRecord(ctx->ev[0], ctx->stream);
-    RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
-                                  ctx->opt[RT_OPT_TRAVERSAL] == 1, count, ctx->stream));
+    /* RT_OPT_TRACE_IMPL: 0 = auto (shared-memory tracer when the scene fits), 1 = HBM-resident LBVH tracer,
+     * 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests) */
+    const bool small = ctx->opt[RT_OPT_TRAVERSAL] != 1 && ctx->opt[RT_OPT_TRACE_IMPL] != 1 &&
+                       rt_trace_small_supported(ctx->scene.n_bvh_prims, ctx->scene.n_objects, ctx->scene.n_planes);
+    if (small) {
+        const size_t need = rt_trace_small_list_bytes(frame->imgw, frame->imgh) / sizeof(unsigned short);
+        if (need > ctx->cap_tile_lists) {
+            RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));   /* a frame in flight may still read the old lists */
+            RT_CHECK(ctx, regrow(&ctx->d_tile_lists, need));
+            ctx->cap_tile_lists = need;
+        }
+        RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
+                                            ctx->d_tile_counter, ctx->d_tile_lists, count,
+                                            ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ctx->stream));
+    }
+    else {
+        RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
+                                      ctx->opt[RT_OPT_TRAVERSAL] == 1, count, ctx->stream));
+    }
     if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }
     int rc = RT_OK;
     if (frame->alias) rc = run_fxaa(ctx, ctx->d_base, out_dev, frame->imgw, frame->imgh, shard);

@@ -388,7 +388,7 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
                                 const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
                                 const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
                                 unsigned int* __restrict__ flags, float* __restrict__ nodes,
-                                float* __restrict__ node_aux, float4* __restrict__ prims) {
+                                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
     const int k = (int)sorted_vals[j];
@@ -396,7 +396,10 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
     prims[3 * j] = recs[3 * obj];
     prims[3 * j + 1] = recs[3 * obj + 1];
     prims[3 * j + 2] = recs[3 * obj + 2];
-    if (n < 2) return;
+    if (n < 2) {
+        *depth_out = 0;
+        return;
+    }
 
     const float4 plo = prim_lo[k], phi = prim_hi[k];
     const float extent = fmaxf(fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), ord2f(bounds[4]) - ord2f(bounds[1])),
@@ -413,6 +416,7 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
     }
     int child = ~j;
     int node = leaf_parent[j];
+    unsigned int height = 0;                 /* of the subtree being carried up (leaf = 0) */
     while (node >= 0) {
         const int2 ch = children[node];
         const int which = (ch.x == child) ? 0 : 1;
@@ -422,7 +426,10 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
         if (which == 0) __stcg(rec + 12, __int_as_float(ch.x));
         else            __stcg(rec + 13, __int_as_float(ch.y));
         __threadfence();
-        if (atomicAdd(&flags[node], 1u) == 0u) return;   /* first arrival: the sibling will carry on */
+        /* bit 0..7: arrivals, bits 8..: height of the first arrival's subtree */
+        const unsigned int old = atomicAdd(&flags[node], 1u + (height << 8));
+        if (old == 0u) return;                           /* first arrival: the sibling will carry on */
+        height = max(height, old >> 8) + 1u;
         /* second arrival: the sibling's box is visible (written before its fence + atomic) */
         const float* oa = aux + 6 * (which ^ 1);
         const float olx = __ldcg(oa + 0), oly = __ldcg(oa + 1), olz = __ldcg(oa + 2);
@@ -432,6 +439,7 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
         child = node;
         node = node_parent[node];
     }
+    *depth_out = (int)height;                /* only the thread that reached the root gets here */
 }
 
 
@@ -587,6 +595,6 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
     }
     rt_refit_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
                                                       b->children, b->node_parent, b->leaf_parent, b->flags, b->nodes,
-                                                      b->node_aux, b->prims);
+                                                      b->node_aux, b->prims, b->depth);
     return cudaGetLastError();
 }

@@ -38,6 +38,9 @@
 #define RT_MAX_LIGHTS 8
 #define RT_NODE_SENTINEL 0x7FFFFFFF   /* empty-stack marker / empty tree */
 #define RT_STACK_SIZE 64
+/* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 48*n must fit 16 bits */
+#define RT_SMALL_MAX_PRIMS 288
+#define RT_SMALL_DYN_SMEM_MAX (24 * 1024)
 
 struct RtSceneDev {
     const float4* nodes;
@@ -45,6 +48,7 @@ struct RtSceneDev {
     const float4* planes;
     const float4* mats;
     const float4* recs;
+    const int* depth;  /* device: height of the hierarchy (edges root -> deepest leaf), written by the refit */
     int root;          /* encoded child: >=0 node, <0 leaf, RT_NODE_SENTINEL = empty */
     int n_bvh_prims;
     int n_planes;
@@ -89,6 +93,7 @@ struct RtBuildBuffers {
     int2* children; int *node_parent, *leaf_parent;
     unsigned int* flags;
     float* nodes; float* node_aux; float4* prims;
+    int* depth;
     int n_bvh;
 };
 

@@ -1,0 +1,489 @@
+/*
+ * trace_small.cu -- tracer for scenes whose whole LBVH fits in shared memory (the
+ * reference's built-in scene: 133 objects, reference scene.h:11; here up to
+ * RT_SMALL_MAX_PRIMS).  Same per-pixel arithmetic as trace.cu (trace_pixel.cuh), so the
+ * two kernels agree bit for bit; only WHICH primitives get tested differs.
+ *
+ *   - rt_cull_tiles_kernel (binning pre-pass, one warp per 16x8-pixel tile): primary rays do
+ *     not traverse the hierarchy at all.  The warp culls the primitives against the tile's
+ *     frustum (4 planes through the eye, 32 primitives per step, back-facing triangles
+ *     dropped -- they fail `det < 0.001`, kernel.cu:104) into a short, index-ordered
+ *     candidate list in HBM (ballot compaction, 64 B per tile);
+ *   - rt_trace_small_kernel: persistent CTAs (4 per SM); the LBVH nodes, leaf records,
+ *     materials and planes are staged into shared memory once per CTA (the reference keeps
+ *     its 133 objects in __constant__, kernel.cu:14).  After that every WARP is autonomous:
+ *     it fetches work from an atomic counter -- whole tiles (four 8x4 patches) for the first
+ *     part of the frame, single patches for the rest so that the tail stays short -- two
+ *     fetches ahead, with the tile's candidate list loaded one unit ahead; no CTA barrier in
+ *     the loop.  Every pixel of a tile tests just the tile's list for its primary ray;
+ *   - shadow and mirror rays traverse the shared-memory LBVH with a per-thread stack of
+ *     16-bit entries in shared memory (no local memory), child links pre-scaled to byte
+ *     offsets, branch-free near/far selection.
+ *
+ * Conservative culling: the tile is grown by one pixel on every side and each plane test
+ * gets a world-space pad (2^-13 of the largest coordinate in play), both orders of
+ * magnitude above the rounding of the ray set-up and of the acceptance region of the leaf
+ * tests; spheres are grown by the rounding noise of d2 = L.L - tca^2 (kernel.cu:55-58).
+ * A primitive is only dropped when it cannot be hit by any ray of the tile, so the
+ * (t, index) minimum over the candidates equals the reference's loop over all objects.
+ */
+#include "trace_pixel.cuh"
+
+#define RT_SMALL_THREADS 256
+#define RT_SMALL_STACK 23            /* per-thread stack entries (16-bit) in shared memory, above the sentinel */
+#ifndef RT_SMALL_CTAS_PER_SM
+#define RT_SMALL_CTAS_PER_SM 4
+#endif
+#define RT_SMALL_STACK_STRIDE (2 * RT_SMALL_THREADS)   /* bytes between two levels of one thread's stack */
+
+/* Shared-memory addressing: the hot loops use 32-bit shared-window addresses and explicit ld/st.shared, so a
+ * node or leaf fetch is one add + LDS.128s with immediate offsets.  Node and leaf links are byte offsets from
+ * the start of the staged scene (`base`): node i -> 64 i, leaf slot j -> ~(64 n_nodes + 48 j). */
+struct RtSmallShared {
+    unsigned int base;       /* shared address of the staged nodes (leaf records follow them) */
+    unsigned int stack0;     /* shared address of this thread's stack column */
+    const float4* mats;
+    const float4* planes;
+    const unsigned short* list;   /* primary candidates of the current tile: [0] count, then leaf byte offsets */
+    int root, n_prims, n_planes, prims_off;
+    bool deep;               /* hierarchy deeper than RT_SMALL_STACK: secondary rays loop linearly instead */
+};
+
+__device__ __forceinline__ float4 rs_lds128(unsigned int a) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ void rs_push(unsigned int& sp, int v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(sp), "h"((short)v));
+    sp += RT_SMALL_STACK_STRIDE;
+}
+__device__ __forceinline__ int rs_pop(unsigned int& sp) {
+    short v;
+    sp -= RT_SMALL_STACK_STRIDE;
+    asm volatile("ld.shared.s16 %0, [%1];" : "=h"(v) : "r"(sp));
+    return (int)v;
+}
+
+/* leaf record at shared address `rec` */
+__device__ __forceinline__ bool rs_test_record(unsigned int rec, const vec3& o, const vec3& d, float& t,
+                                               unsigned int& tag, RtLocalCounters& cnt, bool count) {
+    const float4 q0 = rs_lds128(rec);
+    const float4 q1 = rs_lds128(rec + 16);
+    tag = __float_as_uint(q0.w);
+    if (tag & RT_TAG_SPHERE) {
+        if (count) cnt.sphere_tests++;
+        return rt_hit_sphere(o, d, f4xyz(q0), q1.y, t);
+    }
+    const float4 q2 = rs_lds128(rec + 32);
+    if (count) cnt.tri_tests++;
+    return rt_hit_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t);
+}
+
+#define RS_STACK_END (-32768)          /* sentinel at the bottom of every per-thread stack (never a valid link) */
+
+/* LBVH traversal in shared memory.  Returns true on an occluder (ANY).  The per-thread stack holds
+ * RT_SMALL_STACK entries above the sentinel; the caller only comes here when the hierarchy is no deeper
+ * than that (RtSceneDev.depth), so pushes are unchecked. */
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool rs_traverse(const RtSmallShared& s, const vec3& o, const vec3& d, RtHit& best,
+                                            float tmax, RtLocalCounters& cnt) {
+    if (s.n_prims == 0) return false;
+    int node = s.root;
+    const RtRayBox rb = rt_ray_box(o, d);
+    const unsigned int base = s.base;
+    unsigned int sp = s.stack0;
+    rs_push(sp, RS_STACK_END);
+    for (;;) {
+        if (node >= 0) {
+            const unsigned int a = base + (unsigned int)node;
+            const float4 n0 = rs_lds128(a), n1 = rs_lds128(a + 16), n2 = rs_lds128(a + 32), n3 = rs_lds128(a + 48);
+            const float lim = ANY ? tmax : fmaxf(best.t, 0.0f);
+            float t0, t1;
+            const bool h0 = rt_slab(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0);
+            const bool h1 = rt_slab(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1);
+            if (COUNT) cnt.node_tests += 2;
+            const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            if (h0 | h1) {
+                const bool second_first = h1 && (!h0 || t1 < t0);
+                const int near = second_first ? c1 : c0;
+                if (h0 && h1) rs_push(sp, c0 ^ c1 ^ near);
+                node = near;
+                continue;
+            }
+        } else {
+            const unsigned int rec = base + (unsigned int)(~node);
+            float t;
+            unsigned int tag;
+            if (rs_test_record(rec, o, d, t, tag, cnt, COUNT)) {
+                if (ANY) {
+                    if (!(tag & RT_TAG_EMISSIVE) && t < tmax) return true;
+                } else {
+                    rt_consider(best, t, tag, ~node);
+                }
+            }
+        }
+        node = rs_pop(sp);
+        if (node == RS_STACK_END) break;
+    }
+    return false;
+}
+
+template <bool COUNT>
+struct RtSmallScene {
+    const RtSmallShared& s;
+    __device__ __forceinline__ RtSmallScene(const RtSmallShared& sh) : s(sh) {}
+
+    __device__ __forceinline__ void planes_closest(const vec3& o, const vec3& d, RtHit& best, RtLocalCounters& cnt) {
+        for (int p = 0; p < s.n_planes; p++) {
+            const float4 q0 = s.planes[2 * p], q1 = s.planes[2 * p + 1];
+            float t;
+            if (COUNT) cnt.plane_tests++;
+            if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t)) rt_consider(best, t, __float_as_uint(q0.w), ~p);
+        }
+    }
+    __device__ __forceinline__ void linear_closest(const vec3& o, const vec3& d, RtHit& best, RtLocalCounters& cnt) {
+        for (int j = 0; j < s.n_prims; j++) {
+            const int off = s.prims_off + 48 * j;
+            float t;
+            unsigned int tag;
+            if (rs_test_record(s.base + off, o, d, t, tag, cnt, COUNT)) rt_consider(best, t, tag, off);
+        }
+    }
+    /* RtHit.slot: >= 0 leaf byte offset from `base`, < 0 ~plane index */
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, RtLocalCounters& cnt) {
+        RtHit best;
+        best.t = __int_as_float(0x7f800000);
+        best.tag = RT_MISS;
+        best.slot = 0;
+        planes_closest(o, d, best, cnt);
+        if (depth == 0) {
+            /* primary ray: the tile's candidate list instead of the hierarchy */
+            const int n = s.list[0];
+            if (n != 0xFFFF) {
+                for (int i = 1; i <= n; i++) {
+                    const int off = s.list[i];
+                    float t;
+                    unsigned int tag;
+                    if (rs_test_record(s.base + off, o, d, t, tag, cnt, COUNT)) rt_consider(best, t, tag, off);
+                }
+                return best;
+            }
+        }
+        if (s.deep) linear_closest(o, d, best, cnt);     /* hierarchy deeper than the shared-memory stacks */
+        else rs_traverse<false, COUNT>(s, o, d, best, 0.0f, cnt);
+        return best;
+    }
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
+        for (int p = 0; p < s.n_planes; p++) {
+            const float4 q0 = s.planes[2 * p], q1 = s.planes[2 * p + 1];
+            float t;
+            if (COUNT) cnt.plane_tests++;
+            if (__float_as_uint(q0.w) & RT_TAG_EMISSIVE) continue;
+            if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t) && t < tmax) return true;
+        }
+        RtHit dummy;
+        if (!s.deep) return rs_traverse<true, COUNT>(s, o, d, dummy, tmax, cnt);
+        {
+            for (int j = 0; j < s.n_prims; j++) {
+                float t;
+                unsigned int tag;
+                if (rs_test_record(s.base + s.prims_off + 48 * j, o, d, t, tag, cnt, COUNT) &&
+                    !(tag & RT_TAG_EMISSIVE) && t < tmax)
+                    return true;
+            }
+        }
+        return false;
+    }
+    __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) {
+        if (h.slot < 0) return f4xyz(s.planes[2 * (~h.slot) + 1]);
+        const unsigned int rec = s.base + (unsigned int)h.slot;
+        if (h.tag & RT_TAG_SPHERE) return rt_normalize(rt_sub(P, f4xyz(rs_lds128(rec))));
+        return rt_normalize(rt_cross(f4xyz(rs_lds128(rec + 16)), f4xyz(rs_lds128(rec + 32))));
+    }
+    __device__ __forceinline__ void material(unsigned int idx, float4& m0, float4& m1) {
+        m0 = s.mats[2 * idx];
+        m1 = s.mats[2 * idx + 1];
+    }
+};
+
+/* un-normalised primary-ray target at a (fractional) pixel position: the bilinear blend of
+ * reference kernel.cu:246-251 */
+__device__ __forceinline__ vec3 rs_primary_target(const RtFrameDev& f, float px, float py) {
+    const float partX = px / (float)(f.imgw - 1), partY = py / (float)(f.imgh - 1);
+    vec3 t;
+    {
+        const float vd = f.LD[0] + partX * (f.RD[0] - f.LD[0]), vu = f.LU[0] + partX * (f.RU[0] - f.LU[0]);
+        t.x = vu - partY * (vu - vd);
+    }
+    {
+        const float vd = f.LD[1] + partX * (f.RD[1] - f.LD[1]), vu = f.LU[1] + partX * (f.RU[1] - f.LU[1]);
+        t.y = vu - partY * (vu - vd);
+    }
+    {
+        const float vd = f.LD[2] + partX * (f.RD[2] - f.LD[2]), vu = f.LU[2] + partX * (f.RU[2] - f.LU[2]);
+        t.z = vu - partY * (vu - vd);
+    }
+    return t;
+}
+
+struct RsFrustum {
+    vec3 n[4];     /* unit inward normals of the 4 side planes through the eye */
+    bool ok;       /* false: degenerate / non-convex corner set -> keep every primitive */
+};
+
+__device__ __forceinline__ RsFrustum rs_tile_frustum(const RtFrameDev& f, int x0, int y0, int x1, int y1) {
+    const float xa = (float)x0 - 1.0f, xb = (float)x1 + 1.0f, ya = (float)y0 - 1.0f, yb = (float)y1 + 1.0f;
+    vec3 c[4];
+    c[0] = rs_primary_target(f, xa, ya);
+    c[1] = rs_primary_target(f, xb, ya);
+    c[2] = rs_primary_target(f, xb, yb);
+    c[3] = rs_primary_target(f, xa, yb);
+    const vec3 mid = vadd(vadd(c[0], c[1]), vadd(c[2], c[3]));
+    RsFrustum fr;
+    fr.ok = true;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const vec3 a = c[k], b = c[(k + 1) & 3];
+        vec3 n = vcross(a, b);
+        const float len = sqrtf(vdot(n, n));
+        const float s = (vdot(n, mid) < 0.0f ? -1.0f : 1.0f) / len;
+        n = vscale(n, s);
+        /* every ray of the tile is a convex combination of the four corners: it is inside plane k if the
+         * two corners that do not span it are */
+        const float e0 = vdot(n, c[(k + 2) & 3]), e1 = vdot(n, c[(k + 3) & 3]);
+        if (!(len > 0.0f) || !(e0 > 0.0f) || !(e1 > 0.0f)) fr.ok = false;
+        fr.n[k] = n;
+    }
+    return fr;
+}
+
+/* can any ray of the tile (origin `eye`, inside `fr`) hit leaf record `rec`? */
+__device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3& eye, const float4* __restrict__ rec,
+                                                float pad) {
+    const float4 q0 = __ldg(rec);
+    const float4 q1 = __ldg(rec + 1);
+    const unsigned int tag = __float_as_uint(q0.w);
+    const vec3 a = vsub(f4xyz(q0), eye);
+    if (tag & RT_TAG_SPHERE) {
+        /* d2 = L.L - tca^2 carries rounding noise of about 2^-21 |L|^2: grow the radius accordingly */
+        const float r = sqrtf(q1.y + 3.814697265625e-06f * vdot(a, a)) + pad;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (vdot(fr.n[k], a) < -r) return false;
+        return true;
+    }
+    const float4 q2 = __ldg(rec + 2);
+    const vec3 e1 = f4xyz(q1), e2 = f4xyz(q2);
+    /* det = -d.Ng for every ray: the eye on the back side means `det < 0.001` rejects them all */
+    const vec3 ng = vcross(e1, e2);
+    const float side = vdot(ng, a);
+    if (side > 1e-3f * sqrtf(vdot(ng, ng) * vdot(a, a)) + pad * sqrtf(vdot(ng, ng))) return false;
+    const vec3 b = vadd(a, e1), c = vadd(a, e2);
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        if (vdot(fr.n[k], a) < -pad && vdot(fr.n[k], b) < -pad && vdot(fr.n[k], c) < -pad) return false;
+    return true;
+}
+
+#define RT_SMALL_WARPS (RT_SMALL_THREADS / 32)
+#define RT_SMALL_TILE_W 16
+#define RT_SMALL_TILE_H 8
+#define RT_SMALL_PATCHES 4            /* 8x4 patches per tile */
+#define RT_SMALL_LIST 32              /* ushorts per tile list: [0] = count (0xFFFF: too many, traverse), [1..31] */
+
+/* ---------------------------------------------------------------- binning pre-pass */
+
+__global__ void __launch_bounds__(256)
+rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
+                     int n_tiles) {
+    const int lane = threadIdx.x & 31;
+    const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (tile >= n_tiles) return;
+    const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
+    const int prims_off = 64 * n_nodes;
+    /* world-space pad of the cull tests from the scene's extent and the eye position */
+    float pad;
+    {
+        float m = fmaxf(fmaxf(fabsf(f.pos[0]), fabsf(f.pos[1])), fabsf(f.pos[2]));
+        if (n_nodes > 0) {
+            const float4 a = __ldg(sc.nodes), b = __ldg(sc.nodes + 1), c = __ldg(sc.nodes + 2);
+            const float r[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int k = 0; k < 2; k++)
+#pragma unroll
+                for (int q = 0; q < 3; q++) m = fmaxf(m, fabsf(r[6 * k + q]) + r[6 * k + 3 + q]);
+        }
+        pad = 1.220703125e-04f * m + 1e-6f;      /* 2^-13 */
+    }
+    const int by = tile / tiles_x, bx = tile - by * tiles_x;
+    const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
+    const int x1 = min(x0 + RT_SMALL_TILE_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_TILE_H - 1, f.imgh - 1);
+    const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
+    const RsFrustum fr = rs_tile_frustum(f, x0, y0, x1, y1);
+    unsigned short* __restrict__ out = tile_lists + (size_t)tile * RT_SMALL_LIST;
+    int count = 0;
+    for (int j0 = 0; j0 < n; j0 += 32) {
+        const int j = j0 + lane;
+        const bool keep = j < n && (!fr.ok || rs_tile_may_hit(fr, eye, sc.prims + 3 * j, pad));
+        const unsigned int m = __ballot_sync(0xffffffffu, keep);
+        const int at = count + __popc(m & ((1u << lane) - 1u));
+        if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + 48 * j);
+        count += __popc(m);
+    }
+    if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
+}
+
+/* ---------------------------------------------------------------- tracer */
+
+template <bool COUNT>
+__global__ void __launch_bounds__(RT_SMALL_THREADS, RT_SMALL_CTAS_PER_SM)
+rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
+                      int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters,
+                      unsigned int* __restrict__ tile_counter, const unsigned short* __restrict__ tile_lists,
+                      int tiles_x, unsigned int n_tiles, unsigned int n_whole, int force_linear) {
+    /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
+    __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
+    __shared__ short s_stack[(RT_SMALL_STACK + 1) * RT_SMALL_THREADS];
+    __shared__ unsigned short s_list[RT_SMALL_WARPS][RT_SMALL_LIST];   /* per-warp primary candidates */
+    extern __shared__ __align__(16) unsigned char smem[];
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
+    const int prims_off = 64 * n_nodes;
+    float4* s_nodes = (float4*)smem;
+    float4* s_prims = s_nodes + 4 * n_nodes;
+    float4* s_mats = s_prims + 3 * n;
+    float4* s_planes = s_mats + 2 * sc.n_objects;
+
+    /* Work fetches k = 0,1,2,...: k < n_whole is the whole tile k (4 patches); beyond that fetch k is the
+     * single patch q = 4 n_whole + (k - n_whole).  While a whole tile is traced the next fetch is already in
+     * flight; in the single-patch part nothing is reserved ahead, so the tail of the frame is one patch. */
+    const unsigned int n_fetch = n_whole + RT_SMALL_PATCHES * (n_tiles - n_whole);
+    unsigned int u0 = 0;
+    if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
+
+    /* stage the scene: links become byte offsets from the start of the nodes */
+    for (int i = tid; i < 4 * n_nodes; i += RT_SMALL_THREADS) {
+        float4 v = __ldg(sc.nodes + i);
+        if ((i & 3) == 3) {
+            const int c0 = __float_as_int(v.x), c1 = __float_as_int(v.y);
+            v.x = __int_as_float(c0 >= 0 ? c0 * 64 : ~(prims_off + (~c0) * 48));
+            v.y = __int_as_float(c1 >= 0 ? c1 * 64 : ~(prims_off + (~c1) * 48));
+        }
+        s_nodes[i] = v;
+    }
+    for (int i = tid; i < 3 * n; i += RT_SMALL_THREADS) s_prims[i] = __ldg(sc.prims + i);
+    for (int i = tid; i < 2 * sc.n_objects; i += RT_SMALL_THREADS) s_mats[i] = __ldg(sc.mats + i);
+    for (int i = tid; i < 2 * sc.n_planes; i += RT_SMALL_THREADS) s_planes[i] = __ldg(sc.planes + i);
+    __syncthreads();                             /* the only CTA barrier */
+
+    RtSmallShared sh;
+    /* opaque moves: keep the two addresses in registers instead of re-deriving them in the hot loops */
+    {
+        const unsigned int b0 = (unsigned int)__cvta_generic_to_shared(smem);
+        const unsigned int s0 = (unsigned int)__cvta_generic_to_shared(s_stack + tid);
+        asm volatile("mov.u32 %0, %1;" : "=r"(sh.base) : "r"(b0));
+        asm volatile("mov.u32 %0, %1;" : "=r"(sh.stack0) : "r"(s0));
+    }
+    sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;
+    sh.mats = s_mats;
+    sh.planes = s_planes;
+    sh.list = s_list[warp];
+    sh.n_prims = n;
+    sh.n_planes = sc.n_planes;
+    sh.prims_off = prims_off;
+    sh.root = n > 1 ? 0 : ~prims_off;
+    RtSmallScene<COUNT> acc(sh);
+
+    RtPixelCounters pc = {{0, 0, 0, 0}, 0, 0, 0, 0};
+    unsigned int n_pixels = 0;
+
+    u0 = __shfl_sync(0xffffffffu, u0, 0);
+    while (u0 < n_fetch) {
+        const bool whole = u0 < n_whole;
+        const unsigned int tile = whole ? u0 : (RT_SMALL_PATCHES * n_whole + (u0 - n_whole)) / RT_SMALL_PATCHES;
+        const unsigned short entry = __ldg(tile_lists + (size_t)tile * RT_SMALL_LIST + lane);
+        unsigned int u1 = 0;
+        if (whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);      /* lands while the tile is traced */
+        const int p_first = whole ? 0 : (int)((u0 - n_whole) % RT_SMALL_PATCHES);
+        const int p_count = whole ? RT_SMALL_PATCHES : 1;
+        const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
+        const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
+        s_list[warp][lane] = entry;
+        __syncwarp();
+
+#pragma unroll 1
+        for (int p = p_first; p < p_first + p_count; p++) {
+            const int x = x0 + (p % (RT_SMALL_TILE_W / 8)) * 8 + (lane & 7);
+            const int y = y0 + (p / (RT_SMALL_TILE_W / 8)) * 4 + (lane >> 3);
+            if (x < f.imgw && y < f.imgh && rt_shard_needs(f, x, y)) {
+                image[y * f.imgw + x] = rt_trace_pixel<RtSmallScene<COUNT>, COUNT>(acc, f, x, y, s_pending,
+                                                                                  RT_SMALL_THREADS, tid, hit_ids, pc);
+                n_pixels++;
+            }
+        }
+        __syncwarp();                            /* the list is rewritten for the next unit */
+        if (!whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);
+        u0 = __shfl_sync(0xffffffffu, u1, 0);
+    }
+    if (COUNT) {
+        /* all lanes take part: lanes without pixels add zeros */
+        rt_flush_counters(pc, n_pixels, counters);
+    }
+    /* The last warp to finish re-arms the work counter for the next launch on this stream: every warp's
+     * fetches precede its arrival here. */
+    if (lane == 0) {
+        __threadfence();
+        if (atomicAdd(tile_counter + 1, 1u) == gridDim.x * RT_SMALL_WARPS - 1) {
+            tile_counter[0] = 0;
+            tile_counter[1] = 0;
+        }
+    }
+}
+
+/* dynamic shared memory: the staged scene */
+extern "C" size_t rt_trace_small_smem_bytes(int n_bvh_prims, int n_objects, int n_planes) {
+    const size_t n_nodes = n_bvh_prims > 1 ? (size_t)n_bvh_prims - 1 : 0;
+    return 16 * (4 * n_nodes + 3 * (size_t)n_bvh_prims + 2 * (size_t)n_objects + 2 * (size_t)n_planes);
+}
+
+/* scenes this kernel accepts: link offsets (64 n_nodes + 48 n) must fit the 16-bit stack entries */
+extern "C" int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_planes) {
+    return n_bvh_prims <= RT_SMALL_MAX_PRIMS && n_planes <= 16 &&
+           rt_trace_small_smem_bytes(n_bvh_prims, n_objects, n_planes) <= RT_SMALL_DYN_SMEM_MAX;
+}
+
+/* per device, once (rt_create): opt in to the dynamic shared memory the largest accepted scene needs */
+extern "C" cudaError_t rt_trace_small_init(void) {
+    cudaError_t e = cudaFuncSetAttribute(rt_trace_small_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         RT_SMALL_DYN_SMEM_MAX);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(rt_trace_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                RT_SMALL_DYN_SMEM_MAX);
+}
+
+/* bytes of tile-list storage a frame of this size needs */
+extern "C" size_t rt_trace_small_list_bytes(int imgw, int imgh) {
+    const size_t tiles = (size_t)((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
+    return tiles * RT_SMALL_LIST * sizeof(unsigned short);
+}
+
+extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image,
+                                             int* hit_ids, RtCountersDev* counters, unsigned int* tile_counter,
+                                             unsigned short* tile_lists, int count, int force_linear, int n_sm,
+                                             cudaStream_t stream) {
+    const size_t smem = rt_trace_small_smem_bytes(sc->n_bvh_prims, sc->n_objects, sc->n_planes);
+    const int tiles_x = (f->imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W;
+    const int tiles = tiles_x * ((f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
+    rt_cull_tiles_kernel<<<(tiles + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, tiles_x, tiles);
+    int grid = n_sm * RT_SMALL_CTAS_PER_SM;
+    if (grid > (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
+    /* whole tiles for the first 5/8 of the frame, single patches after that: keeps the tail of the
+     * persistent warps to about one patch */
+    const unsigned int n_whole = (unsigned int)(((long long)tiles * 5) / 8);
+    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, force_linear);
+    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, force_linear);
+    return cudaGetLastError();
+}
