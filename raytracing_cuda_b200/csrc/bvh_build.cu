@@ -44,15 +44,13 @@ extern "C" __global__ void rt_bounds_init_kernel(unsigned int* bounds) {
     else if (threadIdx.x < 7) bounds[threadIdx.x] = 0u;
 }
 
-__global__ void rt_setup_kernel(const float* __restrict__ objs, int n_objects, const int* __restrict__ plane_idx,
-                                int n_planes, float4* __restrict__ mats, float4* __restrict__ recs,
-                                float4* __restrict__ planes, int* __restrict__ bvh_src,
-                                float4* __restrict__ prim_lo, float4* __restrict__ prim_hi,
-                                unsigned int* __restrict__ bounds) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    /* neutral elements for the warp-level bounds reduction at the end */
-    unsigned int bmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, bmax[4] = {0u, 0u, 0u, 0u};
-    if (i < n_objects) {
+/* One object of the reference's AoS (68 B, structs.h:27-38) -> leaf record, material, padded-later AABB.
+ * Fills the ordered-uint centroid bounds of this object into bmin/bmax (neutral elements for planes). */
+__device__ __forceinline__ void rt_setup_object(int i, const float* __restrict__ objs, const int* __restrict__ plane_idx,
+                                                int n_planes, float4* __restrict__ mats, float4* __restrict__ recs,
+                                                float4* __restrict__ planes, int* __restrict__ bvh_src,
+                                                float4* __restrict__ prim_lo, float4* __restrict__ prim_hi,
+                                                unsigned int bmin[3], unsigned int bmax[4]) {
     const float* o = objs + (size_t)i * 17;
     const int type = __float_as_int(o[0]);
     const float shine = o[1], specular = o[2], mirror = o[3];
@@ -81,7 +79,8 @@ __global__ void rt_setup_kernel(const float* __restrict__ objs, int n_objects, c
         recs[3 * i] = q0; recs[3 * i + 1] = q1; recs[3 * i + 2] = make_float4(0.f, 0.f, 0.f, 0.f);
         planes[2 * my_plane] = q0;
         planes[2 * my_plane + 1] = q1;
-    } else {
+        return;
+    }
     const int k = i - planes_before;
     bvh_src[k] = i;
     float3 lo, hi;
@@ -111,20 +110,31 @@ __global__ void rt_setup_kernel(const float* __restrict__ objs, int n_objects, c
                            fmaxf(fabsf(lo.z), fabsf(hi.z)));
     bmin[0] = f2ord(cx); bmin[1] = f2ord(cy); bmin[2] = f2ord(cz);
     bmax[0] = f2ord(cx); bmax[1] = f2ord(cy); bmax[2] = f2ord(cz); bmax[3] = f2ord(ma);
-    }   /* non-plane */
-    }   /* i < n_objects */
-    /* one atomic per warp and bound instead of one per primitive */
+}
+
+/* warp reduction of the centroid bounds, then one atomic per warp and bound (bounds: global or shared) */
+__device__ __forceinline__ void rt_merge_bounds(unsigned int bmin[3], unsigned int bmax[4], unsigned int* bounds) {
 #pragma unroll
     for (int a = 0; a < 3; a++) bmin[a] = __reduce_min_sync(0xFFFFFFFFu, bmin[a]);
 #pragma unroll
     for (int a = 0; a < 4; a++) bmax[a] = __reduce_max_sync(0xFFFFFFFFu, bmax[a]);
-    if ((threadIdx.x & 31) == 0) {
-        if (bmin[0] != 0xFFFFFFFFu) {
-            atomicMin(&bounds[0], bmin[0]); atomicMin(&bounds[1], bmin[1]); atomicMin(&bounds[2], bmin[2]);
-            atomicMax(&bounds[3], bmax[0]); atomicMax(&bounds[4], bmax[1]); atomicMax(&bounds[5], bmax[2]);
-            atomicMax(&bounds[6], bmax[3]);
-        }
+    if ((threadIdx.x & 31) == 0 && bmin[0] != 0xFFFFFFFFu) {
+        atomicMin(&bounds[0], bmin[0]); atomicMin(&bounds[1], bmin[1]); atomicMin(&bounds[2], bmin[2]);
+        atomicMax(&bounds[3], bmax[0]); atomicMax(&bounds[4], bmax[1]); atomicMax(&bounds[5], bmax[2]);
+        atomicMax(&bounds[6], bmax[3]);
     }
+}
+
+__global__ void rt_setup_kernel(const float* __restrict__ objs, int n_objects, const int* __restrict__ plane_idx,
+                                int n_planes, float4* __restrict__ mats, float4* __restrict__ recs,
+                                float4* __restrict__ planes, int* __restrict__ bvh_src,
+                                float4* __restrict__ prim_lo, float4* __restrict__ prim_hi,
+                                unsigned int* __restrict__ bounds) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    /* neutral elements for the warp-level bounds reduction */
+    unsigned int bmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, bmax[4] = {0u, 0u, 0u, 0u};
+    if (i < n_objects) rt_setup_object(i, objs, plane_idx, n_planes, mats, recs, planes, bvh_src, prim_lo, prim_hi, bmin, bmax);
+    rt_merge_bounds(bmin, bmax, bounds);
 }
 
 __device__ __forceinline__ unsigned int expand10(unsigned int v) {
@@ -367,12 +377,17 @@ __global__ void rt_karras_kernel(const unsigned int* __restrict__ keys, int n, i
 
 /* A child's box goes to two places: exact (lo,hi) into the build-side `aux` array, from which the sibling
  * forms the union, and centre / half-extent into the traversal node record (rt_device.h), rounded outward
- * so that [c-e, c+e] contains [lo,hi]. */
-__device__ __forceinline__ void rt_store_child_box(float* __restrict__ node, float* __restrict__ aux, int which,
+ * so that [c-e, c+e] contains [lo,hi].  BLOCK: aux lives in shared memory (single-CTA refit). */
+template <bool BLOCK>
+__device__ __forceinline__ void rt_store_child_box(float* __restrict__ node, float* aux, int which,
                                                    const float3& lo, const float3& hi) {
     float* a = aux + 6 * which;
-    __stcg(a + 0, lo.x); __stcg(a + 1, lo.y); __stcg(a + 2, lo.z);
-    __stcg(a + 3, hi.x); __stcg(a + 4, hi.y); __stcg(a + 5, hi.z);
+    if (BLOCK) {
+        a[0] = lo.x; a[1] = lo.y; a[2] = lo.z; a[3] = hi.x; a[4] = hi.y; a[5] = hi.z;
+    } else {
+        __stcg(a + 0, lo.x); __stcg(a + 1, lo.y); __stcg(a + 2, lo.z);
+        __stcg(a + 3, hi.x); __stcg(a + 4, hi.y); __stcg(a + 5, hi.z);
+    }
     const float grow = 1.0f + 4.76837158203125e-07f;   /* 1 + 2^-21 */
     const float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
     const float ex = fmaxf(hi.x - cx, cx - lo.x) * grow, ey = fmaxf(hi.y - cy, cy - lo.y) * grow,
@@ -382,15 +397,16 @@ __device__ __forceinline__ void rt_store_child_box(float* __restrict__ node, flo
     __stcg(r + 3, ex); __stcg(r + 4, ey); __stcg(r + 5, ez);
 }
 
-__global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
-                                const int* __restrict__ bvh_src, const float4* __restrict__ recs,
-                                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
-                                const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
-                                const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
-                                unsigned int* __restrict__ flags, float* __restrict__ nodes,
-                                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+/* Leaf slot j: copy its record into Morton order, pad its box and carry unions up while this thread is the
+ * second arrival at each node.  BLOCK: flags / aux in shared memory, block-scope fences (single CTA). */
+template <bool BLOCK>
+__device__ __forceinline__ void rt_refit_leaf(int j, int n, const unsigned int* __restrict__ sorted_vals,
+                                              const int* __restrict__ bvh_src, const float4* recs,
+                                              const float4* prim_lo, const float4* prim_hi, float extent, float maxabs,
+                                              const int2* __restrict__ children, const int* __restrict__ node_parent,
+                                              const int* __restrict__ leaf_parent, unsigned int* flags,
+                                              float* __restrict__ nodes, float* node_aux, float4* __restrict__ prims,
+                                              int* __restrict__ depth_out) {
     const int k = (int)sorted_vals[j];
     const int obj = bvh_src[k];
     prims[3 * j] = recs[3 * obj];
@@ -400,12 +416,9 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
         *depth_out = 0;
         return;
     }
-
     const float4 plo = prim_lo[k], phi = prim_hi[k];
-    const float extent = fmaxf(fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), ord2f(bounds[4]) - ord2f(bounds[1])),
-                               ord2f(bounds[5]) - ord2f(bounds[2]));
-    const float global_pad = 9.5367431640625e-07f * fmaxf(extent, ord2f(bounds[6]));   /* 2^-20 */
-    const float kRel = 3.0517578125e-05f;                                               /* 2^-15 */
+    const float global_pad = 9.5367431640625e-07f * fmaxf(extent, maxabs);   /* 2^-20 */
+    const float kRel = 3.0517578125e-05f;                                     /* 2^-15 */
     float3 lo, hi;
     {
         const float px = kRel * fmaxf(fabsf(plo.x), fabsf(phi.x)) + global_pad;
@@ -422,18 +435,24 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
         const int which = (ch.x == child) ? 0 : 1;
         float* rec = nodes + 16 * (size_t)node;
         float* aux = node_aux + 12 * (size_t)node;
-        rt_store_child_box(rec, aux, which, lo, hi);
+        rt_store_child_box<BLOCK>(rec, aux, which, lo, hi);
         if (which == 0) __stcg(rec + 12, __int_as_float(ch.x));
         else            __stcg(rec + 13, __int_as_float(ch.y));
-        __threadfence();
+        if (BLOCK) __threadfence_block(); else __threadfence();
         /* bit 0..7: arrivals, bits 8..: height of the first arrival's subtree */
         const unsigned int old = atomicAdd(&flags[node], 1u + (height << 8));
         if (old == 0u) return;                           /* first arrival: the sibling will carry on */
         height = max(height, old >> 8) + 1u;
         /* second arrival: the sibling's box is visible (written before its fence + atomic) */
         const float* oa = aux + 6 * (which ^ 1);
-        const float olx = __ldcg(oa + 0), oly = __ldcg(oa + 1), olz = __ldcg(oa + 2);
-        const float ohx = __ldcg(oa + 3), ohy = __ldcg(oa + 4), ohz = __ldcg(oa + 5);
+        float olx, oly, olz, ohx, ohy, ohz;
+        if (BLOCK) {
+            const volatile float* va = oa;
+            olx = va[0]; oly = va[1]; olz = va[2]; ohx = va[3]; ohy = va[4]; ohz = va[5];
+        } else {
+            olx = __ldcg(oa + 0); oly = __ldcg(oa + 1); olz = __ldcg(oa + 2);
+            ohx = __ldcg(oa + 3); ohy = __ldcg(oa + 4); ohz = __ldcg(oa + 5);
+        }
         lo = make_float3(fminf(lo.x, olx), fminf(lo.y, oly), fminf(lo.z, olz));
         hi = make_float3(fmaxf(hi.x, ohx), fmaxf(hi.y, ohy), fmaxf(hi.z, ohz));
         child = node;
@@ -442,6 +461,53 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
     *depth_out = (int)height;                /* only the thread that reached the root gets here */
 }
 
+__global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
+                                const int* __restrict__ bvh_src, const float4* __restrict__ recs,
+                                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
+                                const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
+                                const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
+                                unsigned int* __restrict__ flags, float* __restrict__ nodes,
+                                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const float extent = fmaxf(fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), ord2f(bounds[4]) - ord2f(bounds[1])),
+                               ord2f(bounds[5]) - ord2f(bounds[2]));
+    rt_refit_leaf<false>(j, n, sorted_vals, bvh_src, recs, prim_lo, prim_hi, extent, ord2f(bounds[6]), children,
+                         node_parent, leaf_parent, flags, nodes, node_aux, prims, depth_out);
+}
+
+/* Small scenes (<= RT_FUSED_MAX objects), topology unchanged: bounds + setup + refit in ONE single-CTA launch,
+ * arrival counters and the union scratch in shared memory (the per-frame path of launchKernel: the
+ * reference re-uploads its 133 objects every frame, kernel.cu:448). */
+#define RT_FUSED_MAX 1024
+__global__ void __launch_bounds__(RT_FUSED_MAX)
+rt_fused_refit_kernel(const float* __restrict__ objs, int n_objects, const int* __restrict__ plane_idx, int n_planes,
+                      float4* mats, float4* recs, float4* planes, int* bvh_src, float4* prim_lo, float4* prim_hi,
+                      unsigned int* __restrict__ bounds, const unsigned int* __restrict__ sorted_vals, int n,
+                      const int2* __restrict__ children, const int* __restrict__ node_parent,
+                      const int* __restrict__ leaf_parent, float* __restrict__ nodes, float4* __restrict__ prims,
+                      int* __restrict__ depth_out) {
+    extern __shared__ __align__(16) unsigned char fused_smem[];
+    __shared__ unsigned int s_bounds[8];
+    unsigned int* s_flags = (unsigned int*)fused_smem;                   /* [n-1] */
+    float* s_aux = (float*)(s_flags + (n > 1 ? n - 1 : 0));             /* [n-1][12] */
+    const int i = threadIdx.x;
+    if (i < 3) s_bounds[i] = 0xFFFFFFFFu;
+    else if (i < 8) s_bounds[i] = 0u;
+    for (int k = i; k < n - 1; k += blockDim.x) s_flags[k] = 0u;
+    __syncthreads();
+    unsigned int bmin[3] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu}, bmax[4] = {0u, 0u, 0u, 0u};
+    if (i < n_objects) rt_setup_object(i, objs, plane_idx, n_planes, mats, recs, planes, bvh_src, prim_lo, prim_hi, bmin, bmax);
+    rt_merge_bounds(bmin, bmax, s_bounds);
+    __syncthreads();                         /* recs / prim boxes written above are visible to the whole CTA */
+    if (i < 8) bounds[i] = s_bounds[i];
+    if (i < n) {
+        const float extent = fmaxf(fmaxf(ord2f(s_bounds[3]) - ord2f(s_bounds[0]), ord2f(s_bounds[4]) - ord2f(s_bounds[1])),
+                                   ord2f(s_bounds[5]) - ord2f(s_bounds[2]));
+        rt_refit_leaf<true>(i, n, sorted_vals, bvh_src, recs, prim_lo, prim_hi, extent, ord2f(s_bounds[6]), children,
+                            node_parent, leaf_parent, s_flags, nodes, s_aux, prims, depth_out);
+    }
+}
 
 /* ------------------------------------------------------------------ PLOC hierarchy (small scenes)
  *
@@ -567,6 +633,16 @@ rt_ploc_small_kernel(const unsigned int* __restrict__ sorted_vals, int n, const 
  * builder 0: PLOC when n <= PLOC_MAX, else Karras; 1: Karras; 2: PLOC (falls back to Karras above PLOC_MAX) */
 extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, int builder, cudaStream_t stream) {
     const int T = RT_BUILD_THREADS;
+    const size_t fused_smem = (size_t)(b->n_bvh > 1 ? b->n_bvh - 1 : 0) * (sizeof(unsigned int) + 12 * sizeof(float));
+    if (mode == 1 && b->n_objects <= RT_FUSED_MAX && b->n_bvh >= 1 && fused_smem <= 40 * 1024) {
+        const int n = b->n_bvh;
+        const size_t smem = fused_smem;
+        rt_fused_refit_kernel<<<1, RT_FUSED_MAX, smem, stream>>>(b->objs, b->n_objects, b->plane_idx, b->n_planes, b->mats,
+                                                               b->recs, b->planes, b->bvh_src, b->prim_lo, b->prim_hi,
+                                                               b->bounds, b->vals, n, b->children, b->node_parent,
+                                                               b->leaf_parent, b->nodes, b->prims, b->depth);
+        return cudaGetLastError();
+    }
     rt_bounds_init_kernel<<<1, 32, 0, stream>>>(b->bounds);
     if (b->n_objects > 0)
         rt_setup_kernel<<<(b->n_objects + T - 1) / T, T, 0, stream>>>(b->objs, b->n_objects, b->plane_idx, b->n_planes,

@@ -40,7 +40,9 @@
 #define RT_STACK_SIZE 64
 /* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 48*n must fit 16 bits */
 #define RT_SMALL_MAX_PRIMS 288
+#ifndef RT_SMALL_DYN_SMEM_MAX
 #define RT_SMALL_DYN_SMEM_MAX (24 * 1024)
+#endif
 
 struct RtSceneDev {
     const float4* nodes;

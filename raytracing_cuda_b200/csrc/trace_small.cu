@@ -58,6 +58,9 @@ __device__ __forceinline__ void rs_push(unsigned int& sp, int v) {
     asm volatile("st.shared.u16 [%0], %1;" ::"r"(sp), "h"((short)v));
     sp += RT_SMALL_STACK_STRIDE;
 }
+__device__ __forceinline__ void rs_store(unsigned int sp, int v) {
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(sp), "h"((short)v));
+}
 __device__ __forceinline__ int rs_pop(unsigned int& sp) {
     short v;
     sp -= RT_SMALL_STACK_STRIDE;
@@ -107,7 +110,12 @@ __device__ __forceinline__ bool rs_traverse(const RtSmallShared& s, const vec3& 
             if (h0 | h1) {
                 const bool second_first = h1 && (!h0 || t1 < t0);
                 const int near = second_first ? c1 : c0;
-                if (h0 && h1) rs_push(sp, c0 ^ c1 ^ near);
+#ifndef RS_BRANCHLESS_PUSH
+                if (h0 && h1) rs_push(sp, c0 ^ c1 ^ near);     /* measured faster than the branch-free form below */
+#else
+                rs_store(sp, c0 ^ c1 ^ near);
+                sp += (h0 && h1) ? RT_SMALL_STACK_STRIDE : 0;
+#endif
                 node = near;
                 continue;
             }
@@ -290,13 +298,20 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 #define RT_SMALL_TILE_W 16
 #define RT_SMALL_TILE_H 8
 #define RT_SMALL_PATCHES 4            /* 8x4 patches per tile */
-#define RT_SMALL_LIST 32              /* ushorts per tile list: [0] = count (0xFFFF: too many, traverse), [1..31] */
+#define RT_SMALL_LIST 32              /* ushorts per bin list: [0] = count (0xFFFF: too many, traverse), [1..31] */
+/* candidate lists are kept per BIN of RT_SMALL_BIN_W x RT_SMALL_BIN_H pixels (whole tiles) */
+#ifndef RT_SMALL_BIN_W
+#define RT_SMALL_BIN_W 64
+#endif
+#ifndef RT_SMALL_BIN_H
+#define RT_SMALL_BIN_H 16
+#endif
 
 /* ---------------------------------------------------------------- binning pre-pass */
 
 __global__ void __launch_bounds__(256)
 rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
-                     int n_tiles) {
+                     int n_tiles) {   /* tiles here = bins */
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (tile >= n_tiles) return;
@@ -317,8 +332,8 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
         pad = 1.220703125e-04f * m + 1e-6f;      /* 2^-13 */
     }
     const int by = tile / tiles_x, bx = tile - by * tiles_x;
-    const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
-    const int x1 = min(x0 + RT_SMALL_TILE_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_TILE_H - 1, f.imgh - 1);
+    const int x0 = bx * RT_SMALL_BIN_W, y0 = by * RT_SMALL_BIN_H;
+    const int x1 = min(x0 + RT_SMALL_BIN_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_BIN_H - 1, f.imgh - 1);
     const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
     const RsFrustum fr = rs_tile_frustum(f, x0, y0, x1, y1);
     unsigned short* __restrict__ out = tile_lists + (size_t)tile * RT_SMALL_LIST;
@@ -341,10 +356,10 @@ __global__ void __launch_bounds__(RT_SMALL_THREADS, RT_SMALL_CTAS_PER_SM)
 rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
                       int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters,
                       unsigned int* __restrict__ tile_counter, const unsigned short* __restrict__ tile_lists,
-                      int tiles_x, unsigned int n_tiles, unsigned int n_whole, int force_linear) {
+                      int tiles_x, unsigned int n_tiles, unsigned int n_whole, int bins_x, int force_linear) {
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
-    __shared__ short s_stack[(RT_SMALL_STACK + 1) * RT_SMALL_THREADS];
+    __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
     __shared__ unsigned short s_list[RT_SMALL_WARPS][RT_SMALL_LIST];   /* per-warp primary candidates */
     extern __shared__ __align__(16) unsigned char smem[];
 
@@ -387,7 +402,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.base) : "r"(b0));
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.stack0) : "r"(s0));
     }
-    sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;
+    sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;   /* one slot above the top is scratch (rs_store) */
     sh.mats = s_mats;
     sh.planes = s_planes;
     sh.list = s_list[warp];
@@ -404,13 +419,14 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     while (u0 < n_fetch) {
         const bool whole = u0 < n_whole;
         const unsigned int tile = whole ? u0 : (RT_SMALL_PATCHES * n_whole + (u0 - n_whole)) / RT_SMALL_PATCHES;
-        const unsigned short entry = __ldg(tile_lists + (size_t)tile * RT_SMALL_LIST + lane);
+        const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
+        const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
+        const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
+        const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
         unsigned int u1 = 0;
         if (whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);      /* lands while the tile is traced */
         const int p_first = whole ? 0 : (int)((u0 - n_whole) % RT_SMALL_PATCHES);
         const int p_count = whole ? RT_SMALL_PATCHES : 1;
-        const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
-        const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
         s_list[warp][lane] = entry;
         __syncwarp();
 
@@ -466,8 +482,8 @@ extern "C" cudaError_t rt_trace_small_init(void) {
 
 /* bytes of tile-list storage a frame of this size needs */
 extern "C" size_t rt_trace_small_list_bytes(int imgw, int imgh) {
-    const size_t tiles = (size_t)((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
-    return tiles * RT_SMALL_LIST * sizeof(unsigned short);
+    const size_t bins = (size_t)((imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W) * ((imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
+    return bins * RT_SMALL_LIST * sizeof(unsigned short);
 }
 
 extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image,
@@ -477,13 +493,15 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const size_t smem = rt_trace_small_smem_bytes(sc->n_bvh_prims, sc->n_objects, sc->n_planes);
     const int tiles_x = (f->imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W;
     const int tiles = tiles_x * ((f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
-    rt_cull_tiles_kernel<<<(tiles + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, tiles_x, tiles);
+    const int bins_x = (f->imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W;
+    const int bins = bins_x * ((f->imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
+    rt_cull_tiles_kernel<<<(bins + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, bins_x, bins);
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     if (grid > (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
     /* whole tiles for the first 5/8 of the frame, single patches after that: keeps the tail of the
      * persistent warps to about one patch */
     const unsigned int n_whole = (unsigned int)(((long long)tiles * 5) / 8);
-    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, force_linear);
-    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, force_linear);
+    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, bins_x, force_linear);
+    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, bins_x, force_linear);
     return cudaGetLastError();
 }
