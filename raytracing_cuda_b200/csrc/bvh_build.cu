@@ -520,7 +520,9 @@ rt_fused_refit_kernel(const float* __restrict__ objs, int n_objects, const int* 
  * prefix sum, descending, so the last merge -- the root -- is node 0).  Emits the same topology arrays
  * as rt_karras_kernel; rt_refit_kernel then fills the boxes. */
 #define PLOC_MAX 1024
-#define PLOC_RADIUS 16
+#ifndef PLOC_RADIUS
+#define PLOC_RADIUS 40
+#endif
 
 __device__ __forceinline__ float ploc_area(const float* a, const float* b) {
     const float dx = fmaxf(a[3], b[3]) - fminf(a[0], b[0]);

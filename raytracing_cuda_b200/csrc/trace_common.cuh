@@ -173,12 +173,24 @@ __device__ __forceinline__ vec3 rt_hit_normal(const RtSceneDev& sc, const RtHit&
     return rt_normalize(rt_cross(f4xyz(__ldg(rec + 1)), f4xyz(__ldg(rec + 2))));
 }
 
+/* a / b in FP64 for a constant divisor b with rc = RN(1/b): q0 = a*rc, r = a - q0*b (exact in one FMA),
+ * q = q0 + r*rc is the correctly rounded quotient (Markstein), i.e. bit-identical to the IEEE division the
+ * reference executes -- 3 DFMA-class instructions instead of a ~30-instruction DDIV sequence.
+ * tests/test_numerics.py checks the identity with exact rational arithmetic. */
+__device__ __forceinline__ double rt_div_const(double a, double b, double rc) {
+    const double q0 = a * rc;
+    return __fma_rn(__fma_rn(-q0, b, a), rc, q0);
+}
+
 /* reference kernel.cu:154-164 with the truncating / wrapping uchar4 operators of structs.h:86-91.
- * Maps with weight 0 contribute (uchar)(v*0.0f) = 0, so skipping them is bit-identical. */
+ * Maps with weight 0 contribute (uchar)(v*0.0f) = 0, so skipping them is bit-identical.
+ * fmodf(v, 1) == v - truncf(v) exactly (the difference of a float and its integer part is representable). */
 __device__ __forceinline__ vec3 rt_sky(const RtFrameDev& f, const vec3& d) {
     const double PI = RTB_PI;
-    float y = (float)(1 - (asinf(d.y) + PI / 2.0f) / PI);
-    float x = fmodf((float)((atan2f(d.x, d.z) + PI) / (2.0f * PI) + f.dayTime), 1);
+    const double TWO_PI = 2.0f * PI;
+    float y = (float)(1 - rt_div_const(asinf(d.y) + PI / 2.0f, PI, 1.0 / PI));
+    const float xv = (float)(rt_div_const(atan2f(d.x, d.z) + PI, TWO_PI, 1.0 / TWO_PI) + f.dayTime);
+    float x = xv - truncf(xv);
     unsigned char r = 0, g = 0, b = 0;
 #pragma unroll
     for (int k = 0; k < 4; k++) {

@@ -50,3 +50,26 @@ def test_pack_roundtrip_all_bytes():
     v = np.arange(256, dtype=np.float32)
     back = (v * np.float32(1.0 / 255.0)) * np.float32(255.0)
     assert (np.clip(back, 0, 255).astype(np.int32) == np.arange(256)).all()
+
+
+def test_constant_division_by_fma_correction_is_ieee_division():
+    """rt_div_const (csrc/trace_common.cuh): q0 = a*rc, q = q0 + (a - q0*b)*rc equals RN(a/b) for the two
+    divisors of the sky lookup (reference kernel.cu:156-157, PI = 3.141592).  Exact rational arithmetic
+    stands in for the two FMAs."""
+    from fractions import Fraction as F
+    PI = 3.141592
+    rng = np.random.default_rng(11)
+    for b in (PI, float(np.float32(2.0)) * PI):
+        rc = 1.0 / b
+        vals = list(rng.uniform(0.0, 6.4, 4000)) + [float(np.float64(np.arcsin(np.float32(v))) + PI / 2.0)
+                                                     for v in rng.uniform(-1, 1, 2000).astype(np.float32)]
+        for a in vals:
+            q0 = a * rc
+            r = float(F(a) - F(q0) * F(b))            # fma(-q0, b, a): one rounding
+            q = float(F(q0) + F(r) * F(rc))           # fma(r, rc, q0): one rounding
+            assert q == a / b, (a, b)
+
+
+def test_fmodf_one_equals_x_minus_trunc():
+    x = np.concatenate([np.random.default_rng(5).uniform(-3, 3, 20000), [0.0, 1.0, 1.9999999, -0.5]]).astype(np.float32)
+    assert (np.fmod(x, np.float32(1.0)) == x - np.trunc(x)).all()
