@@ -186,8 +186,8 @@ int rt_create(int device, rt_context** out) {
     cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
     if (cudaMalloc((void**)&ctx->d_counters, sizeof(RtCountersDev)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
     cudaMemset(ctx->d_counters, 0, sizeof(RtCountersDev));
-    if (cudaMalloc((void**)&ctx->d_tile_counter, 4 * sizeof(unsigned int)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
-    cudaMemset(ctx->d_tile_counter, 0, 4 * sizeof(unsigned int));
+    if (cudaMalloc((void**)&ctx->d_tile_counter, 64 * sizeof(unsigned int)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
+    cudaMemset(ctx->d_tile_counter, 0, 64 * sizeof(unsigned int));
     if (rt_trace_small_init() != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
     for (int i = 0; i < 6; i++) cudaEventCreate(&ctx->ev[i]);
     *out = ctx;

@@ -88,6 +88,12 @@ rt_fxaa_smem_kernel(const unsigned int* __restrict__ in, unsigned int* __restric
     __shared__ unsigned int s_px[FX_BH + 2][FX_BW + 2];
     __shared__ float s_lum[FX_BH + 2][FX_BW + 2];
     const int x0 = blockIdx.x * FX_BW - 1, y0 = blockIdx.y * FX_BH - 1;
+    if (n_shards > 1) {
+        /* blocks that own no pixel of this shard leave before touching memory */
+        const int px = blockIdx.x * FX_BW + threadIdx.x, py = blockIdx.y * FX_BH + threadIdx.y;
+        const bool mine = px < w && py < h && rt_tile_owner(px, py, tile_w, tile_h, n_shards, stride) == shard_id;
+        if (!__syncthreads_or(mine)) return;
+    }
     for (int i = threadIdx.y * FX_BW + threadIdx.x; i < (FX_BH + 2) * (FX_BW + 2); i += FX_BW * FX_BH) {
         const int ly = i / (FX_BW + 2), lx = i % (FX_BW + 2);
         const int gx = x0 + lx, gy = y0 + ly;

@@ -4,21 +4,23 @@
  * RT_SMALL_MAX_PRIMS).  Same per-pixel arithmetic as trace.cu (trace_pixel.cuh), so the
  * two kernels agree bit for bit; only WHICH primitives get tested differs.
  *
- *   - rt_cull_tiles_kernel (binning pre-pass, one warp per 16x8-pixel tile): primary rays do
- *     not traverse the hierarchy at all.  The warp culls the primitives against the tile's
+ *   - rt_cull_tiles_kernel (binning pre-pass, one warp per 64x16-pixel bin): primary rays do
+ *     not traverse the hierarchy at all.  The warp culls the primitives against the bin's
  *     frustum (4 planes through the eye, 32 primitives per step, back-facing triangles
  *     dropped -- they fail `det < 0.001`, kernel.cu:104) into a short, index-ordered
- *     candidate list in HBM (ballot compaction, 64 B per tile);
+ *     candidate list in HBM (ballot compaction, 64 B per bin).  For a screen-tile shard it
+ *     also marks which 16x8 work tiles hold pixels to trace (own tiles + 1-pixel FXAA apron)
+ *     and rt_worklist_scan_kernel turns the marks into a compact, raster-ordered work list;
  *   - rt_trace_small_kernel: persistent CTAs (4 per SM); the LBVH nodes, leaf records,
  *     materials and planes are staged into shared memory once per CTA (the reference keeps
  *     its 133 objects in __constant__, kernel.cu:14).  After that every WARP is autonomous:
- *     it fetches work from an atomic counter -- whole tiles (four 8x4 patches) for the first
- *     part of the frame, single patches for the rest so that the tail stays short -- two
- *     fetches ahead, with the tile's candidate list loaded one unit ahead; no CTA barrier in
- *     the loop.  Every pixel of a tile tests just the tile's list for its primary ray;
+ *     it fetches work from an atomic counter -- whole 16x8 tiles (four 8x4 patches) for the
+ *     first 5/8 of the frame, single patches for the rest so that the tail stays short --
+ *     with the next fetch in flight while a whole tile is traced; no CTA barrier in the
+ *     loop.  Every pixel tests just its bin's list for its primary ray;
  *   - shadow and mirror rays traverse the shared-memory LBVH with a per-thread stack of
- *     16-bit entries in shared memory (no local memory), child links pre-scaled to byte
- *     offsets, branch-free near/far selection.
+ *     16-bit entries in shared memory (no local memory, sentinel at the bottom), child links
+ *     pre-scaled to byte offsets so that a node fetch is one add + four LDS.128.
  *
  * Conservative culling: the tile is grown by one pixel on every side and each plane test
  * gets a world-space pad (2^-13 of the largest coordinate in play), both orders of
@@ -298,6 +300,7 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 #define RT_SMALL_TILE_W 16
 #define RT_SMALL_TILE_H 8
 #define RT_SMALL_PATCHES 4            /* 8x4 patches per tile */
+#define RS_CNT_TILES 32               /* tile_counter[]: [0] next fetch, [1] finished warps, [32] listed tiles */
 #define RT_SMALL_LIST 32              /* ushorts per bin list: [0] = count (0xFFFF: too many, traverse), [1..31] */
 /* candidate lists are kept per BIN of RT_SMALL_BIN_W x RT_SMALL_BIN_H pixels (whole tiles) */
 #ifndef RT_SMALL_BIN_W
@@ -311,10 +314,32 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 
 __global__ void __launch_bounds__(256)
 rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
-                     int n_tiles) {   /* tiles here = bins */
+                     int n_tiles, unsigned char* __restrict__ bin_need, int work_tiles_x,
+                     int work_tiles_y) {   /* tiles_x, n_tiles count BINS here; bin_need = NULL for whole frames */
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (tile >= n_tiles) return;
+    /* The work tiles (16x8) of this bin that hold at least one pixel to trace: all of them, or with a
+     * screen-tile shard those with own pixels or pixels of the 1-pixel FXAA apron. */
+    const int bby = tile / tiles_x, bbx = tile - bby * tiles_x;
+    const int wx = bbx * (RT_SMALL_BIN_W / RT_SMALL_TILE_W) + lane % (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
+    const int wy = bby * (RT_SMALL_BIN_H / RT_SMALL_TILE_H) + lane / (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
+    bool need = lane < (RT_SMALL_BIN_W / RT_SMALL_TILE_W) * (RT_SMALL_BIN_H / RT_SMALL_TILE_H) && wx < work_tiles_x &&
+                wy < work_tiles_y;
+    if (need && f.n_shards > 1) {
+        /* the work tile grown by one pixel, in shard-tile coordinates */
+        const int ax = max(wx * RT_SMALL_TILE_W - 1, 0) / f.tile_w;
+        const int bx2 = min(wx * RT_SMALL_TILE_W + RT_SMALL_TILE_W, f.imgw - 1) / f.tile_w;
+        const int ay = max(wy * RT_SMALL_TILE_H - 1, 0) / f.tile_h;
+        const int by2 = min(wy * RT_SMALL_TILE_H + RT_SMALL_TILE_H, f.imgh - 1) / f.tile_h;
+        need = false;
+        for (int ty = ay; ty <= by2 && !need; ty++)
+            for (int tx = ax; tx <= bx2; tx++)
+                if ((tx + ty * f.stride) % f.n_shards == f.shard_id) { need = true; break; }
+    }
+    const unsigned int need_mask = __ballot_sync(0xffffffffu, need);
+    if (bin_need && lane == 0) bin_need[tile] = (unsigned char)need_mask;   /* sharded frames: input of the list scan */
+    if (need_mask == 0u) return;                 /* nothing of this bin is traced here: no list needed either */
     const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
     const int prims_off = 64 * n_nodes;
     /* world-space pad of the cull tests from the scene's extent and the eye position */
@@ -331,8 +356,7 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
         }
         pad = 1.220703125e-04f * m + 1e-6f;      /* 2^-13 */
     }
-    const int by = tile / tiles_x, bx = tile - by * tiles_x;
-    const int x0 = bx * RT_SMALL_BIN_W, y0 = by * RT_SMALL_BIN_H;
+    const int x0 = bbx * RT_SMALL_BIN_W, y0 = bby * RT_SMALL_BIN_H;
     const int x1 = min(x0 + RT_SMALL_BIN_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_BIN_H - 1, f.imgh - 1);
     const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
     const RsFrustum fr = rs_tile_frustum(f, x0, y0, x1, y1);
@@ -347,6 +371,51 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
         count += __popc(m);
     }
     if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
+
+}
+
+/* Sharded frames: the work tiles this shard has to trace, as a compact list in bin-raster order (deterministic:
+ * positions come from a block scan, not from atomics).  One CTA; thread t owns a contiguous run of bins. */
+__global__ void __launch_bounds__(1024)
+rt_worklist_scan_kernel(const unsigned char* __restrict__ bin_need, int bins_x, int n_bins, int work_tiles_x,
+                        unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count) {
+    __shared__ unsigned int s_warp[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int per = (n_bins + 1023) / 1024;
+    const int b0 = min(t * per, n_bins), b1 = min(b0 + per, n_bins);
+    unsigned int mine = 0;
+    for (int b = b0; b < b1; b++) mine += (unsigned int)__popc((unsigned int)bin_need[b]);
+    unsigned int s = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int v = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane >= o) s += v;
+    }
+    if (lane == 31) s_warp[warp] = s;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned int ws = s_warp[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int v = __shfl_up_sync(0xffffffffu, ws, o);
+            if (lane >= o) ws += v;
+        }
+        s_warp[lane] = ws;
+    }
+    __syncthreads();
+    unsigned int at = (warp ? s_warp[warp - 1] : 0u) + s - mine;
+    for (int b = b0; b < b1; b++) {
+        unsigned int m = (unsigned int)bin_need[b];
+        const int bby = b / bins_x, bbx = b - bby * bins_x;
+        while (m) {
+            const int l = __ffs(m) - 1;
+            m &= m - 1;
+            const int wx = bbx * (RT_SMALL_BIN_W / RT_SMALL_TILE_W) + l % (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
+            const int wy = bby * (RT_SMALL_BIN_H / RT_SMALL_TILE_H) + l / (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
+            work_list[at++] = (unsigned int)(wy * work_tiles_x + wx);
+        }
+    }
+    if (t == 1023) *work_count = s_warp[31];
 }
 
 /* ---------------------------------------------------------------- tracer */
@@ -356,7 +425,8 @@ __global__ void __launch_bounds__(RT_SMALL_THREADS, RT_SMALL_CTAS_PER_SM)
 rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
                       int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters,
                       unsigned int* __restrict__ tile_counter, const unsigned short* __restrict__ tile_lists,
-                      int tiles_x, unsigned int n_tiles, unsigned int n_whole, int bins_x, int force_linear) {
+                      int tiles_x, unsigned int n_tiles_all, int bins_x,
+                      const unsigned int* __restrict__ work_list, int force_linear) {
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
@@ -372,9 +442,16 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     float4* s_mats = s_prims + 3 * n;
     float4* s_planes = s_mats + 2 * sc.n_objects;
 
-    /* Work fetches k = 0,1,2,...: k < n_whole is the whole tile k (4 patches); beyond that fetch k is the
-     * single patch q = 4 n_whole + (k - n_whole).  While a whole tile is traced the next fetch is already in
-     * flight; in the single-patch part nothing is reserved ahead, so the tail of the frame is one patch. */
+    /* Work units over the tiles in raster order (screen-tile shards: over the list of the pre-pass, count in
+     * tile_counter[RS_CNT_TILES], its own cache line):
+     * fetch k < n_whole is the whole tile k (4 patches); beyond that fetch k is the single patch
+     * q = 4 n_whole + (k - n_whole).  While a whole tile is traced the next fetch is already in flight; in the
+     * single-patch part nothing is reserved ahead, so the tail of the frame is one patch.  (Ordering the tiles
+     * by an estimated cost class -- mirror surfaces first -- was measured and did not beat this: the long
+     * patches are few and not predictable from the candidate lists.) */
+    const bool listed = f.n_shards > 1;          /* whole frames walk all tiles in raster order, no list */
+    const unsigned int n_tiles = listed ? __ldcg(tile_counter + RS_CNT_TILES) : n_tiles_all;
+    const unsigned int n_whole = (unsigned int)(((unsigned long long)n_tiles * 5u) / 8u);
     const unsigned int n_fetch = n_whole + RT_SMALL_PATCHES * (n_tiles - n_whole);
     unsigned int u0 = 0;
     if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
@@ -416,17 +493,22 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     unsigned int n_pixels = 0;
 
     u0 = __shfl_sync(0xffffffffu, u0, 0);
+#ifdef RS_TIMELINE
+    unsigned long long tl_t0, tl_t1 = 0, tl_units = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
+#endif
     while (u0 < n_fetch) {
         const bool whole = u0 < n_whole;
-        const unsigned int tile = whole ? u0 : (RT_SMALL_PATCHES * n_whole + (u0 - n_whole)) / RT_SMALL_PATCHES;
+        const unsigned int slot = whole ? u0 : (RT_SMALL_PATCHES * n_whole + (u0 - n_whole)) / RT_SMALL_PATCHES;
+        const int p_first = whole ? 0 : (int)((u0 - n_whole) % RT_SMALL_PATCHES);
+        const int p_count = whole ? RT_SMALL_PATCHES : 1;
+        const unsigned int tile = listed ? __ldg(work_list + slot) : slot;
         const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
         const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
         const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
         const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
         unsigned int u1 = 0;
         if (whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);      /* lands while the tile is traced */
-        const int p_first = whole ? 0 : (int)((u0 - n_whole) % RT_SMALL_PATCHES);
-        const int p_count = whole ? RT_SMALL_PATCHES : 1;
         s_list[warp][lane] = entry;
         __syncwarp();
 
@@ -441,6 +523,10 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
             }
         }
         __syncwarp();                            /* the list is rewritten for the next unit */
+#ifdef RS_TIMELINE
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
+        tl_units += (unsigned long long)p_count;
+#endif
         if (!whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);
         u0 = __shfl_sync(0xffffffffu, u1, 0);
     }
@@ -448,6 +534,14 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         /* all lanes take part: lanes without pixels add zeros */
         rt_flush_counters(pc, n_pixels, counters);
     }
+#ifdef RS_TIMELINE
+    if (hit_ids && lane == 0) {   /* debug variant: per-warp (start, last unit done, exit, patches) as 4 x u64 */
+        unsigned long long tl_t2;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t2));
+        unsigned long long* o = (unsigned long long*)hit_ids + 4 * (size_t)(blockIdx.x * RT_SMALL_WARPS + warp);
+        o[0] = tl_t0; o[1] = tl_t1; o[2] = tl_t2; o[3] = tl_units;
+    }
+#endif
     /* The last warp to finish re-arms the work counter for the next launch on this stream: every warp's
      * fetches precede its arrival here. */
     if (lane == 0) {
@@ -455,6 +549,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         if (atomicAdd(tile_counter + 1, 1u) == gridDim.x * RT_SMALL_WARPS - 1) {
             tile_counter[0] = 0;
             tile_counter[1] = 0;
+            tile_counter[RS_CNT_TILES] = 0;
         }
     }
 }
@@ -483,7 +578,8 @@ extern "C" cudaError_t rt_trace_small_init(void) {
 /* bytes of tile-list storage a frame of this size needs */
 extern "C" size_t rt_trace_small_list_bytes(int imgw, int imgh) {
     const size_t bins = (size_t)((imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W) * ((imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
-    return bins * RT_SMALL_LIST * sizeof(unsigned short);
+    const size_t tiles = (size_t)((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
+    return bins * RT_SMALL_LIST * sizeof(unsigned short) + tiles * sizeof(unsigned int) + ((bins + 3) & ~(size_t)3);   /* bin lists + work list + need masks */
 }
 
 extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image,
@@ -495,13 +591,18 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const int tiles = tiles_x * ((f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
     const int bins_x = (f->imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W;
     const int bins = bins_x * ((f->imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
-    rt_cull_tiles_kernel<<<(bins + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, bins_x, bins);
+    const int tiles_y = (f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H;
+    /* behind the bin lists: the work list and the per-bin need masks of sharded frames */
+    unsigned int* work_list = (unsigned int*)(tile_lists + (size_t)bins * RT_SMALL_LIST);
+    unsigned char* bin_need = (unsigned char*)(work_list + tiles);
+    const bool sharded = f->n_shards > 1;
+    rt_cull_tiles_kernel<<<(bins + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, bins_x, bins, sharded ? bin_need : nullptr,
+                                                            tiles_x, tiles_y);
+    if (sharded)
+        rt_worklist_scan_kernel<<<1, 1024, 0, stream>>>(bin_need, bins_x, bins, tiles_x, work_list, tile_counter + RS_CNT_TILES);
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     if (grid > (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
-    /* whole tiles for the first 5/8 of the frame, single patches after that: keeps the tail of the
-     * persistent warps to about one patch */
-    const unsigned int n_whole = (unsigned int)(((long long)tiles * 5) / 8);
-    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, bins_x, force_linear);
-    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, n_whole, bins_x, force_linear);
+    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear);
+    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear);
     return cudaGetLastError();
 }

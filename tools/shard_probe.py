@@ -17,7 +17,7 @@ def t(fn, n=20):
     for _ in range(n): fn()
     b.record(); torch.cuda.synchronize()
     return a.elapsed_time(b) / n
-for name in ("builtin", "terrain"):
+for name in (sys.argv[1:] or ["builtin", "terrain"]):
     s = rt.Scene()
     if name == "builtin":
         f = s.configure(view=6, hours=14.0, imgw=w, imgh=h, alias=True); r.set_scene(s.objects, s.lights)
