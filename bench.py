@@ -260,15 +260,22 @@ def main():
     for k in range(args.steps):
         flush.fill_(k & 255)                      # L2 flush between timed iterations, outside the events
         ev[k][0].record(stream)
-        step_device(k == args.steps - 1)          # library-internal per-kernel events on the last step only
+        step_device(False)
         ev[k][1].record(stream)
     torch.cuda.synchronize()
     t_wall = time.perf_counter() - t_wall0
-    # per-kernel split of the LAST step (events inside the library, same stream)
-    for r, _ in ctxs:
-        t = r.timings()
-        trace_ms += t["trace_ms"]
-        fxaa_ms += t["fxaa_ms"]
+    # per-kernel split: the same K steps once more with the library's own CUDA events around the tracer
+    # (binning pre-pass + trace kernel) and the FXAA kernel, on the launching stream; averaged over the steps
+    for k in range(args.steps):
+        flush.fill_(k & 255)
+        for r, fr in ctxs:
+            r.set_option(_lib.RT_OPT_TIMING, 1)
+            r.render(fr, out_dev)
+            r.synchronize()
+            t = r.timings()
+            trace_ms += t["trace_ms"] / args.steps
+            fxaa_ms += t["fxaa_ms"] / args.steps
+            r.set_option(_lib.RT_OPT_TIMING, 0)
     clocks = sampler.stop()
     dev_ms = sum(a.elapsed_time(b) for a, b in ev)
     t = torch.tensor([dev_ms], dtype=torch.float64, device="cuda")
@@ -338,15 +345,21 @@ def main():
     trace_bytes = 4 * npx * 4 + sky_bytes                      # framebuffer write + sky texels per step
     trace_s = max(trace_ms, 1e-6) * 1e-3
     fxaa_s = max(fxaa_ms, 1e-6) * 1e-3
-    roofline = {"bound": "hbm", "kernel": "rt_trace_kernel", "achieved": trace_bytes / trace_s / 1e9, "peak": hbm_peak,
-                "unit": "GB/s", "frac": trace_bytes / trace_s / 1e9 / hbm_peak, "traffic": None,
+    traffic = {}
+    tp = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu --set full captures
+    if os.path.isfile(tp):
+        traffic = json.load(open(tp))
+    roofline = {"bound": "hbm", "kernel": "rt_trace_small_kernel (+ rt_cull_tiles_kernel)", "achieved": trace_bytes / trace_s / 1e9,
+                "peak": hbm_peak, "unit": "GB/s", "frac": trace_bytes / trace_s / 1e9 / hbm_peak,
+                "traffic": traffic.get("trace_bytes_per_step"),
                 "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                 "note": "tracer is FP32/latency bound (SURVEY 8d): see roofline_fp32; HBM-bound kernel is FXAA"}
-    roofline_fp32 = {"bound": "fp32", "kernel": "rt_trace_kernel", "achieved": flops_step / trace_s / 1e12,
+    roofline_fp32 = {"bound": "fp32", "kernel": "rt_trace_small_kernel (+ rt_cull_tiles_kernel)", "achieved": flops_step / trace_s / 1e12,
                      "peak": fp32_peak, "unit": "TFLOP/s", "frac": flops_step / trace_s / 1e12 / max(fp32_peak, 1e-9),
                      "peak_source": "measured FFMA microbenchmark (rt_measure_fp32_peak); nominal 74.4"}
     roofline_fxaa = {"bound": "hbm", "kernel": "rt_fxaa_tma_kernel", "achieved": 8.0 * npx * 4 / fxaa_s / 1e9,
-                     "peak": hbm_peak, "unit": "GB/s", "frac": 8.0 * npx * 4 / fxaa_s / 1e9 / hbm_peak, "traffic": None}
+                     "peak": hbm_peak, "unit": "GB/s", "frac": 8.0 * npx * 4 / fxaa_s / 1e9 / hbm_peak,
+                     "traffic": traffic.get("fxaa_bytes_per_step")}
 
     line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -356,12 +369,13 @@ def main():
                        "sky": "procedural %dx%d x4" % (SKY_W, SKY_H) if args.sky == "synthetic" else args.sky,
                        "l2": "flushed by a 256 MiB write between steps"},
             "frames_per_s": world * 4 / (ms_per_step * 1e-3), "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,
-            "kernel_ms_last_step": {"trace": trace_ms, "fxaa": fxaa_ms},
+            "kernel_ms_per_step": {"trace": trace_ms, "fxaa": fxaa_ms},
             "roofline": roofline, "roofline_fp32": roofline_fp32, "roofline_fxaa": roofline_fxaa,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "launchKernel (host Object/Light arrays per frame) + frame copied to pinned host memory",
                     "frames_per_s": world * 4 * args.steps / float(t.item())},
-            "gpu_launches": world * args.steps * 4 * 2, "clocks": clocks, "counters_per_step": counts}
+            "gpu_launches": world * args.steps * 4 * 3,   # per frame: binning pre-pass, tracer, FXAA
+            "clocks": clocks, "counters_per_step": counts}
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         y_step = 4

@@ -498,9 +498,17 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 #endif
     while (u0 < n_fetch) {
+#ifdef RS_SINGLES_FIRST
+        /* experiment: the last 3/8 of the raster (singles) first, the whole tiles of the first 5/8 after them */
+        const unsigned int n_single = RT_SMALL_PATCHES * (n_tiles - n_whole);
+        const bool whole = u0 >= n_single;
+        const unsigned int slot = whole ? u0 - n_single : n_whole + u0 / RT_SMALL_PATCHES;
+        const int p_first = whole ? 0 : (int)(u0 % RT_SMALL_PATCHES);
+#else
         const bool whole = u0 < n_whole;
         const unsigned int slot = whole ? u0 : (RT_SMALL_PATCHES * n_whole + (u0 - n_whole)) / RT_SMALL_PATCHES;
         const int p_first = whole ? 0 : (int)((u0 - n_whole) % RT_SMALL_PATCHES);
+#endif
         const int p_count = whole ? RT_SMALL_PATCHES : 1;
         const unsigned int tile = listed ? __ldg(work_list + slot) : slot;
         const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
