@@ -55,7 +55,7 @@ struct rt_context {
     int n_sm = 148;
     cudaStream_t stream = 0;
     std::string err;
-    int opt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int opt[RT_OPT_N] = {0};
 
     /* sky */
     cudaArray_t sky_arr[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -215,7 +215,7 @@ int rt_destroy(rt_context* ctx) {
 const char* rt_last_error(rt_context* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 
 int rt_set_option(rt_context* ctx, int key, int value) {
-    if (!ctx || key < 0 || key >= 8) return RT_ERR_ARG;
+    if (!ctx || key < 0 || key >= RT_OPT_N) return RT_ERR_ARG;
     if ((key == RT_OPT_BUILDER || key == RT_OPT_FORCE_RADIX) && ctx->opt[key] != value)
         ctx->have_scene = false;   /* the next rt_set_scene rebuilds the hierarchy */
     ctx->opt[key] = value;

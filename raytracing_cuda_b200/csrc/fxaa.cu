@@ -24,58 +24,7 @@
 #include <stdint.h>
 
 #include "rt_device.h"
-
-__device__ __forceinline__ float fx_lum(unsigned int c) {
-    const float r = (float)(c & 255u), g = (float)((c >> 8) & 255u), b = (float)((c >> 16) & 255u);
-    float l = __fmaf_rn(b, 0.0721750f, __fmaf_rn(r, 0.2126729f, __fmul_rn(g, 0.7151522f)));
-    return __fmul_rn(fminf(l, 255.0f), 0.0039215688593685626984f);
-}
-
-__device__ __forceinline__ unsigned int fx_pack(float r, float g, float b) {
-    r = fmaxf(0.0f, fminf(r, 255.0f));
-    g = fmaxf(0.0f, fminf(g, 255.0f));
-    b = fmaxf(0.0f, fminf(b, 255.0f));
-    return (unsigned int)(((int)b << 16) | ((int)g << 8) | (int)r);
-}
-
-/* Decide from the nine luminances.  Returns false when the pixel passes through
- * (kernel.cu:349-354); else the blend factor and the neighbour offset (kernel.cu:369-392). */
-__device__ __forceinline__ bool fx_decide(float M, float E, float W, float N, float S, float NE, float NW,
-                                          float SE, float SW, float& b, int& dx, int& dy) {
-    const float high = fmaxf(fmaxf(fmaxf(fmaxf(E, W), N), S), M);
-    const float low = fminf(fminf(fminf(fminf(E, W), N), S), M);
-    const float contrast = __fadd_rn(high, -low);
-    const float threshold = fmaxf(0.0312f, __fmul_rn(0.063f, high));
-    if (contrast < threshold) return false;
-
-    float sum = __fadd_rn(__fadd_rn(__fadd_rn(E, W), S), N);
-    sum = __fadd_rn(__fadd_rn(__fadd_rn(__fmaf_rn(sum, 2.0f, NE), NW), SE), SW);
-    float filter = (float)((double)sum / 12.0);
-    float rc;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(contrast));
-    filter = fminf(__fmul_rn(fabsf(__fadd_rn(filter, -M)), rc), 1.0f);
-    b = __fmul_rn(__fadd_rn(3.0f, -__fadd_rn(filter, filter)), __fmul_rn(filter, filter));
-
-    const float hor = __fadd_rn(__fmaf_rn(fabsf(__fadd_rn(__fadd_rn(N, S), -__fadd_rn(M, M))), 2.0f,
-                                          fabsf(__fadd_rn(__fadd_rn(NE, SE), -__fadd_rn(E, E)))),
-                                fabsf(__fadd_rn(__fadd_rn(NW, SW), -__fadd_rn(W, W))));
-    const float ver = __fadd_rn(__fmaf_rn(fabsf(__fadd_rn(__fadd_rn(E, W), -__fadd_rn(M, M))), 2.0f,
-                                          fabsf(__fadd_rn(__fadd_rn(NE, NW), -__fadd_rn(N, N)))),
-                                fabsf(__fadd_rn(__fadd_rn(SE, SW), -__fadd_rn(S, S))));
-    dx = 0;
-    dy = 0;
-    if (hor >= ver) dy = fabsf(__fadd_rn(N, -M)) >= fabsf(__fadd_rn(S, -M)) ? -1 : 1;
-    else            dx = fabsf(__fadd_rn(E, -M)) >= fabsf(__fadd_rn(W, -M)) ? 1 : -1;
-    return true;
-}
-
-__device__ __forceinline__ unsigned int fx_blend(unsigned int centre, unsigned int nb, float b) {
-    const float omb = __fadd_rn(1.0f, -b);
-    const float r = __fmaf_rn(omb, (float)(centre & 255u), __fmul_rn(b, (float)(nb & 255u)));
-    const float g = __fmaf_rn(omb, (float)((centre >> 8) & 255u), __fmul_rn(b, (float)((nb >> 8) & 255u)));
-    const float bl = __fmaf_rn(omb, (float)((centre >> 16) & 255u), __fmul_rn(b, (float)((nb >> 16) & 255u)));
-    return fx_pack(r, g, bl);
-}
+#include "fxaa_core.cuh"
 
 /* ------------------------------------------------------------------ plain shared-memory kernel */
 

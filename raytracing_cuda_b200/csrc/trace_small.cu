@@ -14,10 +14,9 @@
  *   - rt_trace_small_kernel: persistent CTAs (4 per SM); the LBVH nodes, leaf records,
  *     materials and planes are staged into shared memory once per CTA (the reference keeps
  *     its 133 objects in __constant__, kernel.cu:14).  After that every WARP is autonomous:
- *     it fetches work from an atomic counter -- whole 16x8 tiles (four 8x4 patches) for the
- *     first 5/8 of the frame, single patches for the rest so that the tail stays short --
- *     with the next fetch in flight while a whole tile is traced; no CTA barrier in the
- *     loop.  Every pixel tests just its bin's list for its primary ray;
+ *     it fetches single 8x4 patches from an atomic counter, walking the frame bottom-up so
+ *     that the expensive patches (mirror chains in the lower half) start early and the frame
+ *     ends on cheap sky patches; no CTA barrier in the loop.  Every pixel tests just its bin's list for its primary ray;
  *   - shadow and mirror rays traverse the shared-memory LBVH with a per-thread stack of
  *     16-bit entries in shared memory (no local memory, sentinel at the bottom), child links
  *     pre-scaled to byte offsets so that a node fetch is one add + four LDS.128.
@@ -442,17 +441,18 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     float4* s_mats = s_prims + 3 * n;
     float4* s_planes = s_mats + 2 * sc.n_objects;
 
-    /* Work units over the tiles in raster order (screen-tile shards: over the list of the pre-pass, count in
-     * tile_counter[RS_CNT_TILES], its own cache line):
-     * fetch k < n_whole is the whole tile k (4 patches); beyond that fetch k is the single patch
-     * q = 4 n_whole + (k - n_whole).  While a whole tile is traced the next fetch is already in flight; in the
-     * single-patch part nothing is reserved ahead, so the tail of the frame is one patch.  (Ordering the tiles
-     * by an estimated cost class -- mirror surfaces first -- was measured and did not beat this: the long
-     * patches are few and not predictable from the candidate lists.) */
-    const bool listed = f.n_shards > 1;          /* whole frames walk all tiles in raster order, no list */
+    /* Work units: single 8x4 patches, fetched one at a time from an atomic counter, nothing reserved ahead.
+     * Unit k is patch 3 - k % 4 of tile n_tiles - 1 - k / 4: the frame is walked from its LAST tile to its
+     * first (screen-tile shards: the list of the pre-pass, count in tile_counter[RS_CNT_TILES], its own cache
+     * line).  Patch costs are heavy-tailed (mean 11 us, p99 52 us, max 111 us in the Island view at 1080p,
+     * tools/costmap_probe.py) and the expensive ones -- mirror chains between the sea and the icy slopes -- sit
+     * in the lower half of the frame, the sky at the top costs 2 us a patch: bottom-up, the long patches
+     * start early and the frame ends on cheap ones.  Measured against the alternatives:
+     * whole tiles first / patches last in raster order +5..13 % time, reserving one unit ahead +7 % (a warp
+     * inside a 100 us patch sits on its reserved unit), whole tiles over the expensive part +60 %. */
+    const bool listed = f.n_shards > 1;          /* whole frames walk all tiles, no list */
     const unsigned int n_tiles = listed ? __ldcg(tile_counter + RS_CNT_TILES) : n_tiles_all;
-    const unsigned int n_whole = (unsigned int)(((unsigned long long)n_tiles * 5u) / 8u);
-    const unsigned int n_fetch = n_whole + RT_SMALL_PATCHES * (n_tiles - n_whole);
+    const unsigned int n_fetch = RT_SMALL_PATCHES * n_tiles;
     unsigned int u0 = 0;
     if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
 
@@ -498,44 +498,43 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 #endif
     while (u0 < n_fetch) {
-#ifdef RS_SINGLES_FIRST
-        /* experiment: the last 3/8 of the raster (singles) first, the whole tiles of the first 5/8 after them */
-        const unsigned int n_single = RT_SMALL_PATCHES * (n_tiles - n_whole);
-        const bool whole = u0 >= n_single;
-        const unsigned int slot = whole ? u0 - n_single : n_whole + u0 / RT_SMALL_PATCHES;
-        const int p_first = whole ? 0 : (int)(u0 % RT_SMALL_PATCHES);
-#else
-        const bool whole = u0 < n_whole;
-        const unsigned int slot = whole ? u0 : (RT_SMALL_PATCHES * n_whole + (u0 - n_whole)) / RT_SMALL_PATCHES;
-        const int p_first = whole ? 0 : (int)((u0 - n_whole) % RT_SMALL_PATCHES);
-#endif
-        const int p_count = whole ? RT_SMALL_PATCHES : 1;
+        const unsigned int slot = n_tiles - 1u - u0 / RT_SMALL_PATCHES;
+        const int p = (int)(RT_SMALL_PATCHES - 1u - u0 % RT_SMALL_PATCHES);
         const unsigned int tile = listed ? __ldg(work_list + slot) : slot;
         const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
         const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
         const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
         const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
-        unsigned int u1 = 0;
-        if (whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);      /* lands while the tile is traced */
         s_list[warp][lane] = entry;
         __syncwarp();
-
-#pragma unroll 1
-        for (int p = p_first; p < p_first + p_count; p++) {
+        {
             const int x = x0 + (p % (RT_SMALL_TILE_W / 8)) * 8 + (lane & 7);
             const int y = y0 + (p / (RT_SMALL_TILE_W / 8)) * 4 + (lane >> 3);
+#ifdef RS_COSTMAP
+            unsigned long long cm_t0;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cm_t0));
+#endif
             if (x < f.imgw && y < f.imgh && rt_shard_needs(f, x, y)) {
                 image[y * f.imgw + x] = rt_trace_pixel<RtSmallScene<COUNT>, COUNT>(acc, f, x, y, s_pending,
                                                                                   RT_SMALL_THREADS, tid, hit_ids, pc);
                 n_pixels++;
             }
+#ifdef RS_COSTMAP
+            __syncwarp();   /* debug variant: ns spent on the patch, stored over the hit id of its first pixel */
+            if (lane == 0 && hit_ids && x < f.imgw && y < f.imgh) {
+                unsigned long long cm_t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cm_t1));
+                hit_ids[y * f.imgw + x] = (int)(cm_t1 - cm_t0);
+            }
+#endif
         }
         __syncwarp();                            /* the list is rewritten for the next unit */
 #ifdef RS_TIMELINE
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
-        tl_units += (unsigned long long)p_count;
+        tl_units++;
 #endif
-        if (!whole && lane == 0) u1 = atomicAdd(tile_counter, 1u);
+        unsigned int u1 = 0;
+        if (lane == 0) u1 = atomicAdd(tile_counter, 1u);
         u0 = __shfl_sync(0xffffffffu, u1, 0);
     }
     if (COUNT) {
@@ -609,7 +608,8 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     if (sharded)
         rt_worklist_scan_kernel<<<1, 1024, 0, stream>>>(bin_need, bins_x, bins, tiles_x, work_list, tile_counter + RS_CNT_TILES);
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
-    if (grid > (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (tiles + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
+    const int units = tiles * RT_SMALL_PATCHES;
+    if (grid > (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
     if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear);
     else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear);
     return cudaGetLastError();
