@@ -67,7 +67,8 @@ enum {
     RT_OPT_TRACE_IMPL = 5,  /* 0 = auto: shared-memory tracer when the scene fits (<= ~165 primitives), else the HBM-resident LBVH tracer; 1 = always the HBM tracer; 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests) */
     RT_OPT_BUILDER = 6,     /* hierarchy over the Morton-sorted primitives: 0 = auto (PLOC up to 1024 primitives, Karras above), 1 = Karras, 2 = PLOC */
     RT_OPT_FORCE_RADIX = 7, /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
-    RT_OPT_N = 8
+    RT_OPT_ORDER = 8,       /* work order of the shared-memory tracer on whole frames: 0 = most expensive patches of the previous frame of this size first (default; first frame bottom-up), 1 = always bottom-up.  Scheduling only: identical pixels */
+    RT_OPT_N = 9
 };
 
 /* One frame's uniforms: what launchKernel receives by value / as small host arrays. */

@@ -16,6 +16,7 @@ RT_OK, RT_ERR_CUDA, RT_ERR_ARG, RT_ERR_STATE, RT_ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 (RT_OPT_TRAVERSAL, RT_OPT_COUNTERS, RT_OPT_FXAA_IMPL, RT_OPT_TIMING, RT_OPT_SKY_ALL4, RT_OPT_TRACE_IMPL) = range(6)
 RT_OPT_BUILDER = 6
 RT_OPT_FORCE_RADIX = 7
+RT_OPT_ORDER = 8
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
                  "plane_tests", "sky_lookups", "shadow_skipped")

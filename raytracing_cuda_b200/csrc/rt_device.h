@@ -40,6 +40,8 @@
 #define RT_STACK_SIZE 64
 /* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 48*n must fit 16 bits */
 #define RT_SMALL_MAX_PRIMS 288
+#define RT_SMALL_ORDER_CLASSES 8      /* patch cost classes of the tracer's order history */
+#define RT_SMALL_ORDER_HEAD 32        /* uints before the class lists of an order buffer: [0..7] class counts */
 #ifndef RT_SMALL_DYN_SMEM_MAX
 #define RT_SMALL_DYN_SMEM_MAX (24 * 1024)
 #endif

@@ -299,6 +299,11 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 #define RT_SMALL_TILE_W 16
 #define RT_SMALL_TILE_H 8
 #define RT_SMALL_PATCHES 4            /* 8x4 patches per tile */
+#define RS_CLASSES RT_SMALL_ORDER_CLASSES   /* class c = floor(log2(cycles / 1024)), clamped */
+#ifndef RS_AHEAD_CLASSES
+#define RS_AHEAD_CLASSES 4            /* classes 0..3 (< 8 us): the next unit is fetched ahead */
+#endif
+#define RS_ORDER_HEAD RT_SMALL_ORDER_HEAD              /* uints before the class lists of an order buffer: [0..7] class counts */
 #define RS_CNT_TILES 32               /* tile_counter[]: [0] next fetch, [1] finished warps, [32] listed tiles */
 #define RT_SMALL_LIST 32              /* ushorts per bin list: [0] = count (0xFFFF: too many, traverse), [1..31] */
 /* candidate lists are kept per BIN of RT_SMALL_BIN_W x RT_SMALL_BIN_H pixels (whole tiles) */
@@ -425,7 +430,8 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
                       int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters,
                       unsigned int* __restrict__ tile_counter, const unsigned short* __restrict__ tile_lists,
                       int tiles_x, unsigned int n_tiles_all, int bins_x,
-                      const unsigned int* __restrict__ work_list, int force_linear) {
+                      const unsigned int* __restrict__ work_list, int force_linear,
+                      const unsigned int* order_r, unsigned int* order_w) {
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
@@ -453,6 +459,26 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     const bool listed = f.n_shards > 1;          /* whole frames walk all tiles, no list */
     const unsigned int n_tiles = listed ? __ldcg(tile_counter + RS_CNT_TILES) : n_tiles_all;
     const unsigned int n_fetch = RT_SMALL_PATCHES * n_tiles;
+    /* Order history (whole frames, order_r != NULL): the previous frame of this size filed every patch under
+     * the class of its measured cost (order_w below); this frame walks the classes from the most expensive
+     * down, so the longest patches start first wherever they are on the screen.  Lane j < 8 keeps the running
+     * end of class 7 - j in walking order.  Results do not depend on the order; a history that does not
+     * hold every patch exactly once (first frame, other size) is not used. */
+    unsigned int cls_end = 0;
+    bool by_cost = false;
+    if (order_r) {
+        unsigned int c = lane < RS_CLASSES ? __ldcg(order_r + (RS_CLASSES - 1 - lane)) : 0u;
+#pragma unroll
+        for (int o = 1; o < RS_CLASSES; o <<= 1) {
+            const unsigned int v = __shfl_up_sync(0xffffffffu, c, o);
+            if (lane >= o) c += v;
+        }
+        cls_end = c;
+        by_cost = __shfl_sync(0xffffffffu, c, RS_CLASSES - 1) == n_fetch;
+#ifdef RS_DIAG_NO_READ
+        by_cost = false;
+#endif
+    }
     unsigned int u0 = 0;
     if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
 
@@ -498,9 +524,23 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 #endif
     while (u0 < n_fetch) {
-        const unsigned int slot = n_tiles - 1u - u0 / RT_SMALL_PATCHES;
-        const int p = (int)(RT_SMALL_PATCHES - 1u - u0 % RT_SMALL_PATCHES);
+        unsigned int q = n_fetch - 1u - u0;       /* patch id = 4 * tile slot + patch */
+        unsigned int u1 = 0;
+        bool ahead = false;
+        if (by_cost) {
+            const int j = __popc(__ballot_sync(0xffffffffu, lane < RS_CLASSES && u0 >= cls_end));
+            const unsigned int start = __shfl_sync(0xffffffffu, cls_end, (j + 31) & 31);   /* end of the class before */
+            const unsigned int idx = u0 - (j ? start : 0u);
+            q = __ldcg(order_r + RS_ORDER_HEAD + (size_t)(RS_CLASSES - 1 - j) * n_fetch + idx);
+            /* a patch of the cheap classes (< 8 us last time): fetch the next unit while this one is traced.
+             * Never for the expensive ones -- a warp inside a 100 us patch must not sit on another unit. */
+            ahead = j >= RS_CLASSES - RS_AHEAD_CLASSES;
+            if (ahead && lane == 0) u1 = atomicAdd(tile_counter, 1u);
+        }
+        const unsigned int slot = q / RT_SMALL_PATCHES;
+        const int p = (int)(q % RT_SMALL_PATCHES);
         const unsigned int tile = listed ? __ldg(work_list + slot) : slot;
+        const unsigned int unit_t0 = (unsigned int)clock();
         const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
         const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
         const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
@@ -533,8 +573,15 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
         tl_units++;
 #endif
-        unsigned int u1 = 0;
-        if (lane == 0) u1 = atomicAdd(tile_counter, 1u);
+        if (lane == 0) {
+            if (!ahead) u1 = atomicAdd(tile_counter, 1u);
+            if (order_w) {                       /* file the patch under its cost class for the next frame */
+                const unsigned int k = ((unsigned int)clock() - unit_t0) >> 10;
+                const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
+                const unsigned int at = atomicAdd(order_w + cls, 1u);
+                order_w[RS_ORDER_HEAD + (size_t)cls * n_fetch + at] = q;
+            }
+        }
         u0 = __shfl_sync(0xffffffffu, u1, 0);
     }
     if (COUNT) {
@@ -557,6 +604,8 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
             tile_counter[0] = 0;
             tile_counter[1] = 0;
             tile_counter[RS_CNT_TILES] = 0;
+            if (order_r)                         /* this buffer is written by the next frame */
+                for (int c = 0; c < RS_CLASSES; c++) ((unsigned int*)order_r)[c] = 0;
         }
     }
 }
@@ -589,10 +638,22 @@ extern "C" size_t rt_trace_small_list_bytes(int imgw, int imgh) {
     return bins * RT_SMALL_LIST * sizeof(unsigned short) + tiles * sizeof(unsigned int) + ((bins + 3) & ~(size_t)3);   /* bin lists + work list + need masks */
 }
 
+extern "C" size_t rt_trace_small_patches(int imgw, int imgh) {
+    return (size_t)RT_SMALL_PATCHES * ((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
+}
+
+/* bytes of ONE order buffer (class counts + RS_CLASSES lists of all patches) for a frame of this size */
+extern "C" size_t rt_trace_small_order_bytes(int imgw, int imgh) {
+    const size_t tiles = (size_t)((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
+    return sizeof(unsigned int) * (RS_ORDER_HEAD + (size_t)RS_CLASSES * RT_SMALL_PATCHES * tiles);
+}
+
 extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image,
                                              int* hit_ids, RtCountersDev* counters, unsigned int* tile_counter,
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
+                                             const unsigned int* order_r, unsigned int* order_w,
                                              cudaStream_t stream) {
+    /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel */
     const size_t smem = rt_trace_small_smem_bytes(sc->n_bvh_prims, sc->n_objects, sc->n_planes);
     const int tiles_x = (f->imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W;
     const int tiles = tiles_x * ((f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
@@ -610,7 +671,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     const int units = tiles * RT_SMALL_PATCHES;
     if (grid > (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
-    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear);
-    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear);
+    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, sharded ? nullptr : order_r, sharded ? nullptr : order_w);
+    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, sharded ? nullptr : order_r, sharded ? nullptr : order_w);
     return cudaGetLastError();
 }

@@ -195,6 +195,38 @@ def test_shared_memory_tracer_poses_shards_and_subsets():
         assert (img_a == img_b).all(), subset
 
 
+def test_order_history_changes_scheduling_only():
+    """Whole frames of the shared-memory tracer are walked most-expensive-patch-first using the costs the
+    previous frame of the same size measured (RT_OPT_ORDER 0).  The frames must not depend on it: same pixels
+    and ids as the plain bottom-up walk, across repeated frames, a moving camera, changing sizes and an
+    interleaved sharded frame."""
+    r = gu.renderer()
+    s = rt.Scene()
+    for (view, hours, w, h) in ((5, 14.0, 1920, 1080), (6, 18.0, 641, 359), (5, 1.0, 33, 9)):
+        f = s.configure(view=view, hours=hours, imgw=w, imgh=h, alias=True)
+        r.set_option(_lib.RT_OPT_ORDER, 1)
+        img_ref, ids_ref = gu.render(r, s, f)
+        r.set_option(_lib.RT_OPT_ORDER, 0)
+        for k in range(4):
+            if k == 2:   # a sharded frame and a frame of another size in between
+                gu.render(r, s, f, shard=rt.make_shard(2, 1, 64, 32))
+                gu.render(r, s, s.configure(view=view, hours=hours, imgw=160, imgh=90, alias=True))
+                f = s.configure(view=view, hours=hours, imgw=w, imgh=h, alias=True)
+            img, ids = gu.render(r, s, f)
+            assert (ids == ids_ref).all(), (w, h, k)
+            assert (img == img_ref).all(), (w, h, k)
+    # the history follows a moving camera
+    for k in range(6):
+        s.set_pose((-56.0 + 20 * k, 2.2 + 3 * k, 72.0 - 10 * k), 309.0 - 15 * k, -7.0 + 2 * k)
+        f = s.frame(640, 360)
+        r.set_option(_lib.RT_OPT_ORDER, 0)
+        img, ids = gu.render(r, s, f)
+        r.set_option(_lib.RT_OPT_ORDER, 1)
+        img_ref, ids_ref = gu.render(r, s, f)
+        r.set_option(_lib.RT_OPT_ORDER, 0)
+        assert (ids == ids_ref).all() and (img == img_ref).all(), k
+
+
 # ---------------------------------------------------------------- legacy boundary
 
 def _legacy_call(lib, out_ptr, s, f, sky):

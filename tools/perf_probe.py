@@ -15,6 +15,7 @@ w, h = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (1920, 108
 r = rt.Renderer(0)
 r.set_sky(rt.synthetic_sky(2048, 1024))
 s = rt.Scene()
+r.set_option(_lib.RT_OPT_ORDER, int(os.environ.get("RTB_ORDER", "0")))
 out = torch.empty(w * h, dtype=torch.int32, device="cuda")
 for view in (5, 6):
     for tod in ("afternoon", "night"):

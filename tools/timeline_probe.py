@@ -9,7 +9,7 @@ import numpy as np, torch
 import raytracing_cuda_b200 as rt
 from raytracing_cuda_b200 import _lib
 for (w, h, view) in ((1280, 720, 6), (1920, 1080, 5), (3840, 2160, 6)):
-    r = rt.Renderer(0); r.set_sky(rt.synthetic_sky(2048, 1024))
+    r = rt.Renderer(0); r.set_option(_lib.RT_OPT_ORDER, int(os.environ.get('RTB_ORDER', '0'))); r.set_sky(rt.synthetic_sky(2048, 1024))
     s = rt.Scene(); f = s.configure(view=view, hours=14.0, imgw=w, imgh=h, alias=True); r.set_scene(s.objects, s.lights)
     out = torch.empty(w * h, dtype=torch.int32, device="cuda"); ids = torch.zeros(w * h, dtype=torch.int32, device="cuda")
     for _ in range(3): r.render(f, out, hit_ids=ids)
