@@ -25,12 +25,28 @@ template <bool BRUTE, bool COUNT>
 struct RtGlobalScene {
     const RtSceneDev& sc;
     __device__ __forceinline__ RtGlobalScene(const RtSceneDev& s) : sc(s) {}
+#ifdef RT_NODEMAP
+    unsigned int dbg[3] = {0, 0, 0};   /* debug variant: node tests of primary / bounce / shadow rays */
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, RtLocalCounters& cnt) {
+        const unsigned int before = cnt.node_tests;
+        const RtHit h = rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
+        dbg[depth ? 1 : 0] += cnt.node_tests - before;
+        return h;
+    }
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
+        const unsigned int before = cnt.node_tests;
+        const bool r = rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
+        dbg[2] += cnt.node_tests - before;
+        return r;
+    }
+#else
     __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int, RtLocalCounters& cnt) {
         return rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
     }
     __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
         return rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
     }
+#endif
     __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) { return rt_hit_normal<BRUTE>(sc, h, P); }
     __device__ __forceinline__ void material(unsigned int idx, float4& m0, float4& m1) {
         m0 = __ldg(sc.mats + 2 * idx);
@@ -53,8 +69,22 @@ rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restric
 
     RtPixelCounters pc = {{0, 0, 0, 0}, 0, 0, 0, 0};
     RtGlobalScene<BRUTE, COUNT> acc(sc);
+#ifdef RT_TIMEMAP
+    unsigned long long tm_t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_t0));
+#endif
     image[y * f.imgw + x] = rt_trace_pixel<RtGlobalScene<BRUTE, COUNT>, COUNT>(acc, f, x, y, s_pending, RT_TRACE_THREADS,
                                                                               threadIdx.x, hit_ids, pc);
+#ifdef RT_TIMEMAP
+    if (hit_ids) {   /* debug variant: ns this pixel's thread took */
+        unsigned long long tm_t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_t1));
+        hit_ids[y * f.imgw + x] = (int)(tm_t1 - tm_t0);
+    }
+#endif
+#ifdef RT_NODEMAP
+    if (COUNT && hit_ids) hit_ids[y * f.imgw + x] = (int)acc.dbg[RT_NODEMAP];   /* debug variant: per-pixel node tests of one ray kind */
+#endif
     if (COUNT) rt_flush_counters(pc, 1u, counters);
 }
 

@@ -62,12 +62,10 @@ __device__ __forceinline__ bool rt_test_record(const float4* __restrict__ rec, c
  * ANY = true : returns true at the first non-emissive primitive with t < tmax
  *              (reference kernel.cu:188-193; negative t counts, as in the reference).
  */
-template <bool ANY, bool COUNT>
-__device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o, const vec3& d, RtHit& best,
-                                            float tmax, RtLocalCounters& cnt) {
+template <bool ANY, bool COUNT, bool ROBUST>
+__device__ __forceinline__ bool rt_traverse_loop(const RtSceneDev& sc, const RtRayBox& rb, const vec3& o, const vec3& d,
+                                                 RtHit& best, float tmax, RtLocalCounters& cnt) {
     int node = sc.root;
-    if (node == RT_NODE_SENTINEL) return false;
-    const RtRayBox rb = rt_ray_box(o, d);
     int stack[RT_STACK_SIZE];
     int sp = 0;
     const float4* __restrict__ nodes = sc.nodes;
@@ -79,8 +77,10 @@ __device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o,
             const float4 n3 = __ldg(nodes + 4 * node + 3);
             const float lim = ANY ? tmax : fmaxf(best.t, 0.0f);
             float t0, t1;
-            const bool h0 = rt_slab(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0);
-            const bool h1 = rt_slab(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1);
+            const bool h0 = ROBUST ? rt_slab_robust(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0)
+                                   : rt_slab(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0);
+            const bool h1 = ROBUST ? rt_slab_robust(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1)
+                                   : rt_slab(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1);
             if (COUNT) cnt.node_tests += 2;
             int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
             if (h0 && h1) {
@@ -107,6 +107,16 @@ __device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o,
         node = stack[--sp];
     }
     return false;
+}
+
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o, const vec3& d, RtHit& best,
+                                            float tmax, RtLocalCounters& cnt) {
+    if (sc.root == RT_NODE_SENTINEL) return false;
+    const RtRayBox rb = rt_ray_box(o, d);
+    /* rays with a near-zero direction component: per-axis slack (intersect.cuh) */
+    if (rb.slack > RT_ROBUST_SLACK) return rt_traverse_loop<ANY, COUNT, true>(sc, rb, o, d, best, tmax, cnt);
+    return rt_traverse_loop<ANY, COUNT, false>(sc, rb, o, d, best, tmax, cnt);
 }
 
 /* closest hit over planes + BVH (BRUTE: over all records in original order) */
