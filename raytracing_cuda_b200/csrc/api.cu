@@ -86,7 +86,8 @@ struct rt_context {
     RtCountersDev* d_counters = nullptr;
     unsigned int* d_order = nullptr;         /* two order-history buffers of the persistent tracer (trace_small.cu) */
     size_t cap_order = 0;                    /* uints */
-    int order_w = 0, order_h = 0, order_cur = 0;   /* frame size the history belongs to; buffer holding it */
+    int order_key[7] = {0, 0, 0, 0, 0, 0, 0};   /* frame size + shard the history belongs to */
+    int order_cur = 0;                       /* buffer holding it */
     unsigned short* d_tile_lists = nullptr;  /* per-tile primary candidate lists (trace_small.cu) */
     size_t cap_tile_lists = 0;
     unsigned int* d_tile_counter = nullptr;  /* [0] next tile, [1] finished CTAs (persistent tracer; self re-arming) */
@@ -162,7 +163,7 @@ bool make_fxaa_tmap(rt_context* ctx, const unsigned int* img, int w, int h) {
 }
 
 int run_fxaa(rt_context* ctx, const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh) {
-    const bool shard_ok = !sh || sh->n_shards <= 1 || (sh->tile_w == 64 && sh->tile_h == 32);
+    const bool shard_ok = !sh || sh->n_shards <= 1 || (sh->tile_w % 64 == 0 && sh->tile_h % 32 == 0);
     const bool tma_ok = ctx->opt[RT_OPT_FXAA_IMPL] == 0 && (w % 4 == 0) && (((uintptr_t)in) % 16 == 0) && shard_ok &&
                         make_fxaa_tmap(ctx, in, w, h);
     if (tma_ok) RT_CHECK(ctx, rt_launch_fxaa_tma(&ctx->tmap, in, out, w, h, sh, ctx->n_sm, ctx->stream));
@@ -458,23 +459,24 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
             RT_CHECK(ctx, regrow(&ctx->d_tile_lists, need));
             ctx->cap_tile_lists = need;
         }
-        /* Order history: whole frames file every patch under its measured cost; the next frame of the same
-         * size starts with the most expensive ones (frame-to-frame coherence of an interactive renderer; the
-         * first frame of a size walks bottom-up).  Pure scheduling: pixels do not depend on it. */
+        /* Order history: a frame files every patch under its measured cost; the next frame of the same size
+         * and shard starts with the most expensive ones (frame-to-frame coherence of an interactive renderer;
+         * the first frame of a kind walks bottom-up).  Pure scheduling: pixels do not depend on it. */
         const unsigned int* ord_r = nullptr;
         unsigned int* ord_w = nullptr;
         /* Only where the order matters: below ~32 patches per resident warp (1080p: 14).  A 4K frame (55 per
          * warp) balances by itself bottom-up, and there filing + indirection cost 3 % (measured). */
         const size_t ob = rt_trace_small_order_bytes(frame->imgw, frame->imgh) / sizeof(unsigned int);
         const size_t patches = rt_trace_small_patches(frame->imgw, frame->imgh);
-        if (f.n_shards <= 1 && ctx->opt[RT_OPT_ORDER] == 0 && patches < (size_t)32 * ctx->n_sm * 32) {
+        const int key[7] = {frame->imgw, frame->imgh, f.n_shards, f.shard_id, f.tile_w, f.tile_h, f.stride};
+        if (ctx->opt[RT_OPT_ORDER] == 0 && patches / (size_t)f.n_shards < (size_t)32 * ctx->n_sm * 32) {
             if (2 * ob > ctx->cap_order) {
                 RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
                 RT_CHECK(ctx, regrow(&ctx->d_order, 2 * ob));
                 ctx->cap_order = 2 * ob;
-                ctx->order_w = ctx->order_h = 0;
+                ctx->order_key[0] = 0;
             }
-            const bool same = ctx->order_w == frame->imgw && ctx->order_h == frame->imgh;
+            const bool same = memcmp(ctx->order_key, key, sizeof(key)) == 0;
             if (!same) {
                 RT_CHECK(ctx, cudaMemsetAsync(ctx->d_order, 0, RT_SMALL_ORDER_HEAD * sizeof(unsigned int), ctx->stream));
                 RT_CHECK(ctx, cudaMemsetAsync(ctx->d_order + ob, 0, RT_SMALL_ORDER_HEAD * sizeof(unsigned int), ctx->stream));
@@ -482,8 +484,7 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
             if (same) ord_r = ctx->d_order + (size_t)ctx->order_cur * ob;
             ord_w = ctx->d_order + (size_t)(1 - ctx->order_cur) * ob;
             ctx->order_cur = 1 - ctx->order_cur;
-            ctx->order_w = frame->imgw;
-            ctx->order_h = frame->imgh;
+            memcpy(ctx->order_key, key, sizeof(key));
         }
         RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,

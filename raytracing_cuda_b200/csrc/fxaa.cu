@@ -113,29 +113,38 @@ __device__ __forceinline__ void fx_tma_load_2d(void* dst, const CUtensorMap* map
         : "memory");
 }
 
-/* tile k of this shard -> pixel origin.  Whole frame: row-major over tiles. */
+/* FXAA tile k of this shard -> tile coordinates.  Whole frame: row-major over the 64x32 FXAA tiles.  Shards: the
+ * shard's screen tiles are kx x ky FXAA tiles each (tile_w = 64 kx, tile_h = 32 ky); slot k is FXAA tile
+ * k % (kx ky) of the shard's screen tile k / (kx ky).  Returns false past the last slot; a slot outside the
+ * frame comes back with tx >= tiles_x (the caller skips it). */
 __device__ __forceinline__ bool fx_tile_origin(int k, int tiles_x, int tiles_y, int n_shards, int shard_id,
-                                               int stride, int& tx, int& ty) {
+                                               int stride, int kx, int ky, int& tx, int& ty) {
     if (n_shards <= 1) {
         if (k >= tiles_x * tiles_y) return false;
         tx = k % tiles_x;
         ty = k / tiles_x;
         return true;
     }
-    /* slots: per tile row, ceil(tiles_x / n) candidates i = i0 + m*n with i0 = (shard - j*stride) mod n */
-    const int per_row = (tiles_x + n_shards - 1) / n_shards;
-    if (k >= per_row * tiles_y) return false;
-    ty = k / per_row;
-    const int m = k % per_row;
-    int i0 = (shard_id - ty * stride) % n_shards;
+    /* screen-tile slots: per tile row, ceil(stiles_x / n) candidates i = i0 + m*n with i0 = (shard - j*stride) mod n */
+    const int stiles_x = (tiles_x + kx - 1) / kx, stiles_y = (tiles_y + ky - 1) / ky;
+    const int per_row = (stiles_x + n_shards - 1) / n_shards;
+    const int sub = k % (kx * ky), ks = k / (kx * ky);
+    if (ks >= per_row * stiles_y) return false;
+    const int sty = ks / per_row;
+    const int m = ks % per_row;
+    int i0 = (shard_id - sty * stride) % n_shards;
     if (i0 < 0) i0 += n_shards;
-    tx = i0 + m * n_shards;
-    return true;   /* caller checks tx < tiles_x */
+    const int stx = i0 + m * n_shards;
+    tx = stx * kx + sub % kx;
+    ty = sty * ky + sub / kx;
+    if (stx >= stiles_x || ty >= tiles_y) tx = tiles_x;
+    return true;
 }
 
 __global__ void __launch_bounds__(FX_THREADS)
 rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned int* __restrict__ in,
-                   unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride) {
+                   unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride, int kx,
+                   int ky) {
     __shared__ __align__(128) unsigned int s_px[2][FX_STAGE_WORDS];
     __shared__ float s_lum[FX_BOXH][FX_BOXW];
     __shared__ __align__(8) uint64_t s_bar[2];
@@ -151,7 +160,7 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
 
     int k = blockIdx.x;
     int tx, ty;
-    bool have = fx_tile_origin(k, tiles_x, tiles_y, n_shards, shard_id, stride, tx, ty);
+    bool have = fx_tile_origin(k, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, tx, ty);
     if (tid == 0 && have && tx < tiles_x) {
         fx_mbar_expect_tx(&s_bar[0], FX_STAGE_BYTES);
         fx_tma_load_2d(&s_px[0][0], &in_map, tx * FX_TW - FX_HALO_X, ty * FX_TH - 1, &s_bar[0]);
@@ -161,7 +170,7 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
     while (have) {
         const int kn = k + gridDim.x;
         int ntx, nty;
-        const bool have_next = fx_tile_origin(kn, tiles_x, tiles_y, n_shards, shard_id, stride, ntx, nty);
+        const bool have_next = fx_tile_origin(kn, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, ntx, nty);
         if (tid == 0 && have_next && ntx < tiles_x) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             fx_mbar_expect_tx(&s_bar[stage ^ 1], FX_STAGE_BYTES);
@@ -227,7 +236,8 @@ __global__ void rt_pack_tiles_kernel(const unsigned int* __restrict__ frame, uns
     const int tx = i0 + m * n_shards;
     if (tx >= tiles_x) return;
     unsigned int* dst = packed + (size_t)slot * tile_w * tile_h;
-    for (int i = threadIdx.x; i < tile_w * tile_h; i += blockDim.x) {
+    /* blockIdx.y strides over the tile so that large tiles still fill the GPU */
+    for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < tile_w * tile_h; i += blockDim.x * gridDim.y) {
         const int lx = i % tile_w, ly = i / tile_w;
         const int x = tx * tile_w + lx, y = ty * tile_h + ly;
         if (x < w && y < h) {
@@ -251,16 +261,18 @@ extern "C" cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int*
 extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out,
                                           int w, int h, const rt_shard* sh, int n_sm, cudaStream_t stream) {
     const int tiles_x = (w + FX_TW - 1) / FX_TW, tiles_y = (h + FX_TH - 1) / FX_TH;
-    int n = 1, id = 0, st = 0;
+    int n = 1, id = 0, st = 0, kx = 1, ky = 1;
     int slots = tiles_x * tiles_y;
-    if (sh && sh->n_shards > 1) {
+    if (sh && sh->n_shards > 1) {     /* screen tiles that are whole multiples of the 64x32 FXAA tile */
         n = sh->n_shards; id = sh->shard_id; st = sh->stride;
-        slots = ((tiles_x + n - 1) / n) * tiles_y;
+        kx = sh->tile_w / FX_TW; ky = sh->tile_h / FX_TH;
+        const int stiles_x = (tiles_x + kx - 1) / kx, stiles_y = (tiles_y + ky - 1) / ky;
+        slots = ((stiles_x + n - 1) / n) * stiles_y * kx * ky;
     }
     int grid = n_sm * 4;
     if (grid > slots) grid = slots;
     if (grid < 1) grid = 1;
-    rt_fxaa_tma_kernel<<<grid, FX_THREADS, 0, stream>>>(*map, in, out, w, h, n, id, st);
+    rt_fxaa_tma_kernel<<<grid, FX_THREADS, 0, stream>>>(*map, in, out, w, h, n, id, st, kx, ky);
     return cudaGetLastError();
 }
 
@@ -279,7 +291,9 @@ extern "C" cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned 
                                             const rt_shard* sh, int unpack, cudaStream_t stream) {
     const int tiles_x = (w + sh->tile_w - 1) / sh->tile_w, tiles_y = (h + sh->tile_h - 1) / sh->tile_h;
     const int per_row = (tiles_x + sh->n_shards - 1) / sh->n_shards;
-    rt_pack_tiles_kernel<<<per_row * tiles_y, 256, 0, stream>>>(frame, packed, w, h, sh->tile_w, sh->tile_h,
+    int chunks = (sh->tile_w * sh->tile_h + 2047) / 2048;
+    if (chunks > 64) chunks = 64;
+    rt_pack_tiles_kernel<<<dim3(per_row * tiles_y, chunks, 1), 256, 0, stream>>>(frame, packed, w, h, sh->tile_w, sh->tile_h,
                                                                 sh->n_shards, sh->shard_id, sh->stride, unpack);
     return cudaGetLastError();
 }

@@ -10,7 +10,7 @@
  *     dropped -- they fail `det < 0.001`, kernel.cu:104) into a short, index-ordered
  *     candidate list in HBM (ballot compaction, 64 B per bin).  For a screen-tile shard it
  *     also marks which 16x8 work tiles hold pixels to trace (own tiles + 1-pixel FXAA apron)
- *     and rt_worklist_scan_kernel turns the marks into a compact, raster-ordered work list;
+ *     and appends them to a compact work list;
  *   - rt_trace_small_kernel: persistent CTAs (4 per SM); the LBVH nodes, leaf records,
  *     materials and planes are staged into shared memory once per CTA (the reference keeps
  *     its 133 objects in __constant__, kernel.cu:14).  After that every WARP is autonomous:
@@ -300,9 +300,6 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 #define RT_SMALL_TILE_H 8
 #define RT_SMALL_PATCHES 4            /* 8x4 patches per tile */
 #define RS_CLASSES RT_SMALL_ORDER_CLASSES   /* class c = floor(log2(cycles / 1024)), clamped */
-#ifndef RS_AHEAD_CLASSES
-#define RS_AHEAD_CLASSES 4            /* classes 0..3 (< 8 us): the next unit is fetched ahead */
-#endif
 #define RS_ORDER_HEAD RT_SMALL_ORDER_HEAD              /* uints before the class lists of an order buffer: [0..7] class counts */
 #define RS_CNT_TILES 32               /* tile_counter[]: [0] next fetch, [1] finished warps, [32] listed tiles */
 #define RT_SMALL_LIST 32              /* ushorts per bin list: [0] = count (0xFFFF: too many, traverse), [1..31] */
@@ -318,8 +315,9 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 
 __global__ void __launch_bounds__(256)
 rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
-                     int n_tiles, unsigned char* __restrict__ bin_need, int work_tiles_x,
-                     int work_tiles_y) {   /* tiles_x, n_tiles count BINS here; bin_need = NULL for whole frames */
+                     int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
+                     int work_tiles_x, int work_tiles_y) {
+    /* tiles_x, n_tiles count BINS here; work_list = NULL for whole frames */
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (tile >= n_tiles) return;
@@ -342,7 +340,12 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
                 if ((tx + ty * f.stride) % f.n_shards == f.shard_id) { need = true; break; }
     }
     const unsigned int need_mask = __ballot_sync(0xffffffffu, need);
-    if (bin_need && lane == 0) bin_need[tile] = (unsigned char)need_mask;   /* sharded frames: input of the list scan */
+    if (work_list && need_mask) {                /* sharded frames: append this bin's work tiles to the list */
+        unsigned int at = 0;
+        if (lane == 0) at = atomicAdd(work_count, (unsigned int)__popc(need_mask));
+        at = __shfl_sync(0xffffffffu, at, 0) + __popc(need_mask & ((1u << lane) - 1u));
+        if (need) work_list[at] = (unsigned int)(wy * work_tiles_x + wx);
+    }
     if (need_mask == 0u) return;                 /* nothing of this bin is traced here: no list needed either */
     const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
     const int prims_off = 64 * n_nodes;
@@ -376,50 +379,6 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
     }
     if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
 
-}
-
-/* Sharded frames: the work tiles this shard has to trace, as a compact list in bin-raster order (deterministic:
- * positions come from a block scan, not from atomics).  One CTA; thread t owns a contiguous run of bins. */
-__global__ void __launch_bounds__(1024)
-rt_worklist_scan_kernel(const unsigned char* __restrict__ bin_need, int bins_x, int n_bins, int work_tiles_x,
-                        unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count) {
-    __shared__ unsigned int s_warp[32];
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int per = (n_bins + 1023) / 1024;
-    const int b0 = min(t * per, n_bins), b1 = min(b0 + per, n_bins);
-    unsigned int mine = 0;
-    for (int b = b0; b < b1; b++) mine += (unsigned int)__popc((unsigned int)bin_need[b]);
-    unsigned int s = mine;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const unsigned int v = __shfl_up_sync(0xffffffffu, s, o);
-        if (lane >= o) s += v;
-    }
-    if (lane == 31) s_warp[warp] = s;
-    __syncthreads();
-    if (warp == 0) {
-        unsigned int ws = s_warp[lane];
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned int v = __shfl_up_sync(0xffffffffu, ws, o);
-            if (lane >= o) ws += v;
-        }
-        s_warp[lane] = ws;
-    }
-    __syncthreads();
-    unsigned int at = (warp ? s_warp[warp - 1] : 0u) + s - mine;
-    for (int b = b0; b < b1; b++) {
-        unsigned int m = (unsigned int)bin_need[b];
-        const int bby = b / bins_x, bbx = b - bby * bins_x;
-        while (m) {
-            const int l = __ffs(m) - 1;
-            m &= m - 1;
-            const int wx = bbx * (RT_SMALL_BIN_W / RT_SMALL_TILE_W) + l % (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
-            const int wy = bby * (RT_SMALL_BIN_H / RT_SMALL_TILE_H) + l / (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
-            work_list[at++] = (unsigned int)(wy * work_tiles_x + wx);
-        }
-    }
-    if (t == 1023) *work_count = s_warp[31];
 }
 
 /* ---------------------------------------------------------------- tracer */
@@ -524,22 +483,19 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 #endif
     while (u0 < n_fetch) {
-        unsigned int q = n_fetch - 1u - u0;       /* patch id = 4 * tile slot + patch */
-        unsigned int u1 = 0;
-        bool ahead = false;
+        unsigned int q = 0;                       /* patch id = 4 * tile + patch */
         if (by_cost) {
             const int j = __popc(__ballot_sync(0xffffffffu, lane < RS_CLASSES && u0 >= cls_end));
             const unsigned int start = __shfl_sync(0xffffffffu, cls_end, (j + 31) & 31);   /* end of the class before */
             const unsigned int idx = u0 - (j ? start : 0u);
             q = __ldcg(order_r + RS_ORDER_HEAD + (size_t)(RS_CLASSES - 1 - j) * n_fetch + idx);
-            /* a patch of the cheap classes (< 8 us last time): fetch the next unit while this one is traced.
-             * Never for the expensive ones -- a warp inside a 100 us patch must not sit on another unit. */
-            ahead = j >= RS_CLASSES - RS_AHEAD_CLASSES;
-            if (ahead && lane == 0) u1 = atomicAdd(tile_counter, 1u);
         }
-        const unsigned int slot = q / RT_SMALL_PATCHES;
+        else {
+            const unsigned int slot = n_tiles - 1u - u0 / RT_SMALL_PATCHES;
+            q = RT_SMALL_PATCHES * (listed ? __ldg(work_list + slot) : slot) + (RT_SMALL_PATCHES - 1u - u0 % RT_SMALL_PATCHES);
+        }
+        const unsigned int tile = q / RT_SMALL_PATCHES;
         const int p = (int)(q % RT_SMALL_PATCHES);
-        const unsigned int tile = listed ? __ldg(work_list + slot) : slot;
         const unsigned int unit_t0 = (unsigned int)clock();
         const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
         const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
@@ -573,8 +529,9 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
         tl_units++;
 #endif
+        unsigned int u1 = 0;
         if (lane == 0) {
-            if (!ahead) u1 = atomicAdd(tile_counter, 1u);
+            u1 = atomicAdd(tile_counter, 1u);
             if (order_w) {                       /* file the patch under its cost class for the next frame */
                 const unsigned int k = ((unsigned int)clock() - unit_t0) >> 10;
                 const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
@@ -635,7 +592,7 @@ extern "C" cudaError_t rt_trace_small_init(void) {
 extern "C" size_t rt_trace_small_list_bytes(int imgw, int imgh) {
     const size_t bins = (size_t)((imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W) * ((imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
     const size_t tiles = (size_t)((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
-    return bins * RT_SMALL_LIST * sizeof(unsigned short) + tiles * sizeof(unsigned int) + ((bins + 3) & ~(size_t)3);   /* bin lists + work list + need masks */
+    return bins * RT_SMALL_LIST * sizeof(unsigned short) + tiles * sizeof(unsigned int);   /* bin lists + work list */
 }
 
 extern "C" size_t rt_trace_small_patches(int imgw, int imgh) {
@@ -660,18 +617,15 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const int bins_x = (f->imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W;
     const int bins = bins_x * ((f->imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
     const int tiles_y = (f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H;
-    /* behind the bin lists: the work list and the per-bin need masks of sharded frames */
+    /* behind the bin lists: the work list of sharded frames (filled by the pre-pass) */
     unsigned int* work_list = (unsigned int*)(tile_lists + (size_t)bins * RT_SMALL_LIST);
-    unsigned char* bin_need = (unsigned char*)(work_list + tiles);
     const bool sharded = f->n_shards > 1;
-    rt_cull_tiles_kernel<<<(bins + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, bins_x, bins, sharded ? bin_need : nullptr,
-                                                            tiles_x, tiles_y);
-    if (sharded)
-        rt_worklist_scan_kernel<<<1, 1024, 0, stream>>>(bin_need, bins_x, bins, tiles_x, work_list, tile_counter + RS_CNT_TILES);
+    rt_cull_tiles_kernel<<<(bins + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, bins_x, bins, sharded ? work_list : nullptr,
+                                                            tile_counter + RS_CNT_TILES, tiles_x, tiles_y);
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     const int units = tiles * RT_SMALL_PATCHES;
     if (grid > (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
-    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, sharded ? nullptr : order_r, sharded ? nullptr : order_w);
-    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, sharded ? nullptr : order_r, sharded ? nullptr : order_w);
+    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, order_r, order_w);
+    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, order_r, order_w);
     return cudaGetLastError();
 }

@@ -89,7 +89,7 @@ def test_fxaa_tma_equals_smem_equals_oracle(shape):
 # ---------------------------------------------------------------- shards (multi-GPU partition on one GPU)
 
 @pytest.mark.parametrize("n", [2, 3, 4, 8])
-@pytest.mark.parametrize("tile", [(64, 32), (48, 24)])
+@pytest.mark.parametrize("tile", [(64, 32), (48, 24), (128, 64), (192, 32), (256, 128)])
 def test_shard_count_invariance(n, tile):
     """N logical shards on one GPU: every pixel owned exactly once and the composite equals the
     unsharded frame bit for bit (1-pixel apron -> no halo exchange)."""
@@ -106,6 +106,8 @@ def test_shard_count_invariance(n, tile):
     for k in range(n):
         sh = rt.make_shard(n, k, tile[0], tile[1])
         part = r.render_to_host(f, shard=sh)
+        again = r.render_to_host(f, shard=sh)     # second frame of the same shard: walked in cost order
+        assert (again == part).all()
         yy, xx = np.mgrid[0:h, 0:w]
         mine = ((xx // tile[0]) + (yy // tile[1]) * sh.stride) % n == k
         owned += mine
