@@ -139,6 +139,30 @@ int  rt_pack_tiles(rt_context* ctx, const unsigned int* frame_dev, int imgw, int
 int  rt_unpack_tiles(rt_context* ctx, const unsigned int* packed_dev, int imgw, int imgh,
                      const rt_shard* shard, unsigned int* frame_dev);
 
+/* Peer frame: ONE frame over N GPUs (one process each) without a gather.  The owner allocates n_buffers frames
+ * of n_pixels and exports a 64-byte handle (cudaIpc); the other processes open it and pass
+ * rt_peer_frame_buffer(pf, seq) as `out_dev` of their sharded rt_render, so the FXAA / copy kernel stores the
+ * rank's tiles straight into the owner's memory over NVLink ("peer-mapped stores straight into
+ * GPU 0's framebuffer").  Hand-shake, all asynchronous on the contexts' streams, frame numbers seq = 1, 2, ...:
+ *   every rank:  rt_peer_frame_acquire(seq)  -- buffer seq % n_buffers is free (frame seq - n_buffers released)
+ *                rt_render(..., shard, rt_peer_frame_buffer(pf, seq), ...)
+ *                rt_peer_frame_signal(rank, seq)
+ *   the owner:   rt_peer_frame_wait(n_ranks, seq) ... use the frame ... rt_peer_frame_release(seq)
+ * A wait that is not satisfied within 2 s sets the error word (rt_peer_frame_error) instead of hanging. */
+#define RT_PEER_HANDLE_BYTES 64
+typedef struct rt_peer_frame rt_peer_frame;
+int  rt_peer_frame_create(rt_context* ctx, size_t n_pixels, int n_buffers, rt_peer_frame** out,
+                          unsigned char* handle /* RT_PEER_HANDLE_BYTES */);
+int  rt_peer_frame_open(rt_context* ctx, const unsigned char* handle, size_t n_pixels, int n_buffers,
+                        rt_peer_frame** out);
+unsigned int* rt_peer_frame_buffer(rt_peer_frame* pf, unsigned int seq);
+int  rt_peer_frame_acquire(rt_context* ctx, rt_peer_frame* pf, unsigned int seq);
+int  rt_peer_frame_signal(rt_context* ctx, rt_peer_frame* pf, int rank, unsigned int seq);
+int  rt_peer_frame_wait(rt_context* ctx, rt_peer_frame* pf, int n_ranks, unsigned int seq);
+int  rt_peer_frame_release(rt_context* ctx, rt_peer_frame* pf, unsigned int seq);
+int  rt_peer_frame_error(rt_context* ctx, rt_peer_frame* pf, unsigned int* err);
+int  rt_peer_frame_close(rt_context* ctx, rt_peer_frame* pf);
+
 int  rt_synchronize(rt_context* ctx);
 int  rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]);
 /* ms of the last frame's kernels (RT_OPT_TIMING=1): [0]=trace [1]=fxaa [2]=bvh build/refit */

@@ -17,6 +17,7 @@ RT_OK, RT_ERR_CUDA, RT_ERR_ARG, RT_ERR_STATE, RT_ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 RT_OPT_BUILDER = 6
 RT_OPT_FORCE_RADIX = 7
 RT_OPT_ORDER = 8
+RT_PEER_HANDLE_BYTES = 64
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
                  "plane_tests", "sky_lookups", "shadow_skipped")
@@ -43,6 +44,15 @@ SIGNATURES = {
     "rt_shard_tile_count": (C.c_int, [C.POINTER(Shard), C.c_int, C.c_int]),
     "rt_pack_tiles": (C.c_int, [_P, _P, C.c_int, C.c_int, C.POINTER(Shard), _P]),
     "rt_unpack_tiles": (C.c_int, [_P, _P, C.c_int, C.c_int, C.POINTER(Shard), _P]),
+    "rt_peer_frame_create": (C.c_int, [_P, C.c_size_t, C.c_int, C.POINTER(_P), _u8p]),
+    "rt_peer_frame_open": (C.c_int, [_P, _u8p, C.c_size_t, C.c_int, C.POINTER(_P)]),
+    "rt_peer_frame_buffer": (_P, [_P, C.c_uint]),
+    "rt_peer_frame_acquire": (C.c_int, [_P, _P, C.c_uint]),
+    "rt_peer_frame_signal": (C.c_int, [_P, _P, C.c_int, C.c_uint]),
+    "rt_peer_frame_wait": (C.c_int, [_P, _P, C.c_int, C.c_uint]),
+    "rt_peer_frame_release": (C.c_int, [_P, _P, C.c_uint]),
+    "rt_peer_frame_error": (C.c_int, [_P, _P, C.POINTER(C.c_uint)]),
+    "rt_peer_frame_close": (C.c_int, [_P, _P]),
     "rt_synchronize": (C.c_int, [_P]),
     "rt_get_counters": (C.c_int, [_P, C.POINTER(C.c_ulonglong)]),
     "rt_get_timings": (C.c_int, [_P, C.POINTER(C.c_float)]),

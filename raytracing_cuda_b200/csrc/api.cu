@@ -51,6 +51,10 @@ cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int
 cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned int* packed, int w, int h, const rt_shard* sh,
                                  int unpack, cudaStream_t stream);
 cudaError_t rt_launch_ffma_peak(int n_sm, cudaStream_t stream, float* ms, double* flops);
+cudaError_t rt_launch_peer_signal(unsigned int* flags, int rank, unsigned int seq, cudaStream_t stream);
+cudaError_t rt_launch_peer_wait(unsigned int* flags, int n_ranks, unsigned int seq, cudaStream_t stream);
+cudaError_t rt_launch_peer_release(unsigned int* flags, unsigned int seq, cudaStream_t stream);
+cudaError_t rt_launch_peer_acquire(unsigned int* flags, unsigned int seq, cudaStream_t stream);
 }
 
 struct rt_context {
@@ -540,6 +544,109 @@ int rt_shard_tile_count(const rt_shard* sh, int imgw, int imgh) {
     if (!sh || sh->n_shards < 1 || sh->tile_w < 1 || sh->tile_h < 1) return -1;
     const int tiles_x = (imgw + sh->tile_w - 1) / sh->tile_w, tiles_y = (imgh + sh->tile_h - 1) / sh->tile_h;
     return ((tiles_x + sh->n_shards - 1) / sh->n_shards) * tiles_y;   /* slots, some may be empty */
+}
+
+/* ---------------------------------------------------------------- peer frame (peer.cu) */
+
+#define RT_PEER_FLAG_UINTS 256
+
+struct rt_peer_frame {
+    unsigned int* base = nullptr;    /* n_buffers frames, then the flag block */
+    size_t n_pixels = 0;
+    int n_buffers = 0;
+    bool owner = false;
+    unsigned int* flags() const { return base + (size_t)n_buffers * n_pixels; }
+};
+
+int rt_peer_frame_create(rt_context* ctx, size_t n_pixels, int n_buffers, rt_peer_frame** out, unsigned char* handle) {
+    if (!ctx || !out || !handle || n_pixels == 0 || n_buffers < 1 || n_buffers > 4) return RT_ERR_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == RT_PEER_HANDLE_BYTES, "handle size");
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    rt_peer_frame* pf = new rt_peer_frame;
+    pf->n_pixels = n_pixels;
+    pf->n_buffers = n_buffers;
+    pf->owner = true;
+    const size_t bytes = ((size_t)n_buffers * n_pixels + RT_PEER_FLAG_UINTS) * sizeof(unsigned int);
+    cudaError_t e = cudaMalloc((void**)&pf->base, bytes);
+    if (e == cudaSuccess) e = cudaMemset(pf->base, 0, bytes);
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, pf->base);
+    if (e != cudaSuccess) {
+        if (pf->base) cudaFree(pf->base);
+        delete pf;
+        RT_CHECK(ctx, e);
+    }
+    memcpy(handle, &h, sizeof(h));
+    *out = pf;
+    return RT_OK;
+}
+
+int rt_peer_frame_open(rt_context* ctx, const unsigned char* handle, size_t n_pixels, int n_buffers,
+                       rt_peer_frame** out) {
+    if (!ctx || !out || !handle || n_pixels == 0 || n_buffers < 1 || n_buffers > 4) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    void* p = nullptr;
+    RT_CHECK(ctx, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    rt_peer_frame* pf = new rt_peer_frame;
+    pf->base = (unsigned int*)p;
+    pf->n_pixels = n_pixels;
+    pf->n_buffers = n_buffers;
+    pf->owner = false;
+    *out = pf;
+    return RT_OK;
+}
+
+unsigned int* rt_peer_frame_buffer(rt_peer_frame* pf, unsigned int seq) {
+    if (!pf) return nullptr;
+    return pf->base + (size_t)(seq % (unsigned int)pf->n_buffers) * pf->n_pixels;
+}
+
+int rt_peer_frame_acquire(rt_context* ctx, rt_peer_frame* pf, unsigned int seq) {
+    if (!ctx || !pf) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_peer_acquire(pf->flags(), seq - (unsigned int)pf->n_buffers, ctx->stream));
+    return RT_OK;
+}
+
+int rt_peer_frame_signal(rt_context* ctx, rt_peer_frame* pf, int rank, unsigned int seq) {
+    if (!ctx || !pf || rank < 0 || rank >= 16) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_peer_signal(pf->flags(), rank, seq, ctx->stream));
+    return RT_OK;
+}
+
+int rt_peer_frame_wait(rt_context* ctx, rt_peer_frame* pf, int n_ranks, unsigned int seq) {
+    if (!ctx || !pf || n_ranks < 1 || n_ranks > 16) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_peer_wait(pf->flags(), n_ranks, seq, ctx->stream));
+    return RT_OK;
+}
+
+int rt_peer_frame_release(rt_context* ctx, rt_peer_frame* pf, unsigned int seq) {
+    if (!ctx || !pf) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_peer_release(pf->flags(), seq, ctx->stream));
+    return RT_OK;
+}
+
+int rt_peer_frame_error(rt_context* ctx, rt_peer_frame* pf, unsigned int* err) {
+    if (!ctx || !pf || !err) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    RT_CHECK(ctx, cudaMemcpy(err, pf->flags() + 136, sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    return RT_OK;
+}
+
+int rt_peer_frame_close(rt_context* ctx, rt_peer_frame* pf) {
+    if (!ctx || !pf) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (pf->owner) cudaFree(pf->base);
+    else cudaIpcCloseMemHandle(pf->base);
+    delete pf;
+    return RT_OK;
 }
 
 int rt_pack_tiles(rt_context* ctx, const unsigned int* frame_dev, int imgw, int imgh, const rt_shard* sh,

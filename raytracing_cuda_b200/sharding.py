@@ -101,3 +101,73 @@ def gather_frame(dist, rank, world, packed_local, make_like, unpack, dst=0):
     if rank == dst:
         for k in range(world):
             unpack(bufs[k], k)
+
+
+class PeerFrame:
+    """One frame over N GPUs without a gather (rt_peer_frame_*, csrc/peer.cu): the owner rank allocates the
+    frame and exports a cudaIpc handle, the other ranks open it, and every rank's sharded render stores its
+    tiles straight into the owner's memory over NVLink.  `exchange(handle_or_None) -> handle` moves the 64
+    handle bytes from the owner to everybody (torch.distributed.broadcast_object_list, a pipe, ...).
+
+        pf = PeerFrame(renderer, rank, world, w * h, exchange)
+        for seq in 1, 2, ...:
+            pf.render(frame, shard, seq)        # acquire buffer, trace + FXAA into it, signal
+            if rank == pf.owner_rank:
+                pf.wait(seq); ...use pf.tensor(seq)...; pf.release(seq)
+    """
+
+    def __init__(self, renderer, rank, world, n_pixels, exchange, owner_rank=0, n_buffers=2):
+        import ctypes as C
+
+        from . import _lib
+        self.r, self.rank, self.world, self.owner_rank = renderer, rank, world, owner_rank
+        self.n_pixels, self.n_buffers = int(n_pixels), int(n_buffers)
+        self._lib = renderer._lib
+        self._pf = C.c_void_p()
+        buf = (C.c_ubyte * _lib.RT_PEER_HANDLE_BYTES)()
+        if rank == owner_rank:
+            renderer._check(self._lib.rt_peer_frame_create(renderer._h, self.n_pixels, self.n_buffers,
+                                                           C.byref(self._pf), buf), "rt_peer_frame_create")
+            exchange(bytes(buf))
+        else:
+            handle = exchange(None)
+            buf = (C.c_ubyte * _lib.RT_PEER_HANDLE_BYTES).from_buffer_copy(handle)
+            renderer._check(self._lib.rt_peer_frame_open(renderer._h, buf, self.n_pixels, self.n_buffers,
+                                                         C.byref(self._pf)), "rt_peer_frame_open")
+
+    def buffer_ptr(self, seq):
+        return self._lib.rt_peer_frame_buffer(self._pf, seq)
+
+    def render(self, frame, shard, seq, hit_ids=None):
+        r = self.r
+        r._check(self._lib.rt_peer_frame_acquire(r._h, self._pf, seq), "rt_peer_frame_acquire")
+        r.render(frame, self.buffer_ptr(seq), hit_ids=hit_ids, shard=shard)
+        r._check(self._lib.rt_peer_frame_signal(r._h, self._pf, self.rank, seq), "rt_peer_frame_signal")
+
+    def wait(self, seq):
+        self.r._check(self._lib.rt_peer_frame_wait(self.r._h, self._pf, self.world, seq), "rt_peer_frame_wait")
+
+    def release(self, seq):
+        self.r._check(self._lib.rt_peer_frame_release(self.r._h, self._pf, seq), "rt_peer_frame_release")
+
+    def error(self):
+        import ctypes as C
+        e = C.c_uint(0)
+        self.r._check(self._lib.rt_peer_frame_error(self.r._h, self._pf, C.byref(e)), "rt_peer_frame_error")
+        return e.value
+
+    def tensor(self, seq):
+        """The frame buffer of `seq` as a torch int32 tensor (valid in this process; on the owner it is local)."""
+        import torch
+
+        class _Wrap:
+            pass
+        w = _Wrap()
+        w.__cuda_array_interface__ = {"shape": (self.n_pixels,), "typestr": "<i4", "data": (self.buffer_ptr(seq), False),
+                                      "version": 2}
+        return torch.as_tensor(w, device="cuda")
+
+    def close(self):
+        if self._pf:
+            self.r._check(self._lib.rt_peer_frame_close(self.r._h, self._pf), "rt_peer_frame_close")
+            self._pf = None

@@ -7,7 +7,7 @@ import pytest
 import gpu_util as gu
 import oracle_util as ou
 import raytracing_cuda_b200 as rt
-from raytracing_cuda_b200 import _lib
+from raytracing_cuda_b200 import _lib, sharding
 
 pytestmark = pytest.mark.gpu
 
@@ -123,6 +123,46 @@ def test_shard_count_invariance(n, tile):
     assert (owned == 1).all()
     assert (comp == full).all()
     assert (gu.to_host_u32(frame_dev, (h, w)) == full).all()
+
+
+def test_peer_frame_two_processes():
+    """The gather-free composite (rt_peer_frame_*): a second PROCESS opens the owner's frame through its cudaIpc
+    handle and stores shard 1 of 2 straight into it while this process renders shard 0; after the flag
+    hand-shake the owner's buffer equals the unsharded frame.  Three frames over two buffers, so the third
+    acquire has to wait for the first release."""
+    import subprocess
+    import sys
+    import torch
+    w, h, tw, th = 640, 360, 128, 64
+    r = rt.Renderer(0)
+    r.set_sky(rt.synthetic_sky(256, 128))
+    s = rt.Scene()
+    f = s.configure(view=5, hours=18.0, imgw=w, imgh=h, alias=True)
+    r.set_scene(s.objects, s.lights)
+    full = torch.zeros(w * h, dtype=torch.int32, device="cuda")
+    r.render(f, full)
+    r.synchronize()
+    got = {}
+    pf = sharding.PeerFrame(r, 0, 2, w * h, lambda hb: got.setdefault("h", hb))
+    child = subprocess.Popen([sys.executable, os.path.join(os.path.dirname(__file__), "peer_child.py"), got["h"].hex(),
+                              str(w), str(h), str(tw), str(th)], stdout=subprocess.PIPE, text=True)
+    try:
+        assert child.stdout.readline().strip() == "ready"     # its waits give up after 2 s: start together
+        shard = rt.make_shard(2, 0, tw, th)
+        for seq in (1, 2, 3):
+            pf.render(f, shard, seq)
+            pf.wait(seq)
+            r.synchronize()
+            assert pf.error() == 0
+            assert torch.equal(pf.tensor(seq), full), seq
+            pf.tensor(seq).zero_()
+            pf.release(seq)
+        assert child.wait(timeout=120) == 0
+    finally:
+        if child.poll() is None:
+            child.kill()
+        pf.close()
+        r.close()
 
 
 # ---------------------------------------------------------------- LBVH builder

@@ -143,16 +143,67 @@ def config2(r, sky, fh):
               "frames_per_s": world * 4e3 / tot_ms})
 
 
+COMPOSE = os.environ.get("RTB_COMPOSE", "peer")     # peer: stores into rank 0's frame over NVLink; gather: NCCL
+_peer = {"pf": None, "seq": 0}
+
+
+def peer_frame(r, n_pixels):
+    if _peer["pf"] is None:
+        def exchange(hb):
+            box = [hb]
+            dist.broadcast_object_list(box, src=0)
+            return box[0]
+        _peer["pf"] = sharding.PeerFrame(r, rank, world, n_pixels, exchange)
+    return _peer["pf"]
+
+
 def sharded_frame(r, f, w, h, out_local, packed, frame0, bufs, shard):
-    """Trace + FXAA this rank's tiles, pack them, gather to rank 0, composite there."""
-    r.render(f, out_local, shard=shard)
+    """Trace + FXAA this rank's tiles and composite the frame on rank 0: either every rank's FXAA kernel stores
+    into rank 0's peer-mapped frame (flag hand-shake, no collective), or pack + NCCL gather + unpack."""
     if world == 1:
+        r.render(f, out_local, shard=shard)
         return
+    if COMPOSE == "peer":
+        pf = peer_frame(r, w * h)
+        _peer["seq"] += 1
+        seq = _peer["seq"]
+        pf.render(f, shard, seq)
+        if rank == 0:
+            pf.wait(seq)
+            _peer["last"] = seq
+            pf.release(seq)          # (a consumer would use pf.tensor(seq) between wait and release)
+        return
+    r.render(f, out_local, shard=shard)
     r.pack_tiles(out_local, w, h, shard, packed)
     dist.gather(packed, gather_list=bufs if rank == 0 else None, dst=0)
     if rank == 0:
         for k in range(world):
             r.unpack_tiles(bufs[k], w, h, rt.make_shard(world, k, shard.tile_w, shard.tile_h), frame0)
+
+
+def composite_ok(r, f, w, h, out_local, packed, frame0, bufs, shard, full):
+    """One more composited frame, compared on rank 0 with the unsharded frame `full`."""
+    if world == 1:
+        return True
+    if COMPOSE == "peer":
+        pf = peer_frame(r, w * h)
+        _peer["seq"] += 1
+        seq = _peer["seq"]
+        pf.tensor(seq).zero_() if rank == 0 else None
+        barrier()
+        pf.render(f, shard, seq)
+        ok = True
+        if rank == 0:
+            pf.wait(seq)
+            torch.cuda.synchronize()
+            ok = bool(torch.equal(pf.tensor(seq), full)) and pf.error() == 0
+            pf.release(seq)
+        barrier()
+        return ok
+    frame0.zero_()
+    sharded_frame(r, f, w, h, out_local, packed, frame0, bufs, shard)
+    torch.cuda.synchronize()
+    return bool((frame0 == full).all().item()) if rank == 0 else True
 
 
 def config3(r, sky, fh):
@@ -174,14 +225,12 @@ def config3(r, sky, fh):
         rays, _ = count_rays(r, f, out_local)              # whole frame, unsharded
         full = out_local.clone()
         ms = timed(lambda: sharded_frame(r, f, w, h, out_local, packed, frame0, bufs, shard), 20)
-        ok = True
-        if world > 1 and rank == 0:
-            ok = bool((frame0 == full).all().item())
+        ok = composite_ok(r, f, w, h, out_local, packed, frame0, bufs, shard, full)
         res.append({"sea_level": sea, "ms_per_frame": ms, "Mrays_per_s": rays / ms / 1e3, "rays_per_frame": rays,
                     "composite_equals_single_gpu_frame": ok})
     ms_all = sum(x["ms_per_frame"] for x in res)
     emit(fh, {"config": 3, "what": "Mountains 3840x2160 FXAA on, sea-level sweep; one frame tile-sharded (%dx%d tiles, " % (TILE_W, TILE_H) +
-              "1-px apron) over the ranks, packed tiles gathered to rank 0 over NCCL and composited",
+              "1-px apron) over the ranks; composite on rank 0 by " + ("peer stores over NVLink (no collective)" if COMPOSE == "peer" else "pack + NCCL gather + unpack"),
               "sweep": res, "frames_per_s": len(res) * 1e3 / ms_all,
               "Mrays_per_s": sum(x["rays_per_frame"] for x in res) / ms_all / 1e3})
 
@@ -217,9 +266,7 @@ def config4(r, sky, fh):
     rays, c = count_rays(r, f, out_local)
     full = out_local.clone()
     ms = timed(lambda: sharded_frame(r, f, w, h, out_local, packed, frame0, bufs, shard), 20)
-    ok = True
-    if world > 1 and rank == 0:
-        ok = bool((frame0 == full).all().item())
+    ok = composite_ok(r, f, w, h, out_local, packed, frame0, bufs, shard, full)
     # cross-check against the brute-force kernel (reference arithmetic over all primitives) on a small frame
     fs = s.frame(96, 54)
     fs.alias = 0
@@ -227,8 +274,8 @@ def config4(r, sky, fh):
     r.set_option(_lib.RT_OPT_TRAVERSAL, 1)
     b, ib = r.render_to_host(fs, want_ids=True)
     r.set_option(_lib.RT_OPT_TRAVERSAL, 0)
-    emit(fh, {"config": 4, "what": "synthetic terrain %dx%d cells = %d objects, 3840x2160 FXAA on, tile-sharded + gather"
-              % (cells, cells, len(objs)), "ms_per_frame": ms, "frames_per_s": 1e3 / ms, "Mrays_per_s": rays / ms / 1e3,
+    emit(fh, {"config": 4, "what": "synthetic terrain %dx%d cells = %d objects, 3840x2160 FXAA on, tile-sharded, composite on rank 0 (%s)"
+              % (cells, cells, len(objs), COMPOSE), "ms_per_frame": ms, "frames_per_s": 1e3 / ms, "Mrays_per_s": rays / ms / 1e3,
               "rays_per_frame": rays, "lbvh_build_ms_first": build_ms, "lbvh_build_ms": build_ms_warm,
               "node_tests_per_pixel": c["node_tests"] / (w * h), "tri_tests_per_pixel": c["tri_tests"] / (w * h),
               "composite_equals_single_gpu_frame": ok,
