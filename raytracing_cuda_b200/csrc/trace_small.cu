@@ -43,8 +43,6 @@
 struct RtSmallShared {
     unsigned int base;       /* shared address of the staged nodes (leaf records follow them) */
     unsigned int stack0;     /* shared address of this thread's stack column */
-    const float4* mats;
-    const float4* planes;
     const unsigned short* list;   /* primary candidates of the current tile: [0] count, then leaf byte offsets */
     int root, n_prims, n_planes, prims_off;
     bool deep;               /* hierarchy deeper than RT_SMALL_STACK: secondary rays loop linearly instead */
@@ -84,6 +82,7 @@ __device__ __forceinline__ bool rs_test_record(unsigned int rec, const vec3& o, 
     return rt_hit_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t);
 }
 
+#define RS_PLANES_BYTES 512            /* 16 planes x 2 float4, in front of the staged nodes */
 #define RS_STACK_END (-32768)          /* sentinel at the bottom of every per-thread stack (never a valid link) */
 
 /* LBVH traversal in shared memory.  Returns true on an occluder (ANY).  The per-thread stack holds
@@ -145,7 +144,7 @@ struct RtSmallScene {
 
     __device__ __forceinline__ void planes_closest(const vec3& o, const vec3& d, RtHit& best, RtLocalCounters& cnt) {
         for (int p = 0; p < s.n_planes; p++) {
-            const float4 q0 = s.planes[2 * p], q1 = s.planes[2 * p + 1];
+            const float4 q0 = rs_lds128(s.base - RS_PLANES_BYTES + 32 * p), q1 = rs_lds128(s.base - RS_PLANES_BYTES + 32 * p + 16);
             float t;
             if (COUNT) cnt.plane_tests++;
             if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t)) rt_consider(best, t, __float_as_uint(q0.w), ~p);
@@ -185,7 +184,7 @@ struct RtSmallScene {
     }
     __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
         for (int p = 0; p < s.n_planes; p++) {
-            const float4 q0 = s.planes[2 * p], q1 = s.planes[2 * p + 1];
+            const float4 q0 = rs_lds128(s.base - RS_PLANES_BYTES + 32 * p), q1 = rs_lds128(s.base - RS_PLANES_BYTES + 32 * p + 16);
             float t;
             if (COUNT) cnt.plane_tests++;
             if (__float_as_uint(q0.w) & RT_TAG_EMISSIVE) continue;
@@ -205,14 +204,15 @@ struct RtSmallScene {
         return false;
     }
     __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) {
-        if (h.slot < 0) return f4xyz(s.planes[2 * (~h.slot) + 1]);
+        if (h.slot < 0) return f4xyz(rs_lds128(s.base - RS_PLANES_BYTES + 32 * (~h.slot) + 16));
         const unsigned int rec = s.base + (unsigned int)h.slot;
         if (h.tag & RT_TAG_SPHERE) return rt_normalize(rt_sub(P, f4xyz(rs_lds128(rec))));
         return rt_normalize(rt_cross(f4xyz(rs_lds128(rec + 16)), f4xyz(rs_lds128(rec + 32))));
     }
     __device__ __forceinline__ void material(unsigned int idx, float4& m0, float4& m1) {
-        m0 = s.mats[2 * idx];
-        m1 = s.mats[2 * idx + 1];
+        const unsigned int a = s.base + (unsigned int)(s.prims_off + 48 * s.n_prims) + 32u * idx;
+        m0 = rs_lds128(a);
+        m1 = rs_lds128(a + 16);
     }
 };
 
@@ -401,10 +401,12 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     const int warp = tid >> 5, lane = tid & 31;
     const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
     const int prims_off = 64 * n_nodes;
-    float4* s_nodes = (float4*)smem;
+    /* dynamic shared memory: [planes, RS_PLANES_BYTES][nodes][leaf records][materials]; everything is addressed
+     * relative to the nodes (`base`), the planes at a fixed negative offset */
+    float4* s_planes = (float4*)smem;
+    float4* s_nodes = (float4*)(smem + RS_PLANES_BYTES);
     float4* s_prims = s_nodes + 4 * n_nodes;
     float4* s_mats = s_prims + 3 * n;
-    float4* s_planes = s_mats + 2 * sc.n_objects;
 
     /* Work units: single 8x4 patches, fetched one at a time from an atomic counter, nothing reserved ahead.
      * Unit k is patch 3 - k % 4 of tile n_tiles - 1 - k / 4: the frame is walked from its LAST tile to its
@@ -459,14 +461,12 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     RtSmallShared sh;
     /* opaque moves: keep the two addresses in registers instead of re-deriving them in the hot loops */
     {
-        const unsigned int b0 = (unsigned int)__cvta_generic_to_shared(smem);
+        const unsigned int b0 = (unsigned int)__cvta_generic_to_shared(smem) + RS_PLANES_BYTES;
         const unsigned int s0 = (unsigned int)__cvta_generic_to_shared(s_stack + tid);
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.base) : "r"(b0));
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.stack0) : "r"(s0));
     }
     sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;   /* one slot above the top is scratch (rs_store) */
-    sh.mats = s_mats;
-    sh.planes = s_planes;
     sh.list = s_list[warp];
     sh.n_prims = n;
     sh.n_planes = sc.n_planes;
@@ -570,7 +570,8 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
 /* dynamic shared memory: the staged scene */
 extern "C" size_t rt_trace_small_smem_bytes(int n_bvh_prims, int n_objects, int n_planes) {
     const size_t n_nodes = n_bvh_prims > 1 ? (size_t)n_bvh_prims - 1 : 0;
-    return 16 * (4 * n_nodes + 3 * (size_t)n_bvh_prims + 2 * (size_t)n_objects + 2 * (size_t)n_planes);
+    (void)n_planes;   /* the plane block has a fixed size (<= 16 planes) */
+    return RS_PLANES_BYTES + 16 * (4 * n_nodes + 3 * (size_t)n_bvh_prims + 2 * (size_t)n_objects);
 }
 
 /* scenes this kernel accepts: link offsets (64 n_nodes + 48 n) must fit the 16-bit stack entries */
