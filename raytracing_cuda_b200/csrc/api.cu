@@ -36,7 +36,7 @@ cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned 
 cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
-                                  unsigned int* order_w, cudaStream_t stream);
+                                  unsigned int* order_w, int after_own_post, cudaStream_t stream);
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
@@ -88,6 +88,9 @@ struct rt_context {
     int* d_stage_ids = nullptr;
     size_t cap_stage = 0;
     RtCountersDev* d_counters = nullptr;
+    /* every write to the scene buffers completes before the last kernel enqueued by rt_render runs to its end:
+     * the next frame's binning pre-pass may overlap that kernel (programmatic dependent launch, trace_small.cu) */
+    bool scene_settled = false;
     unsigned int* d_order = nullptr;         /* two order-history buffers of the persistent tracer (trace_small.cu) */
     size_t cap_order = 0;                    /* uints */
     int order_key[7] = {0, 0, 0, 0, 0, 0, 0};   /* frame size + shard the history belongs to */
@@ -227,6 +230,7 @@ const char* rt_last_error(rt_context* ctx) { return ctx ? ctx->err.c_str() : "nu
 
 int rt_set_option(rt_context* ctx, int key, int value) {
     if (!ctx || key < 0 || key >= RT_OPT_N) return RT_ERR_ARG;
+    ctx->scene_settled = false;
     if ((key == RT_OPT_BUILDER || key == RT_OPT_FORCE_RADIX) && ctx->opt[key] != value)
         ctx->have_scene = false;   /* the next rt_set_scene rebuilds the hierarchy */
     ctx->opt[key] = value;
@@ -236,6 +240,7 @@ int rt_set_option(rt_context* ctx, int key, int value) {
 int rt_set_stream(rt_context* ctx, void* cuda_stream) {
     if (!ctx) return RT_ERR_ARG;
     ctx->stream = (cudaStream_t)cuda_stream;
+    ctx->scene_settled = false;
     return RT_OK;
 }
 
@@ -314,6 +319,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
             if (objects[i].type != ctx->host_objs[i].type) { mode = 0; break; }
     }
     if (mode < 0) return RT_OK;
+    ctx->scene_settled = false;
 
     bool bvh_geometry_changed = (mode == 0);
     if (mode == 1) {
@@ -492,7 +498,8 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
         }
         RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,
-                                            ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w, ctx->stream));
+                                            ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
+                                            ctx->scene_settled ? 1 : 0, ctx->stream));
     }
     else {
         RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
@@ -504,6 +511,7 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
     else RT_CHECK(ctx, rt_launch_copy(ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, ctx->stream));
     if (rc != RT_OK) return rc;
     if (timing) { cudaEventRecord(ctx->ev[3], ctx->stream); ctx->timing_valid = true; }
+    ctx->scene_settled = true;
     return RT_OK;
 }
 

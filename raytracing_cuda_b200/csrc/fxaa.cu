@@ -158,6 +158,10 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
     }
     __syncthreads();
 
+    /* programmatic dependent launch: the tracer has completed from here on; the next frame's pre-pass may start */
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
     int k = blockIdx.x;
     int tx, ty;
     bool have = fx_tile_origin(k, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, tx, ty);
@@ -272,7 +276,17 @@ extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned
     int grid = n_sm * 4;
     if (grid > slots) grid = slots;
     if (grid < 1) grid = 1;
-    rt_fxaa_tma_kernel<<<grid, FX_THREADS, 0, stream>>>(*map, in, out, w, h, n, id, st, kx, ky);
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(FX_THREADS, 1, 1);
+    cfg.stream = stream;
+    cfg.attrs = pdl;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, rt_fxaa_tma_kernel, *map, in, out, w, h, n, id, st, kx, ky);
+    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 

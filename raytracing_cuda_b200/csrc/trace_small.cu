@@ -295,6 +295,12 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
     return true;
 }
 
+/* Programmatic dependent launch (griddepcontrol): a kernel launched with the programmatic-serialization attribute
+ * may start while its predecessor on the stream still runs.  wait = the predecessor has completed and its
+ * writes are visible (no-op without the attribute); launch = the successor may be launched. */
+__device__ __forceinline__ void rs_griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void rs_griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 #define RT_SMALL_WARPS (RT_SMALL_THREADS / 32)
 #define RT_SMALL_TILE_W 16
 #define RT_SMALL_TILE_H 8
@@ -313,10 +319,10 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
 
 /* ---------------------------------------------------------------- binning pre-pass */
 
-__global__ void __launch_bounds__(256)
-rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
-                     int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
-                     int work_tiles_x, int work_tiles_y) {
+__device__ __forceinline__ void
+rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restrict__ tile_lists, int tiles_x,
+            int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
+            int work_tiles_x, int work_tiles_y) {
     /* tiles_x, n_tiles count BINS here; work_list = NULL for whole frames */
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -378,7 +384,20 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
         count += __popc(m);
     }
     if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
+}
 
+/* The pre-pass reads the scene and writes lists nobody else is using, so -- when the host knows that the
+ * scene was complete before the previous kernel on the stream (wait_first = 0: that kernel is the FXAA / copy
+ * of this context's previous frame) -- it runs WHILE that kernel finishes.  Its last act is to wait for it:
+ * the tracer, which waits for this kernel, then never overwrites the base image under a running FXAA. */
+__global__ void __launch_bounds__(256)
+rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
+                     int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
+                     int work_tiles_x, int work_tiles_y, int wait_first) {
+    if (wait_first) rs_griddep_wait();
+    rs_griddep_launch();                         /* the tracer may start staging the scene */
+    rs_cull_bin(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y);
+    rs_griddep_wait();
 }
 
 /* ---------------------------------------------------------------- tracer */
@@ -407,6 +426,25 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     float4* s_nodes = (float4*)(smem + RS_PLANES_BYTES);
     float4* s_prims = s_nodes + 4 * n_nodes;
     float4* s_mats = s_prims + 3 * n;
+
+    unsigned int u0 = 0;
+    if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
+
+    /* stage the scene: links become byte offsets from the start of the nodes */
+    for (int i = tid; i < 4 * n_nodes; i += RT_SMALL_THREADS) {
+        float4 v = __ldg(sc.nodes + i);
+        if ((i & 3) == 3) {
+            const int c0 = __float_as_int(v.x), c1 = __float_as_int(v.y);
+            v.x = __int_as_float(c0 >= 0 ? c0 * 64 : ~(prims_off + (~c0) * 48));
+            v.y = __int_as_float(c1 >= 0 ? c1 * 64 : ~(prims_off + (~c1) * 48));
+        }
+        s_nodes[i] = v;
+    }
+    for (int i = tid; i < 3 * n; i += RT_SMALL_THREADS) s_prims[i] = __ldg(sc.prims + i);
+    for (int i = tid; i < 2 * sc.n_objects; i += RT_SMALL_THREADS) s_mats[i] = __ldg(sc.mats + i);
+    for (int i = tid; i < 2 * sc.n_planes; i += RT_SMALL_THREADS) s_planes[i] = __ldg(sc.planes + i);
+    __syncthreads();                             /* the only CTA barrier */
+    rs_griddep_wait();                           /* the pre-pass has finished: lists, work list, counts */
 
     /* Work units: single 8x4 patches, fetched one at a time from an atomic counter, nothing reserved ahead.
      * Unit k is patch 3 - k % 4 of tile n_tiles - 1 - k / 4: the frame is walked from its LAST tile to its
@@ -440,23 +478,6 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         by_cost = false;
 #endif
     }
-    unsigned int u0 = 0;
-    if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
-
-    /* stage the scene: links become byte offsets from the start of the nodes */
-    for (int i = tid; i < 4 * n_nodes; i += RT_SMALL_THREADS) {
-        float4 v = __ldg(sc.nodes + i);
-        if ((i & 3) == 3) {
-            const int c0 = __float_as_int(v.x), c1 = __float_as_int(v.y);
-            v.x = __int_as_float(c0 >= 0 ? c0 * 64 : ~(prims_off + (~c0) * 48));
-            v.y = __int_as_float(c1 >= 0 ? c1 * 64 : ~(prims_off + (~c1) * 48));
-        }
-        s_nodes[i] = v;
-    }
-    for (int i = tid; i < 3 * n; i += RT_SMALL_THREADS) s_prims[i] = __ldg(sc.prims + i);
-    for (int i = tid; i < 2 * sc.n_objects; i += RT_SMALL_THREADS) s_mats[i] = __ldg(sc.mats + i);
-    for (int i = tid; i < 2 * sc.n_planes; i += RT_SMALL_THREADS) s_planes[i] = __ldg(sc.planes + i);
-    __syncthreads();                             /* the only CTA barrier */
 
     RtSmallShared sh;
     /* opaque moves: keep the two addresses in registers instead of re-deriving them in the hot loops */
@@ -541,6 +562,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         }
         u0 = __shfl_sync(0xffffffffu, u1, 0);
     }
+    rs_griddep_launch();                         /* FXAA may be launched; it waits for this grid to complete */
     if (COUNT) {
         /* all lanes take part: lanes without pixels add zeros */
         rt_flush_counters(pc, n_pixels, counters);
@@ -610,8 +632,10 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
                                              int* hit_ids, RtCountersDev* counters, unsigned int* tile_counter,
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
                                              const unsigned int* order_r, unsigned int* order_w,
-                                             cudaStream_t stream) {
-    /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel */
+                                             int after_own_post, cudaStream_t stream) {
+    /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel.
+     * after_own_post: the previous operation on the stream is the FXAA / copy kernel of this context's previous
+     * frame (nothing this frame reads is still being written): the pre-pass overlaps it, see rt_cull_tiles_kernel */
     const size_t smem = rt_trace_small_smem_bytes(sc->n_bvh_prims, sc->n_objects, sc->n_planes);
     const int tiles_x = (f->imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W;
     const int tiles = tiles_x * ((f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
@@ -621,12 +645,30 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     /* behind the bin lists: the work list of sharded frames (filled by the pre-pass) */
     unsigned int* work_list = (unsigned int*)(tile_lists + (size_t)bins * RT_SMALL_LIST);
     const bool sharded = f->n_shards > 1;
-    rt_cull_tiles_kernel<<<(bins + 7) / 8, 256, 0, stream>>>(*sc, *f, tile_lists, bins_x, bins, sharded ? work_list : nullptr,
-                                                            tile_counter + RS_CNT_TILES, tiles_x, tiles_y);
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.stream = stream;
+    cfg.attrs = pdl;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3((bins + 7) / 8, 1, 1);
+    cfg.blockDim = dim3(256, 1, 1);
+    cfg.dynamicSmemBytes = 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins,
+                                       sharded ? work_list : (unsigned int*)nullptr, tile_counter + RS_CNT_TILES, tiles_x,
+                                       tiles_y, after_own_post ? 0 : 1);
+    if (e != cudaSuccess) return e;
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     const int units = tiles * RT_SMALL_PATCHES;
     if (grid > (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS) grid = (units + RT_SMALL_WARPS - 1) / RT_SMALL_WARPS;
-    if (count) rt_trace_small_kernel<true><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, order_r, order_w);
-    else       rt_trace_small_kernel<false><<<grid, RT_SMALL_THREADS, smem, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, tile_lists, tiles_x, (unsigned int)tiles, bins_x, work_list, force_linear, order_r, order_w);
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(RT_SMALL_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    const unsigned int* wl = work_list;
+    const unsigned short* tl = tile_lists;
+    if (count) e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<true>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w);
+    else       e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<false>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w);
+    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

@@ -227,6 +227,36 @@ def test_order_history_changes_scheduling_only():
         assert (ids == ids_ref).all() and (img == img_ref).all(), k
 
 
+@pytest.mark.parametrize("alias", [True, False])
+def test_back_to_back_frames_overlap_safely(alias):
+    """Consecutive frames of one context with an unchanged scene: the next frame's binning pre-pass is launched
+    programmatically dependent and runs while the previous frame's FXAA / copy kernel finishes; the tracer must
+    still never overwrite the base image under it.  40 frames alternating between two cameras, no host
+    synchronisation in between, every output compared with the frame rendered alone."""
+    import torch
+    r = gu.renderer()
+    s = rt.Scene()
+    w, h = 1280, 720
+    frames, refs = [], []
+    for view in (5, 6):
+        f = s.configure(view=view, hours=14.0, imgw=w, imgh=h, alias=alias)
+        fr = type(f)()
+        C.memmove(C.byref(fr), C.byref(f), C.sizeof(f))
+        frames.append(fr)
+    r.set_scene(s.objects, s.lights)
+    for fr in frames:
+        o = torch.zeros(w * h, dtype=torch.int32, device="cuda")
+        r.render(fr, o)
+        r.synchronize()
+        refs.append(o)
+    outs = [torch.zeros(w * h, dtype=torch.int32, device="cuda") for _ in range(40)]
+    for k, o in enumerate(outs):
+        r.render(frames[k & 1], o)
+    r.synchronize()
+    for k, o in enumerate(outs):
+        assert torch.equal(o, refs[k & 1]), k
+
+
 # ---------------------------------------------------------------- legacy boundary
 
 def _legacy_call(lib, out_ptr, s, f, sky):
