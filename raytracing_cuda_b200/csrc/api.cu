@@ -27,6 +27,7 @@
 
 extern "C" {
 cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, int builder, cudaStream_t stream);
+int rt_build_by_value(const RtBuildBuffers* b, int mode);
 cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned int* tmp_keys, unsigned int* tmp_vals,
                                 unsigned int* hist, int n, int force_radix, cudaStream_t stream);
 int rt_radix_hist_entries(int n);
@@ -319,6 +320,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
             if (objects[i].type != ctx->host_objs[i].type) { mode = 0; break; }
     }
     if (mode < 0) return RT_OK;
+    const bool settled_before = ctx->scene_settled;   /* the stream ends in this context's own FXAA / copy kernel */
     ctx->scene_settled = false;
 
     bool bvh_geometry_changed = (mode == 0);
@@ -375,7 +377,16 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
     }
 
     ctx->host_objs.assign(objects, objects + n_objects);
-    if (n_objects > 0)
+    b.objs = ctx->d_objs;
+    b.n_objects = n_objects;
+    b.plane_idx = ctx->d_plane_idx;
+    b.n_planes = n_planes;
+    b.n_bvh = n_bvh;
+    /* Per-frame refit of a small scene (the launchKernel path: 133 objects move / change colour every frame):
+     * the objects travel in the kernel parameters, no copy; d_objs is refreshed by the next full build. */
+    b.objs_host = rt_build_by_value(&b, mode == 0 ? 0 : 1) ? (const float*)ctx->host_objs.data() : nullptr;
+    b.after_own_post = settled_before ? 1 : 0;
+    if (n_objects > 0 && !b.objs_host)
         RT_CHECK(ctx, cudaMemcpyAsync(ctx->d_objs, ctx->host_objs.data(), sizeof(rtb_Object) * (size_t)n_objects, cudaMemcpyHostToDevice,
                                       ctx->stream));
     if (mode == 0 && n_planes > 0)
@@ -384,11 +395,6 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
     /* host_objs is the staging source of the async copies above: it is only rewritten by the next
      * rt_set_scene, and pageable cudaMemcpyAsync returns after the source has been staged */
 
-    b.objs = ctx->d_objs;
-    b.n_objects = n_objects;
-    b.plane_idx = ctx->d_plane_idx;
-    b.n_planes = n_planes;
-    b.n_bvh = n_bvh;
     const bool timing = ctx->opt[RT_OPT_TIMING] != 0;
     if (timing) cudaEventRecord(ctx->ev[4], ctx->stream);
     /* material / plane-only changes still run the (cheap) setup + refit: one code path */

@@ -24,6 +24,7 @@
  */
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <string.h>
 
 #include "rt_device.h"
 
@@ -480,14 +481,13 @@ __global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, in
  * arrival counters and the union scratch in shared memory (the per-frame path of launchKernel: the
  * reference re-uploads its 133 objects every frame, kernel.cu:448). */
 #define RT_FUSED_MAX 1024
-__global__ void __launch_bounds__(RT_FUSED_MAX)
-rt_fused_refit_kernel(const float* __restrict__ objs, int n_objects, const int* __restrict__ plane_idx, int n_planes,
-                      float4* mats, float4* recs, float4* planes, int* bvh_src, float4* prim_lo, float4* prim_hi,
-                      unsigned int* __restrict__ bounds, const unsigned int* __restrict__ sorted_vals, int n,
-                      const int2* __restrict__ children, const int* __restrict__ node_parent,
-                      const int* __restrict__ leaf_parent, float* __restrict__ nodes, float4* __restrict__ prims,
-                      int* __restrict__ depth_out) {
-    extern __shared__ __align__(16) unsigned char fused_smem[];
+__device__ __forceinline__ void
+rt_fused_refit_body(const float* objs, int n_objects, const int* __restrict__ plane_idx, int n_planes,
+                    float4* mats, float4* recs, float4* planes, int* bvh_src, float4* prim_lo, float4* prim_hi,
+                    unsigned int* __restrict__ bounds, const unsigned int* __restrict__ sorted_vals, int n,
+                    const int2* __restrict__ children, const int* __restrict__ node_parent,
+                    const int* __restrict__ leaf_parent, float* __restrict__ nodes, float4* __restrict__ prims,
+                    int* __restrict__ depth_out, unsigned char* fused_smem) {
     __shared__ unsigned int s_bounds[8];
     unsigned int* s_flags = (unsigned int*)fused_smem;                   /* [n-1] */
     float* s_aux = (float*)(s_flags + (n > 1 ? n - 1 : 0));             /* [n-1][12] */
@@ -507,6 +507,49 @@ rt_fused_refit_kernel(const float* __restrict__ objs, int n_objects, const int* 
         rt_refit_leaf<true>(i, n, sorted_vals, bvh_src, recs, prim_lo, prim_hi, extent, ord2f(s_bounds[6]), children,
                             node_parent, leaf_parent, s_flags, nodes, s_aux, prims, depth_out);
     }
+}
+
+__global__ void __launch_bounds__(RT_FUSED_MAX)
+rt_fused_refit_kernel(const float* __restrict__ objs, int n_objects, const int* __restrict__ plane_idx, int n_planes,
+                      float4* mats, float4* recs, float4* planes, int* bvh_src, float4* prim_lo, float4* prim_hi,
+                      unsigned int* __restrict__ bounds, const unsigned int* __restrict__ sorted_vals, int n,
+                      const int2* __restrict__ children, const int* __restrict__ node_parent,
+                      const int* __restrict__ leaf_parent, float* __restrict__ nodes, float4* __restrict__ prims,
+                      int* __restrict__ depth_out) {
+    extern __shared__ __align__(16) unsigned char fused_smem[];
+    rt_fused_refit_body(objs, n_objects, plane_idx, n_planes, mats, recs, planes, bvh_src, prim_lo, prim_hi, bounds,
+                        sorted_vals, n, children, node_parent, leaf_parent, nodes, prims, depth_out, fused_smem);
+}
+
+/* The same with the objects passed BY VALUE in the kernel parameters (up to RT_BYVALUE_MAX objects = 20.7 KB;
+ * sm_70+ takes 32,764 parameter bytes): the per-frame path of launchKernel needs no host-to-device copy at all,
+ * and because nothing then stands between the previous frame's last kernel and this one on the stream, it is
+ * launched programmatically dependent: with wait_first = 0 (the host knows that every reader of the scene
+ * buffers finished before that kernel started) it refits WHILE that kernel -- the previous frame's FXAA --
+ * runs, and waits for it only at its end, so that the completion of this grid implies the completion of that
+ * one for everything downstream. */
+struct RtObjectsByValue {
+    float v[17 * RT_BYVALUE_MAX];
+};
+__global__ void __launch_bounds__(RT_FUSED_MAX)
+rt_fused_refit_byvalue_kernel(const __grid_constant__ RtObjectsByValue blk, int n_objects,
+                              const int* __restrict__ plane_idx, int n_planes, float4* mats, float4* recs,
+                              float4* planes, int* bvh_src, float4* prim_lo, float4* prim_hi,
+                              unsigned int* __restrict__ bounds, const unsigned int* __restrict__ sorted_vals, int n,
+                              const int2* __restrict__ children, const int* __restrict__ node_parent,
+                              const int* __restrict__ leaf_parent, float* __restrict__ nodes,
+                              float4* __restrict__ prims, int* __restrict__ depth_out, int wait_first) {
+    extern __shared__ __align__(16) unsigned char fused_smem[];
+    if (wait_first) asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    /* parameter space -> shared memory (behind the refit scratch) */
+    const size_t scratch = ((size_t)(n > 1 ? n - 1 : 0) * (sizeof(unsigned int) + 12 * sizeof(float)) + 15) & ~(size_t)15;
+    float* s_objs = (float*)(fused_smem + scratch);
+    for (int k = threadIdx.x; k < 17 * n_objects; k += blockDim.x) s_objs[k] = blk.v[k];
+    __syncthreads();
+    rt_fused_refit_body(s_objs, n_objects, plane_idx, n_planes, mats, recs, planes, bvh_src, prim_lo, prim_hi, bounds,
+                        sorted_vals, n, children, node_parent, leaf_parent, nodes, prims, depth_out, fused_smem);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 /* ------------------------------------------------------------------ PLOC hierarchy (small scenes)
@@ -633,12 +676,38 @@ rt_ploc_small_kernel(const unsigned int* __restrict__ sorted_vals, int n, const 
 
 /* mode 0: full build; mode 1: refit only (topology from the previous build).
  * builder 0: PLOC when n <= PLOC_MAX, else Karras; 1: Karras; 2: PLOC (falls back to Karras above PLOC_MAX) */
+/* does rt_build_bvh(b, mode) take the objects from b->objs_host in the kernel parameters (no upload needed)? */
+extern "C" int rt_build_by_value(const RtBuildBuffers* b, int mode) {
+    const size_t scratch = (size_t)(b->n_bvh > 1 ? b->n_bvh - 1 : 0) * (sizeof(unsigned int) + 12 * sizeof(float));
+    return mode == 1 && b->n_objects <= RT_BYVALUE_MAX && b->n_bvh >= 1 &&
+           scratch + 16 + sizeof(float) * 17 * (size_t)b->n_objects <= 48 * 1024;
+}
+
 extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force_radix, int builder, cudaStream_t stream) {
     const int T = RT_BUILD_THREADS;
     const size_t fused_smem = (size_t)(b->n_bvh > 1 ? b->n_bvh - 1 : 0) * (sizeof(unsigned int) + 12 * sizeof(float));
     if (mode == 1 && b->n_objects <= RT_FUSED_MAX && b->n_bvh >= 1 && fused_smem <= 40 * 1024) {
         const int n = b->n_bvh;
         const size_t smem = fused_smem;
+        if (b->objs_host && rt_build_by_value(b, mode)) {
+            RtObjectsByValue blk;                /* copied into the launch by cudaLaunchKernelEx */
+            memcpy(blk.v, b->objs_host, sizeof(float) * 17 * (size_t)b->n_objects);
+            cudaLaunchAttribute pdl[1];
+            pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            pdl[0].val.programmaticStreamSerializationAllowed = 1;
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(1, 1, 1);
+            cfg.blockDim = dim3(RT_FUSED_MAX, 1, 1);
+            cfg.dynamicSmemBytes = ((smem + 15) & ~(size_t)15) + sizeof(float) * 17 * (size_t)b->n_objects;
+            cfg.stream = stream;
+            cfg.attrs = pdl;
+            cfg.numAttrs = 1;
+            return cudaLaunchKernelEx(&cfg, rt_fused_refit_byvalue_kernel, blk, b->n_objects, (const int*)b->plane_idx,
+                                      b->n_planes, b->mats, b->recs, b->planes, b->bvh_src, b->prim_lo, b->prim_hi,
+                                      b->bounds, (const unsigned int*)b->vals, n, (const int2*)b->children,
+                                      (const int*)b->node_parent, (const int*)b->leaf_parent, b->nodes, b->prims,
+                                      b->depth, b->after_own_post ? 0 : 1);
+        }
         rt_fused_refit_kernel<<<1, RT_FUSED_MAX, smem, stream>>>(b->objs, b->n_objects, b->plane_idx, b->n_planes, b->mats,
                                                                b->recs, b->planes, b->bvh_src, b->prim_lo, b->prim_hi,
                                                                b->bounds, b->vals, n, b->children, b->node_parent,

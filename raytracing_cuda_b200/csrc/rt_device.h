@@ -40,6 +40,7 @@
 #define RT_STACK_SIZE 64
 /* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 48*n must fit 16 bits */
 #define RT_SMALL_MAX_PRIMS 288
+#define RT_BYVALUE_MAX 304             /* objects passed in kernel parameters (68 B each) by the per-frame refit */
 #define RT_SMALL_ORDER_CLASSES 8      /* patch cost classes of the tracer's order history */
 #define RT_SMALL_ORDER_HEAD 32        /* uints before the class lists of an order buffer: [0..7] class counts */
 #ifndef RT_SMALL_DYN_SMEM_MAX
@@ -99,6 +100,10 @@ struct RtBuildBuffers {
     float* nodes; float* node_aux; float4* prims;
     int* depth;
     int n_bvh;
+    /* per-frame refit of a small scene: the objects on the host (NULL: already uploaded to `objs`), and whether the
+     * previous operation on the stream is this context's own FXAA / copy kernel (bvh_build.cu, by-value refit) */
+    const float* objs_host;
+    int after_own_post;
 };
 
 /* owner of the tile containing pixel (x,y) */
