@@ -131,6 +131,12 @@ int  rt_get_base_image(rt_context* ctx, unsigned int** base_dev);
 int  rt_fxaa(rt_context* ctx, const unsigned int* in_dev, unsigned int* out_dev,
              int imgw, int imgh, const rt_shard* shard);
 
+/* The reference's `factor` render-scale knob (main.cpp:40-47): in_dev holds a frame of (out_w*factor) x
+ * (out_h*factor) pixels; mode 0 = the GL_NEAREST blit of the reference (window pixel (x,y) shows texel
+ * (x f + f/2, y f + f/2), main.cpp:317-318), mode 1 = f x f box average (supersampling). factor 1..16. */
+int  rt_present(rt_context* ctx, const unsigned int* in_dev, int out_w, int out_h, int factor, int mode,
+                unsigned int* out_dev);
+
 /* Tile gather helpers for multi-GPU compositing: pack the tiles a shard owns
  * into a dense [n_tiles][tile_h][tile_w] buffer / scatter them back. */
 int  rt_shard_tile_count(const rt_shard* shard, int imgw, int imgh);
@@ -231,6 +237,14 @@ enum {
  * water plane at index 0 and sun/moon spheres as the last two.  Returns object count
  * (2*cells*cells + 3); out may be NULL to query. */
 int  rtb_terrain_build(int cells, unsigned int seed, rtb_Object* out, int capacity);
+/* Scene ingest (csrc/ingest.cpp).  Heightmap: nx x nz samples (row-major, z outer) over [x0,x1] x [z0,z1] ->
+ * 2 (nx-1)(nz-1) up-facing triangles, cells split like the reference's island top (scene.cpp:369-373).
+ * Wavefront OBJ text ("v", "f" with v, v/vt, v//vn, v/vt/vn and negative indices; polygons fan-triangulated).
+ * Material fields (shine, specular, mirror, color, light) are copied from *material (NULL: the mountain
+ * material, scene.cpp:338-342).  out = NULL queries the count; -1 = capacity too small, -2 = malformed face. */
+int  rtb_heightmap_objects(const float* heights, int nx, int nz, float x0, float x1, float z0, float z1,
+                           const rtb_Object* material, rtb_Object* out, int capacity);
+int  rtb_obj_parse(const char* text, size_t len, const rtb_Object* material, rtb_Object* out, int capacity);
 /* Procedural equirectangular sky map `which` (0 morning,1 day,2 evening,3 night), RGBA8. */
 void rtb_sky_synthetic(int which, int w, int h, unsigned char* out);
 

@@ -6,5 +6,5 @@ include/rtb_api.h; this package is the ctypes host mirror used by tests, bench a
 """
 from . import _lib, structs  # noqa: F401
 from .renderer import Renderer, default_stride, make_shard, rays_per_frame  # noqa: F401
-from .scene import (POSES, TIME_PRESETS, VIEW_ISLAND, VIEW_MOUNTAINS, Scene, load_sky_pngs,  # noqa: F401
-                    synthetic_sky, terrain_objects)
+from .scene import (POSES, TIME_PRESETS, VIEW_ISLAND, VIEW_MOUNTAINS, Scene, heightmap_objects,  # noqa: F401
+                    load_obj, load_sky_pngs, synthetic_sky, terrain_objects)

@@ -53,6 +53,7 @@ SIGNATURES = {
     "rt_peer_frame_release": (C.c_int, [_P, _P, C.c_uint]),
     "rt_peer_frame_error": (C.c_int, [_P, _P, C.POINTER(C.c_uint)]),
     "rt_peer_frame_close": (C.c_int, [_P, _P]),
+    "rt_present": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "rt_synchronize": (C.c_int, [_P]),
     "rt_get_counters": (C.c_int, [_P, C.POINTER(C.c_ulonglong)]),
     "rt_get_timings": (C.c_int, [_P, C.POINTER(C.c_float)]),
@@ -80,6 +81,8 @@ SIGNATURES = {
     "rtb_scene_frame": (None, [_P, C.c_int, C.c_int, C.POINTER(Frame)]),
     "rtb_scene_launch": (None, [_P, _P, C.c_int, C.c_int, C.POINTER(_P), C.c_int, C.c_int]),
     "rtb_terrain_build": (C.c_int, [C.c_int, C.c_uint, _P, C.c_int]),
+    "rtb_heightmap_objects": (C.c_int, [_P, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, _P, _P, C.c_int]),
+    "rtb_obj_parse": (C.c_int, [C.c_char_p, C.c_size_t, _P, _P, C.c_int]),
     "rtb_sky_synthetic": (None, [C.c_int, C.c_int, C.c_int, _P]),
     "rtb_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
     "rtb_write_png": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),

@@ -52,6 +52,8 @@ cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int
 cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned int* packed, int w, int h, const rt_shard* sh,
                                  int unpack, cudaStream_t stream);
 cudaError_t rt_launch_ffma_peak(int n_sm, cudaStream_t stream, float* ms, double* flops);
+cudaError_t rt_launch_present(const unsigned int* in, unsigned int* out, int w, int h, int factor, int mode,
+                              cudaStream_t stream);
 cudaError_t rt_launch_peer_signal(unsigned int* flags, int rank, unsigned int seq, cudaStream_t stream);
 cudaError_t rt_launch_peer_wait(unsigned int* flags, int n_ranks, unsigned int seq, cudaStream_t stream);
 cudaError_t rt_launch_peer_release(unsigned int* flags, unsigned int seq, cudaStream_t stream);
@@ -558,6 +560,15 @@ int rt_shard_tile_count(const rt_shard* sh, int imgw, int imgh) {
     if (!sh || sh->n_shards < 1 || sh->tile_w < 1 || sh->tile_h < 1) return -1;
     const int tiles_x = (imgw + sh->tile_w - 1) / sh->tile_w, tiles_y = (imgh + sh->tile_h - 1) / sh->tile_h;
     return ((tiles_x + sh->n_shards - 1) / sh->n_shards) * tiles_y;   /* slots, some may be empty */
+}
+
+int rt_present(rt_context* ctx, const unsigned int* in_dev, int out_w, int out_h, int factor, int mode,
+               unsigned int* out_dev) {
+    if (!ctx || !in_dev || !out_dev || out_w < 1 || out_h < 1 || factor < 1 || factor > 16 || mode < 0 || mode > 1)
+        return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_present(in_dev, out_dev, out_w, out_h, factor, mode, ctx->stream));
+    return RT_OK;
 }
 
 /* ---------------------------------------------------------------- peer frame (peer.cu) */

@@ -226,6 +226,31 @@ __global__ void rt_copy_kernel(const unsigned int* __restrict__ in, unsigned int
     out[(size_t)y * w + x] = in[(size_t)y * w + x];
 }
 
+/* The reference's `factor` knob (main.cpp:40-47): the frame is rendered at factor x the window size and the
+ * fixed-function blit shows it through a GL_NEAREST texture (main.cpp:317-318), i.e. window pixel (x, y) takes
+ * texel (x f + f/2, y f + f/2).  mode 0 restates that; mode 1 averages the f x f block instead (per channel,
+ * rounded to nearest), the supersampling the knob was meant for. */
+__global__ void rt_present_kernel(const unsigned int* __restrict__ in, unsigned int* __restrict__ out, int w, int h,
+                                  int factor, int mode) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+    if (x >= w || y >= h) return;
+    const int sw = w * factor;
+    if (mode == 0) {
+        out[(size_t)y * w + x] = __ldg(in + (size_t)(y * factor + factor / 2) * sw + x * factor + factor / 2);
+        return;
+    }
+    unsigned int r = 0, g = 0, b = 0;
+    for (int j = 0; j < factor; j++)
+        for (int i = 0; i < factor; i++) {
+            const unsigned int c = __ldg(in + (size_t)(y * factor + j) * sw + x * factor + i);
+            r += c & 255u;
+            g += (c >> 8) & 255u;
+            b += (c >> 16) & 255u;
+        }
+    const unsigned int n = (unsigned int)(factor * factor), half = n / 2;
+    out[(size_t)y * w + x] = ((r + half) / n) | (((g + half) / n) << 8) | (((b + half) / n) << 16);
+}
+
 /* gather / scatter of the tiles a shard owns (multi-GPU compositing) */
 __global__ void rt_pack_tiles_kernel(const unsigned int* __restrict__ frame, unsigned int* __restrict__ packed,
                                      int w, int h, int tile_w, int tile_h, int n_shards, int shard_id, int stride,
@@ -298,6 +323,13 @@ extern "C" cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out,
                                                    sh->stride);
     else
         rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0);
+    return cudaGetLastError();
+}
+
+extern "C" cudaError_t rt_launch_present(const unsigned int* in, unsigned int* out, int w, int h, int factor, int mode,
+                                         cudaStream_t stream) {
+    dim3 block(32, 8, 1), grid((w + 31) / 32, (h + 7) / 8, 1);
+    rt_present_kernel<<<grid, block, 0, stream>>>(in, out, w, h, factor, mode);
     return cudaGetLastError();
 }
 

@@ -120,6 +120,12 @@ class Renderer:
         self._check(self._lib.rt_fxaa(self._h, _ptr(in_dev), _ptr(out_dev), imgw, imgh,
                                       C.byref(shard) if shard is not None else None), "rt_fxaa")
 
+    def present(self, in_dev, out_w, out_h, factor, out_dev, box=False):
+        """The reference's `factor` knob (main.cpp:40-47): (out_w*factor x out_h*factor) frame -> window-size frame,
+        point-sampled like its GL_NEAREST blit, or box-averaged (supersampling)."""
+        self._check(self._lib.rt_present(self._h, _ptr(in_dev), int(out_w), int(out_h), int(factor), 1 if box else 0,
+                                         _ptr(out_dev)), "rt_present")
+
     def pack_tiles(self, frame_dev, imgw, imgh, shard, packed_dev):
         self._check(self._lib.rt_pack_tiles(self._h, _ptr(frame_dev), imgw, imgh, C.byref(shard), _ptr(packed_dev)),
                     "rt_pack_tiles")

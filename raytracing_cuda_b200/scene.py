@@ -136,6 +136,46 @@ def terrain_objects(cells, seed=0x5EED):
     return arr
 
 
+def _material_ptr(material):
+    if material is None:
+        return None, None
+    m = np.zeros(1, dtype=OBJECT_DTYPE)
+    m[0] = material
+    return m, m.ctypes.data
+
+
+def heightmap_objects(heights, x0, x1, z0, z1, material=None):
+    """Heightmap [nz][nx] over [x0,x1] x [z0,z1] -> triangle Object array (csrc/ingest.cpp)."""
+    lib = _lib.load()
+    hm = np.ascontiguousarray(heights, dtype=np.float32)
+    nz, nx = hm.shape
+    keep, mp = _material_ptr(material)
+    n = lib.rtb_heightmap_objects(hm.ctypes.data, nx, nz, x0, x1, z0, z1, mp, None, 0)
+    arr = np.zeros(max(n, 0), dtype=OBJECT_DTYPE)
+    if n <= 0 or lib.rtb_heightmap_objects(hm.ctypes.data, nx, nz, x0, x1, z0, z1, mp, arr.ctypes.data, n) != n:
+        raise ValueError("rtb_heightmap_objects: need at least 2 x 2 samples")
+    return arr
+
+
+def load_obj(text_or_path, material=None):
+    """Wavefront OBJ (text, or a path to a file) -> triangle Object array (csrc/ingest.cpp)."""
+    import os
+    lib = _lib.load()
+    if isinstance(text_or_path, str) and "\n" not in text_or_path and os.path.isfile(text_or_path):
+        with open(text_or_path, "rb") as fh:
+            data = fh.read()
+    else:
+        data = text_or_path.encode() if isinstance(text_or_path, str) else bytes(text_or_path)
+    keep, mp = _material_ptr(material)
+    n = lib.rtb_obj_parse(data, len(data), mp, None, 0)
+    if n < 0:
+        raise ValueError("rtb_obj_parse: malformed face (rc=%d)" % n)
+    arr = np.zeros(n, dtype=OBJECT_DTYPE)
+    if n and lib.rtb_obj_parse(data, len(data), mp, arr.ctypes.data, n) != n:
+        raise ValueError("rtb_obj_parse")
+    return arr
+
+
 def synthetic_sky(w, h):
     """Four procedural RGBA8 sky maps [4][h][w][4] (asset-free stand-in for backgrounds/*.png)."""
     lib = _lib.load()
