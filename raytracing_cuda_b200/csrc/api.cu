@@ -403,6 +403,20 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
     RT_CHECK(ctx, rt_build_bvh(&b, mode == 0 ? 0 : 1, ctx->opt[RT_OPT_FORCE_RADIX], ctx->opt[RT_OPT_BUILDER], ctx->stream));
     if (timing) { cudaEventRecord(ctx->ev[5], ctx->stream); ctx->build_timed = true; }
     (void)bvh_geometry_changed;
+    if (mode == 0 && n_bvh > 1 && !rt_trace_small_supported(n_bvh, n_objects, n_planes)) {
+        /* The HBM tracer keeps RT_STACK_SIZE entries per thread; a hierarchy deeper than that (possible with
+         * Karras splits over heavily duplicated Morton codes) would lose pushes.  New topology is the one path
+         * that already costs a build, so the 4-byte read-back is affordable here: fail loudly instead. */
+        int depth = 0;
+        RT_CHECK(ctx, cudaMemcpyAsync(&depth, b.depth, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        if (depth > RT_STACK_SIZE) {
+            ctx->have_scene = false;
+            char msg[160];
+            snprintf(msg, sizeof(msg), "LBVH depth %d exceeds the traversal stack (%d entries)", depth, RT_STACK_SIZE);
+            return fail(ctx, RT_ERR_UNSUPPORTED, msg);
+        }
+    }
 
     ctx->scene.nodes = (const float4*)b.nodes;
     ctx->scene.prims = b.prims;
