@@ -141,6 +141,39 @@ __device__ __forceinline__ bool fx_tile_origin(int k, int tiles_x, int tiles_y, 
     return true;
 }
 
+/* the 64x32 pixels of tile (tx, ty) from the staged box: 256 threads, each walks 8 CONSECUTIVE rows of one
+ * column with the 3x3 luminance window in registers (3 shared-memory loads per pixel instead of 9); a warp
+ * still covers 32 adjacent columns of one row per step, so loads are conflict-free and stores coalesced */
+template <bool INNER>
+__device__ __forceinline__ void fx_filter_tile(const unsigned int* __restrict__ px, const float (*lum)[FX_BOXW],
+                                               unsigned int* __restrict__ out, int tx, int ty, int w, int h, int tid) {
+    const int cx = tid & 63, row0 = (tid >> 6) * (FX_TH / 4);
+    const int x = tx * FX_TW + cx;
+    const int lx = cx + FX_HALO_X;
+    unsigned int* o = out + (size_t)(ty * FX_TH + row0) * w + x;
+    float a0 = lum[row0][lx - 1], a1 = lum[row0][lx], a2 = lum[row0][lx + 1];              /* the row above */
+    float b0 = lum[row0 + 1][lx - 1], b1 = lum[row0 + 1][lx], b2 = lum[row0 + 1][lx + 1];  /* this row */
+#pragma unroll
+    for (int pass = 0; pass < FX_TH / 4; pass++, o += w) {
+        const int ly = row0 + pass + 1;
+        const int y = ty * FX_TH + row0 + pass;
+        const float c0 = lum[ly + 1][lx - 1], c1 = lum[ly + 1][lx], c2 = lum[ly + 1][lx + 1];   /* the row below */
+        if (INNER || (x < w && y < h)) {
+            const unsigned int centre = px[ly * FX_BOXW + lx];
+            unsigned int result = centre;
+            if (INNER || (x > 0 && y > 0 && x + 1 < w && y + 1 < h)) {
+                float b;
+                int dx, dy;
+                if (fx_decide(b1, b2, b0, a1, c1, a2, a0, c2, c0, b, dx, dy))
+                    result = fx_blend(centre, px[(ly + dy) * FX_BOXW + lx + dx], b);
+            }
+            *o = result;
+        }
+        a0 = b0; a1 = b1; a2 = b2;
+        b0 = c0; b1 = c1; b2 = c2;
+    }
+}
+
 __global__ void __launch_bounds__(FX_THREADS)
 rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned int* __restrict__ in,
                    unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride, int kx,
@@ -171,10 +204,20 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
     }
     uint32_t phases = 0;   /* bit s = parity to wait for on stage s */
     int stage = 0;
+    /* whole frames: the next tile by addition (k advances by gridDim.x), no division in the loop */
+    const int step_x = (int)gridDim.x % tiles_x, step_y = (int)gridDim.x / tiles_x;
     while (have) {
         const int kn = k + gridDim.x;
         int ntx, nty;
-        const bool have_next = fx_tile_origin(kn, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, ntx, nty);
+        bool have_next;
+        if (n_shards <= 1) {
+            ntx = tx + step_x;
+            nty = ty + step_y;
+            if (ntx >= tiles_x) { ntx -= tiles_x; nty++; }
+            have_next = kn < tiles_x * tiles_y;
+        } else {
+            have_next = fx_tile_origin(kn, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, ntx, nty);
+        }
         if (tid == 0 && have_next && ntx < tiles_x) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             fx_mbar_expect_tx(&s_bar[stage ^ 1], FX_STAGE_BYTES);
@@ -186,27 +229,10 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
             for (int i = tid; i < FX_BOXH * FX_BOXW; i += FX_THREADS)
                 (&s_lum[0][0])[i] = fx_lum(s_px[stage][i]);
             __syncthreads();
-            const int cx = tid & 63, ry = tid >> 6;
-            const int x = tx * FX_TW + cx;
-#pragma unroll 2
-            for (int pass = 0; pass < FX_TH / 4; pass++) {
-                const int row = pass * 4 + ry;
-                const int y = ty * FX_TH + row;
-                if (x < w && y < h) {
-                    const int lx = cx + FX_HALO_X, ly = row + 1;
-                    const unsigned int centre = s_px[stage][ly * FX_BOXW + lx];
-                    unsigned int result = centre;
-                    if (x > 0 && y > 0 && x + 1 < w && y + 1 < h) {
-                        float b;
-                        int dx, dy;
-                        if (fx_decide(s_lum[ly][lx], s_lum[ly][lx + 1], s_lum[ly][lx - 1], s_lum[ly - 1][lx],
-                                      s_lum[ly + 1][lx], s_lum[ly - 1][lx + 1], s_lum[ly - 1][lx - 1],
-                                      s_lum[ly + 1][lx + 1], s_lum[ly + 1][lx - 1], b, dx, dy))
-                            result = fx_blend(centre, s_px[stage][(ly + dy) * FX_BOXW + lx + dx], b);
-                    }
-                    out[(size_t)y * w + x] = result;
-                }
-            }
+            /* tiles that touch no frame border skip the per-pixel bounds and border tests */
+            const bool inner = tx > 0 && ty > 0 && (tx + 1) * FX_TW < w && (ty + 1) * FX_TH < h;
+            if (inner) fx_filter_tile<true>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
+            else       fx_filter_tile<false>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
         }
         __syncthreads();   /* everyone is done with s_px[stage] and s_lum before they are refilled */
         k = kn;

@@ -70,6 +70,21 @@ def test_constant_division_by_fma_correction_is_ieee_division():
             assert q == a / b, (a, b)
 
 
+def test_fxaa_division_by_twelve_by_fma_correction():
+    """fxaa_core.cuh: (double)sum / 12.0 (reference kernel.cu:372) as q0 + (sum - 12 q0) rc with rc = RN(1/12),
+    for float sums in the range of eight luminances plus doubled axis terms (0 .. 12) and beyond."""
+    from fractions import Fraction as F
+    rng = np.random.default_rng(3)
+    rc = 1.0 / 12.0
+    vals = np.concatenate([rng.uniform(0, 12.5, 20000), rng.uniform(0, 0.05, 2000), [0.0, 12.0, 1.0, 3.0, 1e-30]]).astype(np.float32)
+    for a32 in vals:
+        a = float(a32)
+        q0 = a * rc
+        r = float(F(a) - F(q0) * 12)
+        q = float(F(q0) + F(r) * F(rc))
+        assert q == a / 12.0, a
+
+
 def test_fmodf_one_equals_x_minus_trunc():
     x = np.concatenate([np.random.default_rng(5).uniform(-3, 3, 20000), [0.0, 1.0, 1.9999999, -0.5]]).astype(np.float32)
     assert (np.fmod(x, np.float32(1.0)) == x - np.trunc(x)).all()
