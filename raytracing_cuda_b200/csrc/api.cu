@@ -587,8 +587,6 @@ int rt_present(rt_context* ctx, const unsigned int* in_dev, int out_w, int out_h
 
 /* ---------------------------------------------------------------- peer frame (peer.cu) */
 
-#define RT_PEER_FLAG_UINTS 256
-
 struct rt_peer_frame {
     unsigned int* base = nullptr;    /* n_buffers frames, then the flag block */
     size_t n_pixels = 0;
@@ -674,7 +672,7 @@ int rt_peer_frame_error(rt_context* ctx, rt_peer_frame* pf, unsigned int* err) {
     if (!ctx || !pf || !err) return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
     RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    RT_CHECK(ctx, cudaMemcpy(err, pf->flags() + 136, sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    RT_CHECK(ctx, cudaMemcpy(err, pf->flags() + RT_PEER_FLAG_ERROR, sizeof(unsigned int), cudaMemcpyDeviceToHost));
     return RT_OK;
 }
 

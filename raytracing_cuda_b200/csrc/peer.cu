@@ -24,10 +24,7 @@
 
 #define RT_PEER_TIMEOUT_NS 2000000000ull   /* 2 s */
 
-/* flag block layout (uints, 32-byte spacing): [8 k] done of rank k (k < 16), [128] released, [136] error */
-#define RT_PEER_FLAG_DONE(k) (8 * (k))
-#define RT_PEER_FLAG_RELEASED 128
-#define RT_PEER_FLAG_ERROR 136
+/* flag block layout: rt_device.h (RT_PEER_FLAG_*) */
 
 __device__ __forceinline__ unsigned int rt_peer_load(const unsigned int* p) {
     unsigned int v;

@@ -40,6 +40,11 @@
 #define RT_STACK_SIZE 64
 /* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 48*n must fit 16 bits */
 #define RT_SMALL_MAX_PRIMS 288
+/* peer frame (peer.cu): flag block behind the frames, uints with 32-byte spacing */
+#define RT_PEER_FLAG_UINTS 256
+#define RT_PEER_FLAG_DONE(k) (8 * (k))     /* frame number rank k (< 16) has finished */
+#define RT_PEER_FLAG_RELEASED 128          /* frame number the owner has released */
+#define RT_PEER_FLAG_ERROR 136             /* set by a wait that gave up */
 #define RT_BYVALUE_MAX 304             /* objects passed in kernel parameters (68 B each) by the per-frame refit */
 #define RT_SMALL_ORDER_CLASSES 8      /* patch cost classes of the tracer's order history */
 #define RT_SMALL_ORDER_HEAD 32        /* uints before the class lists of an order buffer: [0..7] class counts */
