@@ -68,7 +68,8 @@ enum {
     RT_OPT_BUILDER = 6,     /* hierarchy over the Morton-sorted primitives: 0 = auto (PLOC up to 1024 primitives, Karras above), 1 = Karras, 2 = PLOC */
     RT_OPT_FORCE_RADIX = 7, /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
     RT_OPT_ORDER = 8,       /* work order of the shared-memory tracer on whole frames: 0 = most expensive patches of the previous frame of this size first (default; first frame bottom-up), 1 = always bottom-up.  Scheduling only: identical pixels */
-    RT_OPT_N = 9
+    RT_OPT_SHADOW_BINS = 9, /* shadow rays of the shared-memory tracer: 0 = per-light direction bins (default), 1 = traverse the hierarchy.  Which primitives get tested only: identical pixels */
+    RT_OPT_N = 10
 };
 
 /* One frame's uniforms: what launchKernel receives by value / as small host arrays. */
@@ -171,6 +172,10 @@ int  rt_peer_frame_close(rt_context* ctx, rt_peer_frame* pf);
 
 int  rt_synchronize(rt_context* ctx);
 int  rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]);
+/* diagnostics: copy the light bins the last frame of the shared-memory tracer used (4 lights x 6 faces x 64 x 64
+ * bins of 8 ushorts: [0] count or 0xFFFF = too many, [1..7] leaf offsets); returns the bytes copied, 0 if none,
+ * -RT_ERR_* on an error */
+long long rt_debug_light_bins(rt_context* ctx, void* out, size_t bytes);
 /* ms of the last frame's kernels (RT_OPT_TIMING=1): [0]=trace [1]=fxaa [2]=bvh build/refit */
 int  rt_get_timings(rt_context* ctx, float out_ms[3]);
 /* FP32 FFMA throughput of the device in TFLOP/s (2 flops per FFMA), measured with a register-resident

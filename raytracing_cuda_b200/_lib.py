@@ -17,6 +17,7 @@ RT_OK, RT_ERR_CUDA, RT_ERR_ARG, RT_ERR_STATE, RT_ERR_UNSUPPORTED = 0, 1, 2, 3, 4
 RT_OPT_BUILDER = 6
 RT_OPT_FORCE_RADIX = 7
 RT_OPT_ORDER = 8
+RT_OPT_SHADOW_BINS = 9
 RT_PEER_HANDLE_BYTES = 64
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
@@ -56,6 +57,7 @@ SIGNATURES = {
     "rt_present": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "rt_synchronize": (C.c_int, [_P]),
     "rt_get_counters": (C.c_int, [_P, C.POINTER(C.c_ulonglong)]),
+    "rt_debug_light_bins": (C.c_longlong, [_P, C.c_void_p, C.c_size_t]),
     "rt_get_timings": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "rt_bvh_info": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rt_bvh_download": (C.c_int, [_P, _P, _P, _P]),

@@ -37,7 +37,7 @@ cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned 
 cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
-                                  unsigned int* order_w, int after_own_post, cudaStream_t stream);
+                                  unsigned int* order_w, int after_own_post, uint4* lgrid, cudaStream_t stream);
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
@@ -99,6 +99,7 @@ struct rt_context {
     int order_key[7] = {0, 0, 0, 0, 0, 0, 0};   /* frame size + shard the history belongs to */
     int order_cur = 0;                       /* buffer holding it */
     unsigned short* d_tile_lists = nullptr;  /* per-tile primary candidate lists (trace_small.cu) */
+    uint4* d_lgrid = nullptr;                /* light bins of the shared-memory tracer (trace_small.cu), RT_LGRID_BYTES */
     size_t cap_tile_lists = 0;
     unsigned int* d_tile_counter = nullptr;  /* [0] next tile, [1] finished CTAs (persistent tracer; self re-arming) */
 
@@ -222,7 +223,7 @@ int rt_destroy(rt_context* ctx) {
     RtBuildBuffers& b = ctx->bb;
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
                     b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.flags, b.node_aux,
-                    b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists, ctx->d_order};
+                    b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists, ctx->d_order, ctx->d_lgrid};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     delete ctx;
@@ -491,6 +492,7 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
             RT_CHECK(ctx, regrow(&ctx->d_tile_lists, need));
             ctx->cap_tile_lists = need;
         }
+        if (!ctx->d_lgrid && ctx->opt[RT_OPT_SHADOW_BINS] == 0) RT_CHECK(ctx, regrow(&ctx->d_lgrid, RT_LGRID_BYTES / sizeof(uint4)));
         /* Order history: a frame files every patch under its measured cost; the next frame of the same size
          * and shard starts with the most expensive ones (frame-to-frame coherence of an interactive renderer;
          * the first frame of a kind walks bottom-up).  Pure scheduling: pixels do not depend on it. */
@@ -521,7 +523,8 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
         RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
-                                            ctx->scene_settled ? 1 : 0, ctx->stream));
+                                            ctx->scene_settled ? 1 : 0,
+                                            ctx->opt[RT_OPT_SHADOW_BINS] == 0 ? ctx->d_lgrid : (uint4*)nullptr, ctx->stream));
     }
     else {
         RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
@@ -715,6 +718,18 @@ int rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]) {
     RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     RT_CHECK(ctx, cudaMemcpy(out, ctx->d_counters, sizeof(RtCountersDev), cudaMemcpyDeviceToHost));
     return RT_OK;
+}
+
+/* diagnostics: the light bins of the last frame of the shared-memory tracer (RT_LGRID_LIGHTS x 6 x G x G bins of
+ * 8 ushorts: [0] count or 0xFFFF, [1..7] leaf offsets).  Returns the bytes copied (<= bytes), 0 if there are none,
+ * minus the status code on an error. */
+long long rt_debug_light_bins(rt_context* ctx, void* out, size_t bytes) {
+    if (!ctx || !out) return -(long long)RT_ERR_ARG;
+    if (!ctx->d_lgrid) return 0;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess) return -(long long)RT_ERR_CUDA;
+    const size_t n = bytes < RT_LGRID_BYTES ? bytes : RT_LGRID_BYTES;
+    if (cudaMemcpy(out, ctx->d_lgrid, n, cudaMemcpyDeviceToHost) != cudaSuccess) return -(long long)RT_ERR_CUDA;
+    return (long long)n;
 }
 
 int rt_get_timings(rt_context* ctx, float out_ms[3]) {

@@ -46,6 +46,11 @@
 #define RT_PEER_FLAG_RELEASED 128          /* frame number the owner has released */
 #define RT_PEER_FLAG_ERROR 136             /* set by a wait that gave up */
 #define RT_BYVALUE_MAX 304             /* objects passed in kernel parameters (68 B each) by the per-frame refit */
+/* light bins of the small-scene tracer (trace_small.cu): per light a cube map of RT_LGRID_G x RT_LGRID_G direction
+ * bins per face, each bin one uint4 = 8 ushorts: [0] count (0xFFFF: too many, traverse), [1..7] leaf offsets */
+#define RT_LGRID_G 64
+#define RT_LGRID_LIGHTS 4             /* lights with bins; further lights traverse the hierarchy */
+#define RT_LGRID_BYTES ((size_t)RT_LGRID_LIGHTS * 6 * RT_LGRID_G * RT_LGRID_G * 16)
 #define RT_SMALL_ORDER_CLASSES 8      /* patch cost classes of the tracer's order history */
 #define RT_SMALL_ORDER_HEAD 32        /* uints before the class lists of an order buffer: [0..7] class counts */
 #ifndef RT_SMALL_DYN_SMEM_MAX

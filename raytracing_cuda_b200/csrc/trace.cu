@@ -33,7 +33,7 @@ struct RtGlobalScene {
         dbg[depth ? 1 : 0] += cnt.node_tests - before;
         return h;
     }
-    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3&, int, RtLocalCounters& cnt) {
         const unsigned int before = cnt.node_tests;
         const bool r = rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
         dbg[2] += cnt.node_tests - before;
@@ -43,7 +43,7 @@ struct RtGlobalScene {
     __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int, RtLocalCounters& cnt) {
         return rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
     }
-    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3&, int, RtLocalCounters& cnt) {
         return rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
     }
 #endif

@@ -72,7 +72,7 @@ __device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDe
             float angle = fmaxf(0.0f, rt_dot(N, sdir));
             if (COUNT) pc.n_shadow++;
             if (angle > 0.0f) {
-                if (acc.occluded(so, sdir, shadowDist, pc.t)) angle = 0.0f;
+                if (acc.occluded(so, sdir, shadowDist, vec, li, pc.t)) angle = 0.0f;
             } else if (COUNT) {
                 pc.n_shadow_skipped++;
             }

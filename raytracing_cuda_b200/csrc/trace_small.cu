@@ -36,6 +36,13 @@
 #define RT_SMALL_CTAS_PER_SM 4
 #endif
 #define RT_SMALL_STACK_STRIDE (2 * RT_SMALL_THREADS)   /* bytes between two levels of one thread's stack */
+/* light bins (see `light bins` below) */
+#define RS_LG_G RT_LGRID_G
+#define RS_LG_CELL 16                        /* bins per edge of the coarse cell one CTA handles */
+#define RS_LG_CELLS (RS_LG_G / RS_LG_CELL)
+#define RS_LG_DELTA 0.00390625f              /* 2^-8: |s|, |t| up to 1 + delta belong to a face */
+#define RS_LG_SCALE ((float)RS_LG_G / (2.0f + 2.0f * RS_LG_DELTA))      /* bin = (s + 1 + delta) * scale */
+#define RS_LG_BLOCKS_PER_LIGHT (6 * RS_LG_CELLS * RS_LG_CELLS)
 
 /* Shared-memory addressing: the hot loops use 32-bit shared-window addresses and explicit ld/st.shared, so a
  * node or leaf fetch is one add + LDS.128s with immediate offsets.  Node and leaf links are byte offsets from
@@ -44,6 +51,7 @@ struct RtSmallShared {
     unsigned int base;       /* shared address of the staged nodes (leaf records follow them) */
     unsigned int stack0;     /* shared address of this thread's stack column */
     const unsigned short* list;   /* primary candidates of the current tile: [0] count, then leaf byte offsets */
+    const uint4* lgrid;           /* light bins (NULL: shadow rays traverse the hierarchy) */
     int root, n_prims, n_planes, prims_off;
     bool deep;               /* hierarchy deeper than RT_SMALL_STACK: secondary rays loop linearly instead */
 };
@@ -182,7 +190,9 @@ struct RtSmallScene {
         else rs_traverse<false, COUNT>(s, o, d, best, 0.0f, cnt);
         return best;
     }
-    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, RtLocalCounters& cnt) {
+    /* to_light = L - P (the vector the caller normalised into d), li = index of the light */
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3& to_light, int li,
+                                             RtLocalCounters& cnt) {
         for (int p = 0; p < s.n_planes; p++) {
             const float4 q0 = rs_lds128(s.base - RS_PLANES_BYTES + 32 * p), q1 = rs_lds128(s.base - RS_PLANES_BYTES + 32 * p + 16);
             float t;
@@ -190,7 +200,38 @@ struct RtSmallScene {
             if (__float_as_uint(q0.w) & RT_TAG_EMISSIVE) continue;
             if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t) && t < tmax) return true;
         }
+        if (s.lgrid && li < RT_LGRID_LIGHTS) {
+            /* light bins: the ray's line passes through the light, its direction from there is -to_light */
+            const float ax = fabsf(to_light.x), ay = fabsf(to_light.y), az = fabsf(to_light.z);
+            const bool X = ax >= ay && ax >= az, Y = !X && ay >= az;
+            const float m = X ? ax : (Y ? ay : az);
+            const float qm = X ? to_light.x : (Y ? to_light.y : to_light.z);
+            const float qa = X ? to_light.y : (Y ? to_light.z : to_light.x);
+            const float qb = X ? to_light.z : (Y ? to_light.x : to_light.y);
+            const int face = (X ? 0 : (Y ? 2 : 4)) + (qm > 0.0f ? 1 : 0);      /* direction = -to_light */
+            const float k = -RS_LG_SCALE * rt_rcp_approx(m);
+            const float gs = __fmaf_rn(qa, k, RS_LG_SCALE * (1.0f + RS_LG_DELTA));
+            const float gt = __fmaf_rn(qb, k, RS_LG_SCALE * (1.0f + RS_LG_DELTA));
+            const int ix = min(max((int)gs, 0), RS_LG_G - 1), iy = min(max((int)gt, 0), RS_LG_G - 1);
+            uint4 e = __ldg(s.lgrid + ((li * 6 + face) * RS_LG_G + iy) * RS_LG_G + ix);
+            unsigned int n = e.x & 0xFFFFu;
+            if (n != 0xFFFFu && m > 0.0f) {
+                for (; n; n--) {
+                    e.x = __funnelshift_r(e.x, e.y, 16);
+                    e.y = __funnelshift_r(e.y, e.z, 16);
+                    e.z = __funnelshift_r(e.z, e.w, 16);
+                    e.w >>= 16;
+                    float t;
+                    unsigned int tag;
+                    if (rs_test_record(s.base + (e.x & 0xFFFFu), o, d, t, tag, cnt, COUNT) && t < tmax) return true;
+                }
+                return false;
+            }
+        }
         RtHit dummy;
+#ifdef RS_DIAG_NO_SHADOW_BVH
+        return false;
+#endif
         if (!s.deep) return rs_traverse<true, COUNT>(s, o, d, dummy, tmax, cnt);
         {
             for (int j = 0; j < s.n_prims; j++) {
@@ -241,13 +282,8 @@ struct RsFrustum {
     bool ok;       /* false: degenerate / non-convex corner set -> keep every primitive */
 };
 
-__device__ __forceinline__ RsFrustum rs_tile_frustum(const RtFrameDev& f, int x0, int y0, int x1, int y1) {
-    const float xa = (float)x0 - 1.0f, xb = (float)x1 + 1.0f, ya = (float)y0 - 1.0f, yb = (float)y1 + 1.0f;
-    vec3 c[4];
-    c[0] = rs_primary_target(f, xa, ya);
-    c[1] = rs_primary_target(f, xb, ya);
-    c[2] = rs_primary_target(f, xb, yb);
-    c[3] = rs_primary_target(f, xa, yb);
+/* the cone of all positive combinations of four corner directions c[0..3] (in order around the cone) */
+__device__ __forceinline__ RsFrustum rs_frustum_from_corners(const vec3* c) {
     const vec3 mid = vadd(vadd(c[0], c[1]), vadd(c[2], c[3]));
     RsFrustum fr;
     fr.ok = true;
@@ -258,13 +294,23 @@ __device__ __forceinline__ RsFrustum rs_tile_frustum(const RtFrameDev& f, int x0
         const float len = sqrtf(vdot(n, n));
         const float s = (vdot(n, mid) < 0.0f ? -1.0f : 1.0f) / len;
         n = vscale(n, s);
-        /* every ray of the tile is a convex combination of the four corners: it is inside plane k if the
+        /* every ray of the cone is a convex combination of the four corners: it is inside plane k if the
          * two corners that do not span it are */
         const float e0 = vdot(n, c[(k + 2) & 3]), e1 = vdot(n, c[(k + 3) & 3]);
         if (!(len > 0.0f) || !(e0 > 0.0f) || !(e1 > 0.0f)) fr.ok = false;
         fr.n[k] = n;
     }
     return fr;
+}
+
+__device__ __forceinline__ RsFrustum rs_tile_frustum(const RtFrameDev& f, int x0, int y0, int x1, int y1) {
+    const float xa = (float)x0 - 1.0f, xb = (float)x1 + 1.0f, ya = (float)y0 - 1.0f, yb = (float)y1 + 1.0f;
+    vec3 c[4];
+    c[0] = rs_primary_target(f, xa, ya);
+    c[1] = rs_primary_target(f, xb, ya);
+    c[2] = rs_primary_target(f, xb, yb);
+    c[3] = rs_primary_target(f, xa, yb);
+    return rs_frustum_from_corners(c);
 }
 
 /* can any ray of the tile (origin `eye`, inside `fr`) hit leaf record `rec`? */
@@ -319,6 +365,239 @@ __device__ __forceinline__ void rs_griddep_launch() { asm volatile("griddepcontr
 
 /* ---------------------------------------------------------------- binning pre-pass */
 
+/* world-space pad of the cull tests from the scene's extent and the apex (eye or light) position: 2^-13 of the
+ * largest coordinate in play */
+__device__ __forceinline__ float rs_cull_pad(const RtSceneDev& sc, const float* apex) {
+    float m = fmaxf(fmaxf(fabsf(apex[0]), fabsf(apex[1])), fabsf(apex[2]));
+    if (sc.n_bvh_prims > 1) {
+        const float4 a = __ldg(sc.nodes), b = __ldg(sc.nodes + 1), c = __ldg(sc.nodes + 2);
+        const float r[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
+#pragma unroll
+        for (int k = 0; k < 2; k++)
+#pragma unroll
+            for (int q = 0; q < 3; q++) m = fmaxf(m, fabsf(r[6 * k + q]) + r[6 * k + 3 + q]);
+    }
+    return 1.220703125e-04f * m + 1e-6f;      /* 2^-13 */
+}
+
+/* ---------------------------------------------------------------- light bins
+ * Every shadow ray of light L lies on a line through L (kernel.cu:177-182: origin P + 0.001 dir, dir towards L), so
+ * which primitives it can meet depends on its DIRECTION SEEN FROM L only.  Per light, a cube map around L with
+ * RT_LGRID_G x RT_LGRID_G direction bins per face holds the (at most 7) non-emissive primitives a line of that
+ * bin can hit; the tracer looks its shadow ray up (major axis of P - L, two divisions) and tests that list instead
+ * of traversing the hierarchy.  Triangles are one-sided (`det < 0.001`, kernel.cu:104): towards a light only
+ * those facing AWAY from it can be hit, which halves the lists.  Conservative like the primary bins: cones grown
+ * by 1 % of a bin, world-space pad on every plane test, faces overlapping by RS_LG_DELTA; the exact leaf tests
+ * decide, so the answer equals the reference's loop over all objects.
+ * Face f = 2 axis + (negative side); face coordinates (s, t) = components (axis+1)%3, (axis+2)%3 over |axis|. */
+
+/* A primitive seen from one light in the coordinates of one cube face: (m, a, b) = (component along the face
+ * axis, made positive towards the face; the two others).  A direction of the face is (1, s, t).
+ *   sphere:   v[0] = centre, r = radius grown by the rounding noise of the leaf test and the pad
+ *   triangle: v[0..2] = vertices, e[k] = plane through the light and edge k as (A, B, C): E_k(s, t) = A + B s + C t
+ *             is >= 0 on the triangle's side, tol[k] its pad. */
+struct RsLgPrim {
+    float v[3][3];
+    float e[3][3];
+    float tol[3];
+    float r;            /* > 0: sphere */
+    float fill[2];      /* 96 B = 6 float4 */
+};
+static_assert(sizeof(RsLgPrim) % 16 == 0, "RsLgPrim is copied as float4s");
+
+/* the bins [g0s, g1s) x [g0t, g1t) of a face, grown by 1 % of a bin: bounds in s, t and the reciprocal lengths of
+ * the normals (-s, 1, 0), (-t, 0, 1) of the four side planes */
+struct RsLgRect {
+    float s0, s1, t0, t1, is0, is1, it0, it1;
+};
+__device__ __forceinline__ float rs_lg_coord(float g) { return g * (1.0f / RS_LG_SCALE) - (1.0f + RS_LG_DELTA); }
+__device__ __forceinline__ RsLgRect rs_lg_rect(float g0s, float g0t, float g1s, float g1t) {
+    RsLgRect r;
+    r.s0 = rs_lg_coord(g0s - 0.01f); r.s1 = rs_lg_coord(g1s + 0.01f);
+    r.t0 = rs_lg_coord(g0t - 0.01f); r.t1 = rs_lg_coord(g1t + 0.01f);
+    r.is0 = rsqrtf(1.0f + r.s0 * r.s0); r.is1 = rsqrtf(1.0f + r.s1 * r.s1);
+    r.it0 = rsqrtf(1.0f + r.t0 * r.t0); r.it1 = rsqrtf(1.0f + r.t1 * r.t1);
+    return r;
+}
+
+/* world vector -> face coordinates */
+__device__ __forceinline__ void rs_lg_to_face(int face, const vec3& w, float* o) {
+    const float sg = (face & 1) ? -1.0f : 1.0f;
+    const int axis = face >> 1;
+    o[0] = sg * (axis == 0 ? w.x : (axis == 1 ? w.y : w.z));
+    o[1] = axis == 0 ? w.y : (axis == 1 ? w.z : w.x);
+    o[2] = axis == 0 ? w.z : (axis == 1 ? w.x : w.y);
+}
+
+/* Leaf record `rec` as an occluder of the light at `lp`: false if it can never be one (emissive, kernel.cu:189;
+ * a triangle showing the light its front, `det < 0.001`).  d = -dir(ray) leaves the light: det = d.Ng > 0 needs
+ * the light on the BACK side. */
+__device__ __forceinline__ bool rs_lg_prim(int face, const vec3& lp, const float4* __restrict__ rec, float pad,
+                                           RsLgPrim& p) {
+    const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1);
+    const unsigned int tag = __float_as_uint(q0.w);
+    if (tag & RT_TAG_EMISSIVE) return false;
+    const vec3 a = vsub(f4xyz(q0), lp);
+    if (tag & RT_TAG_SPHERE) {
+        rs_lg_to_face(face, a, p.v[0]);
+        /* d2 = L.L - tca^2 carries rounding noise of about 2^-21 |L|^2 (as in rs_tile_may_hit) */
+        p.r = sqrtf(q1.y + 3.814697265625e-06f * vdot(a, a)) + pad;
+        return true;
+    }
+    const float4 q2 = __ldg(rec + 2);
+    const vec3 e1 = f4xyz(q1), e2 = f4xyz(q2);
+    const vec3 ng = vcross(e1, e2);
+    const float side = vdot(ng, a);
+    if (-side > 1e-3f * sqrtf(vdot(ng, ng) * vdot(a, a)) + pad * sqrtf(vdot(ng, ng))) return false;
+    const vec3 b = vadd(a, e1), c = vadd(a, e2);
+    rs_lg_to_face(face, a, p.v[0]);
+    rs_lg_to_face(face, b, p.v[1]);
+    rs_lg_to_face(face, c, p.v[2]);
+    p.r = 0.0f;
+    /* planes through the light and the edges, oriented towards the third vertex.  A point y within `pad` of the
+     * triangle has n.y >= -|n| pad; as y = tau (1, s, t) with |y| >= |n| / |edge| - pad (the edge's line is that
+     * far from the light) and |(1, s, t)| <= 1.75, E(s, t) >= -1.75 pad |edge| / (1 - 1/8) = -2 pad |edge| */
+    float T = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float* u = p.v[k];
+        const float* w = p.v[(k + 1) % 3];
+        p.e[k][0] = u[1] * w[2] - u[2] * w[1];
+        p.e[k][1] = u[2] * w[0] - u[0] * w[2];
+        p.e[k][2] = u[0] * w[1] - u[1] * w[0];
+        const float dx = w[0] - u[0], dy = w[1] - u[1], dz = w[2] - u[2];
+        /* |n| / |edge| = distance of the edge's line from the light; closer than 8 pads: no test for this edge */
+        const float el = sqrtf(dx * dx + dy * dy + dz * dz);
+        const float nl2 = p.e[k][0] * p.e[k][0] + p.e[k][1] * p.e[k][1] + p.e[k][2] * p.e[k][2];
+        p.tol[k] = nl2 > 64.0f * pad * pad * el * el ? 2.5f * pad * el : 3.0e38f;
+        if (k == 0) T = p.e[0][0] * p.v[2][0] + p.e[0][1] * p.v[2][1] + p.e[0][2] * p.v[2][2];
+    }
+    const float la = vdot(a, a), lb = vdot(b, b), lc = vdot(c, c);
+    const bool flat = !(T * T > 1e-10f * la * lb * lc);       /* light (nearly) in the triangle's plane: no edge tests */
+    const float sg = flat ? 0.0f : (T > 0.0f ? 1.0f : -1.0f);
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+#pragma unroll
+        for (int q = 0; q < 3; q++) p.e[k][q] *= sg;
+    return true;
+}
+
+/* can a line through the light with a direction inside the rectangle hit the primitive? */
+__device__ __forceinline__ bool rs_lg_may_hit(const RsLgPrim& p, const RsLgRect& r, float pad) {
+    if (p.r > 0.0f) {
+        const float m = p.v[0][0], a = p.v[0][1], b = p.v[0][2];
+        if ((a - r.s0 * m) * r.is0 < -p.r || (r.s1 * m - a) * r.is1 < -p.r) return false;
+        if ((b - r.t0 * m) * r.it0 < -p.r || (r.t1 * m - b) * r.it1 < -p.r) return false;
+        return true;
+    }
+    bool o0 = true, o1 = true, o2 = true, o3 = true, ob = true;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float m = p.v[k][0], a = p.v[k][1], b = p.v[k][2];
+        o0 = o0 && (a - r.s0 * m) * r.is0 < -pad;
+        o1 = o1 && (r.s1 * m - a) * r.is1 < -pad;
+        o2 = o2 && (b - r.t0 * m) * r.it0 < -pad;
+        o3 = o3 && (r.t1 * m - b) * r.it1 < -pad;
+        ob = ob && m < -pad;
+    }
+    if (o0 || o1 || o2 || o3 || ob) return false;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        const float big = p.e[k][0] + fmaxf(p.e[k][1] * r.s0, p.e[k][1] * r.s1) + fmaxf(p.e[k][2] * r.t0, p.e[k][2] * r.t1);
+        if (big < -p.tol[k]) return false;
+    }
+    return true;
+}
+
+#define RS_LG_PRIM_F4 (sizeof(RsLgPrim) / 16)
+
+/* one CTA (256 threads) = one coarse cell of 16x16 bins of one face of one light; a warp = 8x4 bins of it.
+ * Three levels: CTA (every primitive against the cell), warp (the cell's survivors against its 8x4 bins), lane
+ * (the warp's survivors against its bin). */
+__device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFrameDev& f, uint4* __restrict__ lgrid,
+                                              int cell_id) {
+    __shared__ float4 s_prim[RT_SMALL_MAX_PRIMS * RS_LG_PRIM_F4];
+    __shared__ unsigned short s_slot[RT_SMALL_MAX_PRIMS];
+    __shared__ unsigned short s_warp[8][RT_SMALL_MAX_PRIMS];
+    __shared__ int s_n;
+    const int li = cell_id / RS_LG_BLOCKS_PER_LIGHT, rr = cell_id - li * RS_LG_BLOCKS_PER_LIGHT;
+    const int face = rr / (RS_LG_CELLS * RS_LG_CELLS), cell = rr - face * (RS_LG_CELLS * RS_LG_CELLS);
+    const int cy = cell / RS_LG_CELLS, cx = cell - cy * RS_LG_CELLS;
+    const int n = sc.n_bvh_prims;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef RS_LG_TIMING
+    const long long lg_t0 = clock64();
+#endif
+    const float lpos[3] = {f.lights[li].px, f.lights[li].py, f.lights[li].pz};
+    const vec3 lp = v3(lpos[0], lpos[1], lpos[2]);
+    const float pad = rs_cull_pad(sc, lpos);
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    {
+        const RsLgRect rc = rs_lg_rect((float)(cx * RS_LG_CELL), (float)(cy * RS_LG_CELL),
+                                       (float)(cx * RS_LG_CELL + RS_LG_CELL), (float)(cy * RS_LG_CELL + RS_LG_CELL));
+        for (int j = threadIdx.x; j < n; j += blockDim.x) {
+            union { RsLgPrim p; float4 q[RS_LG_PRIM_F4]; } u;
+            if (rs_lg_prim(face, lp, sc.prims + 3 * j, pad, u.p) && rs_lg_may_hit(u.p, rc, pad)) {
+                const int at = atomicAdd(&s_n, 1);             /* any order: the lists serve an any-hit test */
+#pragma unroll
+                for (int k = 0; k < (int)RS_LG_PRIM_F4; k++) s_prim[at * RS_LG_PRIM_F4 + k] = u.q[k];
+                s_slot[at] = (unsigned short)j;
+            }
+        }
+    }
+    __syncthreads();
+    const int nc = s_n;
+    const int wx = cx * RS_LG_CELL + 8 * (warp & 1), wy = cy * RS_LG_CELL + 4 * (warp >> 1);
+    int nw = 0;
+    if (nc) {
+        const RsLgRect rw = rs_lg_rect((float)wx, (float)wy, (float)(wx + 8), (float)(wy + 4));
+        for (int i0 = 0; i0 < nc; i0 += 32) {
+            const int i = i0 + lane;
+            bool keep = false;
+            if (i < nc) {
+                union { RsLgPrim p; float4 q[RS_LG_PRIM_F4]; } u;
+#pragma unroll
+                for (int k = 0; k < (int)RS_LG_PRIM_F4; k++) u.q[k] = s_prim[i * RS_LG_PRIM_F4 + k];
+                keep = rs_lg_may_hit(u.p, rw, pad);
+            }
+            const unsigned int mk = __ballot_sync(0xffffffffu, keep);
+            if (keep) s_warp[warp][nw + __popc(mk & ((1u << lane) - 1u))] = (unsigned short)i;
+            nw += __popc(mk);
+        }
+        __syncwarp();
+    }
+    const int gx = wx + (lane & 7), gy = wy + (lane >> 3);
+    unsigned int w[4] = {0u, 0u, 0u, 0u};
+    int count = 0;
+    if (nw) {
+        const int prims_off = 64 * (n > 1 ? n - 1 : 0);
+        const RsLgRect rb = rs_lg_rect((float)gx, (float)gy, (float)(gx + 1), (float)(gy + 1));
+        for (int k0 = 0; k0 < nw; k0++) {
+            const int i = s_warp[warp][k0];
+            union { RsLgPrim p; float4 q[RS_LG_PRIM_F4]; } u;
+#pragma unroll
+            for (int k = 0; k < (int)RS_LG_PRIM_F4; k++) u.q[k] = s_prim[i * RS_LG_PRIM_F4 + k];
+            if (!rs_lg_may_hit(u.p, rb, pad)) continue;
+            count++;
+            if (count < 8) {
+                const unsigned int off = (unsigned int)(prims_off + 48 * (int)s_slot[i]);
+#pragma unroll
+                for (int k = 1; k < 8; k++)                  /* static register indices */
+                    if (k == count) w[k >> 1] |= off << (16 * (k & 1));
+            }
+        }
+    }
+    w[0] |= count < 8 ? (unsigned int)count : 0xFFFFu;
+    lgrid[((size_t)(li * 6 + face) * RS_LG_G + gy) * RS_LG_G + gx] = make_uint4(w[0], w[1], w[2], w[3]);
+#ifdef RS_LG_TIMING
+    /* debug variant: (cycles, cell survivors, this warp's survivors) of warp w of cell c into the last light's bins */
+    if (lane == 0)
+        lgrid[(size_t)(RT_LGRID_LIGHTS - 1) * 6 * RS_LG_G * RS_LG_G + cell_id * 8 + warp] =
+            make_uint4((unsigned int)(clock64() - lg_t0), (unsigned int)nc, (unsigned int)nw, 0u);
+#endif
+}
+
 __device__ __forceinline__ void
 rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restrict__ tile_lists, int tiles_x,
             int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
@@ -355,20 +634,7 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
     if (need_mask == 0u) return;                 /* nothing of this bin is traced here: no list needed either */
     const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
     const int prims_off = 64 * n_nodes;
-    /* world-space pad of the cull tests from the scene's extent and the eye position */
-    float pad;
-    {
-        float m = fmaxf(fmaxf(fabsf(f.pos[0]), fabsf(f.pos[1])), fabsf(f.pos[2]));
-        if (n_nodes > 0) {
-            const float4 a = __ldg(sc.nodes), b = __ldg(sc.nodes + 1), c = __ldg(sc.nodes + 2);
-            const float r[12] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, c.x, c.y, c.z, c.w};
-#pragma unroll
-            for (int k = 0; k < 2; k++)
-#pragma unroll
-                for (int q = 0; q < 3; q++) m = fmaxf(m, fabsf(r[6 * k + q]) + r[6 * k + 3 + q]);
-        }
-        pad = 1.220703125e-04f * m + 1e-6f;      /* 2^-13 */
-    }
+    const float pad = rs_cull_pad(sc, f.pos);
     const int x0 = bbx * RT_SMALL_BIN_W, y0 = bby * RT_SMALL_BIN_H;
     const int x1 = min(x0 + RT_SMALL_BIN_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_BIN_H - 1, f.imgh - 1);
     const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
@@ -393,10 +659,13 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
 __global__ void __launch_bounds__(256)
 rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
                      int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
-                     int work_tiles_x, int work_tiles_y, int wait_first) {
+                     int work_tiles_x, int work_tiles_y, int wait_first, uint4* __restrict__ lgrid,
+                     int n_cull_blocks) {
     if (wait_first) rs_griddep_wait();
     rs_griddep_launch();                         /* the tracer may start staging the scene */
-    rs_cull_bin(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y);
+    /* the CTAs behind the screen bins fill the light bins (lgrid != NULL), one coarse cell each */
+    if ((int)blockIdx.x >= n_cull_blocks) rs_light_cell(sc, f, lgrid, (int)blockIdx.x - n_cull_blocks);
+    else rs_cull_bin(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y);
     rs_griddep_wait();
 }
 
@@ -409,7 +678,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
                       unsigned int* __restrict__ tile_counter, const unsigned short* __restrict__ tile_lists,
                       int tiles_x, unsigned int n_tiles_all, int bins_x,
                       const unsigned int* __restrict__ work_list, int force_linear,
-                      const unsigned int* order_r, unsigned int* order_w) {
+                      const unsigned int* order_r, unsigned int* order_w, const uint4* __restrict__ lgrid) {
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
@@ -489,6 +758,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     }
     sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;   /* one slot above the top is scratch (rs_store) */
     sh.list = s_list[warp];
+    sh.lgrid = lgrid;
     sh.n_prims = n;
     sh.n_planes = sc.n_planes;
     sh.prims_off = prims_off;
@@ -632,7 +902,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
                                              int* hit_ids, RtCountersDev* counters, unsigned int* tile_counter,
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
                                              const unsigned int* order_r, unsigned int* order_w,
-                                             int after_own_post, cudaStream_t stream) {
+                                             int after_own_post, uint4* lgrid, cudaStream_t stream) {
     /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel.
      * after_own_post: the previous operation on the stream is the FXAA / copy kernel of this context's previous
      * frame (nothing this frame reads is still being written): the pre-pass overlaps it, see rt_cull_tiles_kernel */
@@ -652,12 +922,14 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.stream = stream;
     cfg.attrs = pdl;
     cfg.numAttrs = 1;
-    cfg.gridDim = dim3((bins + 7) / 8, 1, 1);
+    const int cull_blocks = (bins + 7) / 8;
+    const int lit = f->n_lights < RT_LGRID_LIGHTS ? f->n_lights : RT_LGRID_LIGHTS;    /* lights with bins */
+    cfg.gridDim = dim3(cull_blocks + (lgrid ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
     cfg.blockDim = dim3(256, 1, 1);
     cfg.dynamicSmemBytes = 0;
     cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins,
                                        sharded ? work_list : (unsigned int*)nullptr, tile_counter + RS_CNT_TILES, tiles_x,
-                                       tiles_y, after_own_post ? 0 : 1);
+                                       tiles_y, after_own_post ? 0 : 1, lgrid, cull_blocks);
     if (e != cudaSuccess) return e;
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     const int units = tiles * RT_SMALL_PATCHES;
@@ -667,8 +939,9 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.dynamicSmemBytes = smem;
     const unsigned int* wl = work_list;
     const unsigned short* tl = tile_lists;
-    if (count) e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<true>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w);
-    else       e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<false>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w);
+    const uint4* lg = lgrid;
+    if (count) e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<true>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg);
+    else       e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<false>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

@@ -145,6 +145,16 @@ class Renderer:
         self._check(self._lib.rt_get_counters(self._h, buf), "rt_get_counters")
         return {name: int(buf[i]) for i, name in enumerate(_lib.COUNTER_NAMES)}
 
+    def light_bins(self):
+        """Diagnostics: the light bins of the last small-scene frame as uint16[4 lights, 6 faces, 64, 64, 8]
+        ([..., 0] = count or 0xFFFF, [..., 1:] = leaf offsets), or None."""
+        import numpy as np
+        a = np.zeros((4, 6, 64, 64, 8), dtype=np.uint16)
+        n = self._lib.rt_debug_light_bins(self._h, a.ctypes.data, a.nbytes)
+        if n < 0:
+            self._check(int(-n), "rt_debug_light_bins")
+        return a if n == a.nbytes else None
+
     def timings(self):
         buf = (C.c_float * 3)()
         self._check(self._lib.rt_get_timings(self._h, buf), "rt_get_timings")

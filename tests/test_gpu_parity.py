@@ -195,6 +195,72 @@ def test_shared_memory_tracer_poses_shards_and_subsets():
         assert (img_a == img_b).all(), subset
 
 
+def _bins_on_off(r, s, f, objects=None, lights=None):
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 0)
+    a = gu.render(r, s, f, objects=objects, lights=lights)
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 1)
+    b = gu.render(r, s, f, objects=objects, lights=lights)
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 0)
+    return a, b
+
+
+def test_light_bins_change_tested_primitives_only():
+    """Shadow rays of the shared-memory tracer look up per-light direction bins (a cube map around each light
+    with the primitives a line of that direction can hit) instead of traversing the hierarchy
+    (RT_OPT_SHADOW_BINS 0).  Conservative culling: every frame must equal the traversal's (and, in the tests
+    above, the HBM tracer's and the oracle's) bit for bit -- all hours of both views, lights moved into and
+    under the scene, random clouds of spheres and triangles around the lights, more lights than have bins."""
+    r = gu.renderer()
+    s = rt.Scene()
+    for view in (5, 6):
+        for hours in np.arange(0.0, 24.0, 0.75):
+            f = s.configure(view=view, hours=float(hours), imgw=480, imgh=270, alias=False)
+            (img_a, ids_a), (img_b, ids_b) = _bins_on_off(r, s, f)
+            assert (ids_a == ids_b).all() and (img_a == img_b).all(), (view, hours, int((img_a != img_b).sum()))
+    # lights anywhere: inside the island, under the sea, next to triangles, far away
+    rng = np.random.default_rng(11)
+    f = s.configure(view=5, hours=14.0, imgw=320, imgh=180, alias=False)
+    for k in range(16):
+        lights = s.lights.copy()
+        for li in range(len(lights)):
+            lights[li]["pos"] = rng.uniform([-120, -20, -120], [120, 60, 120]) if k % 2 else \
+                rng.uniform([-900, -600, -900], [900, 900, 900])
+        (img_a, ids_a), (img_b, ids_b) = _bins_on_off(r, s, f, lights=lights)
+        assert (img_a == img_b).all(), (k, lights["pos"], int((img_a != img_b).sum()))
+        r.set_option(_lib.RT_OPT_TRACE_IMPL, 1)
+        img_c, _ = gu.render(r, s, f, lights=lights)
+        r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
+        assert (img_a == img_c).all(), (k, "hbm")
+    # random clouds: many small primitives stacked along the light directions (bins overflow -> traversal)
+    base = s.objects.copy()
+    for k in range(8):
+        n = int(rng.integers(20, 160))
+        o = np.zeros(n + 1, dtype=base.dtype)
+        o[0] = base[0]                                  # the sea plane
+        src_t = base[base["type"] == 2][0]
+        src_s = base[(base["type"] == 0) & (base["light"] == 0)][0]
+        for i in range(1, n + 1):
+            c = rng.uniform([-90, -2, 20], [-20, 40, 110])
+            if rng.random() < 0.5:
+                o[i] = src_s
+                o[i]["pos"] = c
+                o[i]["size"] = [rng.uniform(0.3, 6.0)] * 3
+            else:
+                o[i] = src_t
+                a, b = rng.normal(size=3) * rng.uniform(1, 12), rng.normal(size=3) * rng.uniform(1, 12)
+                o[i]["pos"], o[i]["size"], o[i]["third"] = c, c + a, c + b
+            o[i]["mirror"] = float(rng.choice([0.0, 0.3]))
+        (img_a, ids_a), (img_b, ids_b) = _bins_on_off(r, s, f, objects=o)
+        assert (ids_a == ids_b).all() and (img_a == img_b).all(), (k, n, int((img_a != img_b).sum()))
+    # five lights: the fifth has no bins and traverses
+    lights = np.concatenate([s.lights, s.lights, s.lights[:1]]).copy()
+    for li in range(5):
+        lights[li]["pos"] = rng.uniform([-300, 20, -300], [300, 500, 300])
+        lights[li]["intensity"] = 0.3
+    (img_a, _), (img_b, _) = _bins_on_off(r, s, f, lights=lights)
+    assert (img_a == img_b).all()
+
+
 def test_order_history_changes_scheduling_only():
     """Whole frames of the shared-memory tracer are walked most-expensive-patch-first using the costs the
     previous frame of the same size measured (RT_OPT_ORDER 0).  The frames must not depend on it: same pixels

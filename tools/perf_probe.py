@@ -16,6 +16,7 @@ r = rt.Renderer(0)
 r.set_sky(rt.synthetic_sky(2048, 1024))
 s = rt.Scene()
 r.set_option(_lib.RT_OPT_ORDER, int(os.environ.get("RTB_ORDER", "0")))
+r.set_option(_lib.RT_OPT_SHADOW_BINS, int(os.environ.get("RTB_SHADOW_BINS", "0")))
 out = torch.empty(w * h, dtype=torch.int32, device="cuda")
 for view in (5, 6):
     for tod in ("afternoon", "night"):
