@@ -18,6 +18,7 @@ RT_OPT_BUILDER = 6
 RT_OPT_FORCE_RADIX = 7
 RT_OPT_ORDER = 8
 RT_OPT_SHADOW_BINS = 9
+RT_OPT_MIRROR_BINS = 10
 RT_PEER_HANDLE_BYTES = 64
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",

@@ -37,7 +37,8 @@ cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned 
 cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
-                                  unsigned int* order_w, int after_own_post, uint4* lgrid, cudaStream_t stream);
+                                  unsigned int* order_w, int after_own_post, uint4* lgrid, int mirror_bins,
+                                  cudaStream_t stream);
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
@@ -524,7 +525,8 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
                                             ctx->scene_settled ? 1 : 0,
-                                            ctx->opt[RT_OPT_SHADOW_BINS] == 0 ? ctx->d_lgrid : (uint4*)nullptr, ctx->stream));
+                                            ctx->opt[RT_OPT_SHADOW_BINS] == 0 ? ctx->d_lgrid : (uint4*)nullptr,
+                                            ctx->opt[RT_OPT_MIRROR_BINS] == 0, ctx->stream));
     }
     else {
         RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,

@@ -51,6 +51,7 @@ struct RtSmallShared {
     unsigned int base;       /* shared address of the staged nodes (leaf records follow them) */
     unsigned int stack0;     /* shared address of this thread's stack column */
     const unsigned short* list;   /* primary candidates of the current tile: [0] count, then leaf byte offsets */
+    const unsigned short* mlist;  /* mirror bins: candidates of the rays primary rays of the tile send off plane 0 (NULL: off) */
     const uint4* lgrid;           /* light bins (NULL: shadow rays traverse the hierarchy) */
     int root, n_prims, n_planes, prims_off;
     bool deep;               /* hierarchy deeper than RT_SMALL_STACK: secondary rays loop linearly instead */
@@ -167,18 +168,20 @@ struct RtSmallScene {
         }
     }
     /* RtHit.slot: >= 0 leaf byte offset from `base`, < 0 ~plane index */
-    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, RtLocalCounters& cnt) {
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, int via, RtLocalCounters& cnt) {
         RtHit best;
         best.t = __int_as_float(0x7f800000);
         best.tag = RT_MISS;
         best.slot = 0;
         planes_closest(o, d, best, cnt);
-        if (depth == 0) {
-            /* primary ray: the tile's candidate list instead of the hierarchy */
-            const int n = s.list[0];
+        /* primary ray: the tile's candidate list instead of the hierarchy; the ray a primary ray sends off plane 0
+         * (via = ~0): the tile's mirror list (see `mirror bins`) */
+        const unsigned short* cand = depth == 0 ? s.list : ((depth == 1 && via == ~0) ? s.mlist : nullptr);
+        if (cand) {
+            const int n = cand[0];
             if (n != 0xFFFF) {
                 for (int i = 1; i <= n; i++) {
-                    const int off = s.list[i];
+                    const int off = cand[i];
                     float t;
                     unsigned int tag;
                     if (rs_test_record(s.base + off, o, d, t, tag, cnt, COUNT)) rt_consider(best, t, tag, off);
@@ -303,14 +306,13 @@ __device__ __forceinline__ RsFrustum rs_frustum_from_corners(const vec3* c) {
     return fr;
 }
 
-__device__ __forceinline__ RsFrustum rs_tile_frustum(const RtFrameDev& f, int x0, int y0, int x1, int y1) {
+/* corner directions of the tile [x0, x1] x [y0, y1] grown by one pixel on every side */
+__device__ __forceinline__ void rs_tile_corners(const RtFrameDev& f, int x0, int y0, int x1, int y1, vec3* c) {
     const float xa = (float)x0 - 1.0f, xb = (float)x1 + 1.0f, ya = (float)y0 - 1.0f, yb = (float)y1 + 1.0f;
-    vec3 c[4];
     c[0] = rs_primary_target(f, xa, ya);
     c[1] = rs_primary_target(f, xb, ya);
     c[2] = rs_primary_target(f, xb, yb);
     c[3] = rs_primary_target(f, xa, yb);
-    return rs_frustum_from_corners(c);
 }
 
 /* can any ray of the tile (origin `eye`, inside `fr`) hit leaf record `rec`? */
@@ -601,8 +603,8 @@ __device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFram
 __device__ __forceinline__ void
 rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restrict__ tile_lists, int tiles_x,
             int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
-            int work_tiles_x, int work_tiles_y) {
-    /* tiles_x, n_tiles count BINS here; work_list = NULL for whole frames */
+            int work_tiles_x, int work_tiles_y, unsigned short* __restrict__ mirror_lists) {
+    /* tiles_x, n_tiles count BINS here; work_list = NULL for whole frames; mirror_lists = NULL: no mirror bins */
     const int lane = threadIdx.x & 31;
     const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (tile >= n_tiles) return;
@@ -638,7 +640,9 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
     const int x0 = bbx * RT_SMALL_BIN_W, y0 = bby * RT_SMALL_BIN_H;
     const int x1 = min(x0 + RT_SMALL_BIN_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_BIN_H - 1, f.imgh - 1);
     const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
-    const RsFrustum fr = rs_tile_frustum(f, x0, y0, x1, y1);
+    vec3 corner[4];
+    rs_tile_corners(f, x0, y0, x1, y1, corner);
+    const RsFrustum fr = rs_frustum_from_corners(corner);
     unsigned short* __restrict__ out = tile_lists + (size_t)tile * RT_SMALL_LIST;
     int count = 0;
     for (int j0 = 0; j0 < n; j0 += 32) {
@@ -650,6 +654,63 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
         count += __popc(m);
     }
     if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
+
+    /* ---- mirror bins.  A primary ray that hits plane 0 (the reference's sea, scene.cpp:183-190) at P continues as
+     * P + 0.001 r, r = normalize(d - 2 (N.d) N) (kernel.cu:212-213).  With a unit normal that is the mirror image
+     * of the primary ray: its line passes through the eye's image E' behind the plane with the primary direction's
+     * image, so the rays a tile sends off the plane lie in the tile's frustum mirrored, apex E' -- the same cull as
+     * above with the mirrored corners, plus: nothing wholly on E's far side of the plane can be met (the ray starts on
+     * the plane and leaves it towards the eye's side).  Rounding: P sits within |t| 2^-22 (< 1e-3 world units) of
+     * the exact point and r within 2^-23 of the exact direction, both far inside the pad (2^-13 of the largest
+     * coordinate) every plane test here carries.  The exact leaf tests decide; bit-identical to the traversal. */
+    if (!mirror_lists) return;
+    unsigned short* __restrict__ mout = mirror_lists + (size_t)tile * RT_SMALL_LIST;
+    bool on = false;
+    vec3 pn = v3(0, 0, 0), p0 = v3(0, 0, 0);
+    float hgt = 0.0f;
+    if (sc.n_planes > 0 && fr.ok) {
+        const float4 q0 = __ldg(sc.planes), q1 = __ldg(sc.planes + 1);
+        const unsigned int tag = __float_as_uint(q0.w);
+        pn = f4xyz(q1);
+        p0 = f4xyz(q0);
+        const float mirror = __ldg(sc.mats + 2 * (tag & RT_TAG_INDEX)).w;
+        hgt = vdot(vsub(eye, p0), pn);
+        on = mirror > 0.0f && !(tag & RT_TAG_EMISSIVE) && fabsf(vdot(pn, pn) - 1.0f) <= 1e-6f;
+    }
+    if (!on) {
+        if (lane == 0) mout[0] = (unsigned short)0xFFFFu;       /* traverse */
+        return;
+    }
+    const vec3 eye_m = vsub(eye, vscale(pn, 2.0f * hgt));
+    vec3 corner_m[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) corner_m[k] = vsub(corner[k], vscale(pn, 2.0f * vdot(corner[k], pn)));
+    const RsFrustum frm = rs_frustum_from_corners(corner_m);
+    const float apex_m[3] = {eye_m.x, eye_m.y, eye_m.z};
+    const float pad_m = fmaxf(pad, rs_cull_pad(sc, apex_m));
+    const float side = hgt > pad_m ? 1.0f : (hgt < -pad_m ? -1.0f : 0.0f);   /* eye (nearly) in the plane: no side cull */
+    int mcount = 0;
+    for (int j0 = 0; j0 < n; j0 += 32) {
+        const int j = j0 + lane;
+        bool keep = j < n;
+        if (keep && frm.ok) keep = rs_tile_may_hit(frm, eye_m, sc.prims + 3 * j, pad_m);
+        if (keep && side != 0.0f) {
+            const float4 r0 = __ldg(sc.prims + 3 * j), r1 = __ldg(sc.prims + 3 * j + 1);
+            const float ha = side * vdot(vsub(f4xyz(r0), p0), pn);
+            if (__float_as_uint(r0.w) & RT_TAG_SPHERE) {
+                keep = !(ha < -(fabsf(r1.x) + pad_m));
+            } else {
+                const float4 r2 = __ldg(sc.prims + 3 * j + 2);
+                const float hb = ha + side * vdot(f4xyz(r1), pn), hc = ha + side * vdot(f4xyz(r2), pn);
+                keep = !(ha < -pad_m && hb < -pad_m && hc < -pad_m);
+            }
+        }
+        const unsigned int m = __ballot_sync(0xffffffffu, keep);
+        const int at = mcount + __popc(m & ((1u << lane) - 1u));
+        if (keep && at < RT_SMALL_LIST - 1) mout[1 + at] = (unsigned short)(prims_off + 48 * j);
+        mcount += __popc(m);
+    }
+    if (lane == 0) mout[0] = mcount < RT_SMALL_LIST ? (unsigned short)mcount : (unsigned short)0xFFFFu;
 }
 
 /* The pre-pass reads the scene and writes lists nobody else is using, so -- when the host knows that the
@@ -660,12 +721,12 @@ __global__ void __launch_bounds__(256)
 rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
                      int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
                      int work_tiles_x, int work_tiles_y, int wait_first, uint4* __restrict__ lgrid,
-                     int n_cull_blocks) {
+                     int n_cull_blocks, unsigned short* __restrict__ mirror_lists) {
     if (wait_first) rs_griddep_wait();
     rs_griddep_launch();                         /* the tracer may start staging the scene */
     /* the CTAs behind the screen bins fill the light bins (lgrid != NULL), one coarse cell each */
     if ((int)blockIdx.x >= n_cull_blocks) rs_light_cell(sc, f, lgrid, (int)blockIdx.x - n_cull_blocks);
-    else rs_cull_bin(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y);
+    else rs_cull_bin(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y, mirror_lists);
     rs_griddep_wait();
 }
 
@@ -678,11 +739,12 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
                       unsigned int* __restrict__ tile_counter, const unsigned short* __restrict__ tile_lists,
                       int tiles_x, unsigned int n_tiles_all, int bins_x,
                       const unsigned int* __restrict__ work_list, int force_linear,
-                      const unsigned int* order_r, unsigned int* order_w, const uint4* __restrict__ lgrid) {
+                      const unsigned int* order_r, unsigned int* order_w, const uint4* __restrict__ lgrid,
+                      const unsigned short* __restrict__ mirror_lists) {
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
-    __shared__ unsigned short s_list[RT_SMALL_WARPS][RT_SMALL_LIST];   /* per-warp primary candidates */
+    __shared__ unsigned short s_list[RT_SMALL_WARPS][2 * RT_SMALL_LIST];   /* per-warp primary + mirror candidates */
     extern __shared__ __align__(16) unsigned char smem[];
 
     const int tid = threadIdx.x;
@@ -758,6 +820,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     }
     sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;   /* one slot above the top is scratch (rs_store) */
     sh.list = s_list[warp];
+    sh.mlist = mirror_lists ? s_list[warp] + RT_SMALL_LIST : nullptr;
     sh.lgrid = lgrid;
     sh.n_prims = n;
     sh.n_planes = sc.n_planes;
@@ -793,6 +856,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
         const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
         s_list[warp][lane] = entry;
+        if (mirror_lists) s_list[warp][RT_SMALL_LIST + lane] = __ldg(mirror_lists + (size_t)bin * RT_SMALL_LIST + lane);
         __syncwarp();
         {
             const int x = x0 + (p % (RT_SMALL_TILE_W / 8)) * 8 + (lane & 7);
@@ -885,7 +949,7 @@ extern "C" cudaError_t rt_trace_small_init(void) {
 extern "C" size_t rt_trace_small_list_bytes(int imgw, int imgh) {
     const size_t bins = (size_t)((imgw + RT_SMALL_BIN_W - 1) / RT_SMALL_BIN_W) * ((imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H);
     const size_t tiles = (size_t)((imgw + RT_SMALL_TILE_W - 1) / RT_SMALL_TILE_W) * ((imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H);
-    return bins * RT_SMALL_LIST * sizeof(unsigned short) + tiles * sizeof(unsigned int);   /* bin lists + work list */
+    return 2 * bins * RT_SMALL_LIST * sizeof(unsigned short) + tiles * sizeof(unsigned int);   /* bin lists + work list + mirror lists */
 }
 
 extern "C" size_t rt_trace_small_patches(int imgw, int imgh) {
@@ -902,7 +966,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
                                              int* hit_ids, RtCountersDev* counters, unsigned int* tile_counter,
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
                                              const unsigned int* order_r, unsigned int* order_w,
-                                             int after_own_post, uint4* lgrid, cudaStream_t stream) {
+                                             int after_own_post, uint4* lgrid, int mirror_bins, cudaStream_t stream) {
     /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel.
      * after_own_post: the previous operation on the stream is the FXAA / copy kernel of this context's previous
      * frame (nothing this frame reads is still being written): the pre-pass overlaps it, see rt_cull_tiles_kernel */
@@ -914,6 +978,8 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const int tiles_y = (f->imgh + RT_SMALL_TILE_H - 1) / RT_SMALL_TILE_H;
     /* behind the bin lists: the work list of sharded frames (filled by the pre-pass) */
     unsigned int* work_list = (unsigned int*)(tile_lists + (size_t)bins * RT_SMALL_LIST);
+    /* behind the work list: the mirror lists of the bins */
+    unsigned short* mirror_lists = mirror_bins ? (unsigned short*)(work_list + tiles) : (unsigned short*)nullptr;
     const bool sharded = f->n_shards > 1;
     cudaLaunchAttribute pdl[1];
     pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -929,7 +995,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.dynamicSmemBytes = 0;
     cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins,
                                        sharded ? work_list : (unsigned int*)nullptr, tile_counter + RS_CNT_TILES, tiles_x,
-                                       tiles_y, after_own_post ? 0 : 1, lgrid, cull_blocks);
+                                       tiles_y, after_own_post ? 0 : 1, lgrid, cull_blocks, mirror_lists);
     if (e != cudaSuccess) return e;
     int grid = n_sm * RT_SMALL_CTAS_PER_SM;
     const int units = tiles * RT_SMALL_PATCHES;
@@ -940,8 +1006,9 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const unsigned int* wl = work_list;
     const unsigned short* tl = tile_lists;
     const uint4* lg = lgrid;
-    if (count) e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<true>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg);
-    else       e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<false>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg);
+    const unsigned short* ml = mirror_lists;
+    if (count) e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<true>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml);
+    else       e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<false>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

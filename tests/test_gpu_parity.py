@@ -261,6 +261,103 @@ def test_light_bins_change_tested_primitives_only():
     assert (img_a == img_b).all()
 
 
+def _mirror_on_off(r, s, f, objects=None, lights=None):
+    r.set_option(_lib.RT_OPT_MIRROR_BINS, 0)
+    a = gu.render(r, s, f, objects=objects, lights=lights)
+    r.set_option(_lib.RT_OPT_MIRROR_BINS, 1)
+    b = gu.render(r, s, f, objects=objects, lights=lights)
+    r.set_option(_lib.RT_OPT_MIRROR_BINS, 0)
+    return a, b
+
+
+def test_mirror_bins_change_tested_primitives_only():
+    """The ray a primary ray sends off plane 0 (the sea, reference scene.cpp:183-190; bounce at kernel.cu:209-215)
+    tests the candidate list of its screen bin's MIRRORED frustum (apex = the eye's image behind the plane)
+    instead of traversing the hierarchy (RT_OPT_MIRROR_BINS 0).  Conservative culling: every frame must equal
+    the traversal's bit for bit -- all hours of both views, the sea-level sweep of BASELINE config 3 (including
+    levels above the camera), cameras close to / under the plane, tilted unit and non-unit plane normals (the
+    latter switch the lists off), random clouds above and below the plane, no plane at all."""
+    r = gu.renderer()
+    s = rt.Scene()
+    for view in (5, 6):
+        for hours in np.arange(0.0, 24.0, 1.5):
+            f = s.configure(view=view, hours=float(hours), imgw=480, imgh=270, alias=False)
+            (img_a, ids_a), (img_b, ids_b) = _mirror_on_off(r, s, f)
+            assert (ids_a == ids_b).all() and (img_a == img_b).all(), (view, hours, int((img_a != img_b).sum()))
+    for sea in (-4.5, -2.5, -0.5, 1.5, 3.5, 5.5, 7.5, 9.5, 11.5, 12.40, 12.41, 12.42, 14.0, 40.0):
+        f = s.configure(view=6, hours=14.0, imgw=640, imgh=360, sea_level=sea, alias=False)
+        (img_a, ids_a), (img_b, ids_b) = _mirror_on_off(r, s, f)
+        assert (ids_a == ids_b).all() and (img_a == img_b).all(), (sea, int((img_a != img_b).sum()))
+    # against the HBM tracer too (it has no lists at all)
+    f = s.configure(view=5, hours=18.0, imgw=1920, imgh=1080, alias=False)
+    img_a, ids_a = gu.render(r, s, f)
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 1)
+    img_c, ids_c = gu.render(r, s, f)
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
+    assert (ids_a == ids_c).all() and (img_a == img_c).all()
+    # moving camera: over, on and under the sea, looking up and down
+    rng = np.random.default_rng(23)
+    s.configure(view=5, hours=10.0, imgw=320, imgh=180, alias=False)
+    for k in range(24):
+        pos = rng.uniform([-300, -30, -300], [400, 60, 300])
+        if k % 4 == 0:
+            pos[1] = -4.5 + rng.uniform(-0.02, 0.02)
+        s.set_pose(tuple(float(v) for v in pos), float(rng.uniform(0, 360)), float(rng.uniform(-44, 44)))
+        f = s.frame(320, 180)
+        (img_a, ids_a), (img_b, ids_b) = _mirror_on_off(r, s, f)
+        assert (ids_a == ids_b).all() and (img_a == img_b).all(), (k, pos, int((img_a != img_b).sum()))
+    # tilted planes: unit normals keep the lists, non-unit normals (not a reflection any more) switch them off
+    f = s.configure(view=5, hours=14.0, imgw=320, imgh=180, alias=False)
+    base = s.objects.copy()
+    for k in range(12):
+        o = base.copy()
+        nrm = np.array([rng.uniform(-0.4, 0.4), 1.0, rng.uniform(-0.4, 0.4)])
+        nrm = nrm / np.linalg.norm(nrm)
+        if k % 3 == 1:
+            nrm = nrm * rng.uniform(0.5, 2.0)
+        if k % 3 == 2:
+            nrm = -nrm
+        o[0]["size"] = nrm.astype(np.float32)
+        o[0]["pos"] = [rng.uniform(-50, 50), rng.uniform(-8, 3), rng.uniform(-50, 50)]
+        (img_a, ids_a), (img_b, ids_b) = _mirror_on_off(r, s, f, objects=o)
+        assert (ids_a == ids_b).all() and (img_a == img_b).all(), (k, nrm, int((img_a != img_b).sum()))
+    # random clouds around the plane (lists overflow -> traversal), and a scene without any plane
+    for k in range(8):
+        n = int(rng.integers(10, 200))
+        o = np.zeros(n + 1, dtype=base.dtype)
+        o[0] = base[0]
+        src_t = base[base["type"] == 2][0]
+        src_s = base[(base["type"] == 0) & (base["light"] == 0)][0]
+        for i in range(1, n + 1):
+            c = rng.uniform([-110, -12, 10], [0, 30, 130])
+            if rng.random() < 0.4:
+                o[i] = src_s
+                o[i]["pos"] = c
+                o[i]["size"] = [rng.uniform(0.3, 5.0)] * 3
+            else:
+                o[i] = src_t
+                a, b = rng.normal(size=3) * rng.uniform(1, 15), rng.normal(size=3) * rng.uniform(1, 15)
+                o[i]["pos"], o[i]["size"], o[i]["third"] = c, c + a, c + b
+            o[i]["mirror"] = float(rng.choice([0.0, 0.4]))
+        if k == 7:
+            o = o[1:]
+        (img_a, ids_a), (img_b, ids_b) = _mirror_on_off(r, s, f, objects=o)
+        assert (ids_a == ids_b).all() and (img_a == img_b).all(), (k, n, int((img_a != img_b).sum()))
+        r.set_option(_lib.RT_OPT_TRACE_IMPL, 1)
+        img_c, _ = gu.render(r, s, f, objects=o)
+        r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
+        assert (img_a == img_c).all(), (k, "hbm")
+    # a sharded frame uses the same lists
+    f = s.configure(view=6, hours=14.0, imgw=640, imgh=360, alias=True)
+    r.set_scene(s.objects, s.lights)
+    sh = rt.make_shard(2, 1, 64, 32)
+    img_a = r.render_to_host(f, shard=sh, out=np.zeros(640 * 360, dtype=np.uint32)).copy()
+    r.set_option(_lib.RT_OPT_MIRROR_BINS, 1)
+    img_b = r.render_to_host(f, shard=sh, out=np.zeros(640 * 360, dtype=np.uint32)).copy()
+    r.set_option(_lib.RT_OPT_MIRROR_BINS, 0)
+    assert (img_a == img_b).all() and img_a.any()
+
+
 def test_order_history_changes_scheduling_only():
     """Whole frames of the shared-memory tracer are walked most-expensive-patch-first using the costs the
     previous frame of the same size measured (RT_OPT_ORDER 0).  The frames must not depend on it: same pixels

@@ -17,10 +17,11 @@ r.set_sky(rt.synthetic_sky(2048, 1024))
 s = rt.Scene()
 r.set_option(_lib.RT_OPT_ORDER, int(os.environ.get("RTB_ORDER", "0")))
 r.set_option(_lib.RT_OPT_SHADOW_BINS, int(os.environ.get("RTB_SHADOW_BINS", "0")))
+r.set_option(_lib.RT_OPT_MIRROR_BINS, int(os.environ.get("RTB_MIRROR_BINS", "0")))
 out = torch.empty(w * h, dtype=torch.int32, device="cuda")
 for view in (5, 6):
     for tod in ("afternoon", "night"):
-        for builder in (1, 2):
+        for builder in ((1, 2) if os.environ.get("RTB_BOTH_BUILDERS") else (2,)):
             r.set_option(_lib.RT_OPT_BUILDER, builder)
             f = s.configure(view=view, hours=rt.TIME_PRESETS[tod], imgw=w, imgh=h, alias=True)
             r.set_scene(s.objects, s.lights)
