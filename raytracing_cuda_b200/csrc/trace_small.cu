@@ -521,7 +521,8 @@ __device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFram
     __shared__ float4 s_prim[RT_SMALL_MAX_PRIMS * RS_LG_PRIM_F4];
     __shared__ unsigned short s_slot[RT_SMALL_MAX_PRIMS];
     __shared__ unsigned short s_warp[8][RT_SMALL_MAX_PRIMS];
-    __shared__ int s_n;
+    __shared__ unsigned int s_mask[8][RT_SMALL_MAX_PRIMS];     /* per (warp, survivor): the bins of the warp's block it can hit */
+    __shared__ int s_n, s_nw[8];
     const int li = cell_id / RS_LG_BLOCKS_PER_LIGHT, rr = cell_id - li * RS_LG_BLOCKS_PER_LIGHT;
     const int face = rr / (RS_LG_CELLS * RS_LG_CELLS), cell = rr - face * (RS_LG_CELLS * RS_LG_CELLS);
     const int cy = cell / RS_LG_CELLS, cx = cell - cy * RS_LG_CELLS;
@@ -569,21 +570,44 @@ __device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFram
         }
         __syncwarp();
     }
-    const int gx = wx + (lane & 7), gy = wy + (lane >> 3);
-    unsigned int w[4] = {0u, 0u, 0u, 0u};
-    int count = 0;
-    if (nw) {
-        const int prims_off = 64 * (n > 1 ? n - 1 : 0);
-        const RsLgRect rb = rs_lg_rect((float)gx, (float)gy, (float)(gx + 1), (float)(gy + 1));
-        for (int k0 = 0; k0 < nw; k0++) {
-            const int i = s_warp[warp][k0];
+    /* Level 3, shared by the whole CTA: the (warp, survivor) pairs of all eight warps are dealt round-robin, lane =
+     * bin of that warp's 8x4 block, one ballot per pair.  (Each warp walking its own survivors left the cell to its
+     * densest warp: 24..52 survivors at ~800 cycles each for a lone warp, 12..20 us -- the whole pre-pass.) */
+    if (lane == 0) s_nw[warp] = nw;
+    __syncthreads();
+    {
+        int pw = 0, pbase = 0, pend = s_nw[0];          /* pairs [pbase, pend) belong to warp pw */
+        int total = 0;
+#pragma unroll
+        for (int q = 0; q < 8; q++) total += s_nw[q];
+        RsLgRect rb;
+        int have_rect = -1;
+        for (int pr = warp; pr < total; pr += 8) {
+            while (pr >= pend) { pw++; pbase = pend; pend += s_nw[pw]; }
+            if (have_rect != pw) {
+                const int bx = cx * RS_LG_CELL + 8 * (pw & 1) + (lane & 7), by = cy * RS_LG_CELL + 4 * (pw >> 1) + (lane >> 3);
+                rb = rs_lg_rect((float)bx, (float)by, (float)(bx + 1), (float)(by + 1));
+                have_rect = pw;
+            }
+            const int i = s_warp[pw][pr - pbase];
             union { RsLgPrim p; float4 q[RS_LG_PRIM_F4]; } u;
 #pragma unroll
             for (int k = 0; k < (int)RS_LG_PRIM_F4; k++) u.q[k] = s_prim[i * RS_LG_PRIM_F4 + k];
-            if (!rs_lg_may_hit(u.p, rb, pad)) continue;
+            const unsigned int hit = __ballot_sync(0xffffffffu, rs_lg_may_hit(u.p, rb, pad));
+            if (lane == 0) s_mask[pw][pr - pbase] = hit;
+        }
+    }
+    __syncthreads();
+    const int gx = wx + (lane & 7), gy = wy + (lane >> 3);
+    unsigned int w[4] = {0u, 0u, 0u, 0u};
+    int count = 0;
+    {
+        const int prims_off = 64 * (n > 1 ? n - 1 : 0);
+        for (int k0 = 0; k0 < nw; k0++) {
+            if (!((s_mask[warp][k0] >> lane) & 1u)) continue;
             count++;
             if (count < 8) {
-                const unsigned int off = (unsigned int)(prims_off + 48 * (int)s_slot[i]);
+                const unsigned int off = (unsigned int)(prims_off + 48 * (int)s_slot[s_warp[warp][k0]]);
 #pragma unroll
                 for (int k = 1; k < 8; k++)                  /* static register indices */
                     if (k == count) w[k >> 1] |= off << (16 * (k & 1));
