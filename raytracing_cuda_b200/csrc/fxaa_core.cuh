@@ -11,8 +11,16 @@
 
 #include <cuda_runtime.h>
 
+/* byte k of c as a float, exactly: the byte is permuted into the mantissa of 2^23 and 2^23 subtracted (PRMT on the
+ * ALU pipe + FADD on the FMA pipe, both full rate; I2F.U8 issues at a quarter of that and bounded the luminance
+ * phase) */
+template <int K>
+__device__ __forceinline__ float fx_byte(unsigned int c) {
+    return __fadd_rn(__uint_as_float(__byte_perm(c, 0x4B000000u, 0x7650 + K)), -8388608.0f);
+}
+
 __device__ __forceinline__ float fx_lum(unsigned int c) {
-    const float r = (float)(c & 255u), g = (float)((c >> 8) & 255u), b = (float)((c >> 16) & 255u);
+    const float r = fx_byte<0>(c), g = fx_byte<1>(c), b = fx_byte<2>(c);
     float l = __fmaf_rn(b, 0.0721750f, __fmaf_rn(r, 0.2126729f, __fmul_rn(g, 0.7151522f)));
     return __fmul_rn(fminf(l, 255.0f), 0.0039215688593685626984f);
 }
@@ -61,9 +69,9 @@ __device__ __forceinline__ bool fx_decide(float M, float E, float W, float N, fl
 
 __device__ __forceinline__ unsigned int fx_blend(unsigned int centre, unsigned int nb, float b) {
     const float omb = __fadd_rn(1.0f, -b);
-    const float r = __fmaf_rn(omb, (float)(centre & 255u), __fmul_rn(b, (float)(nb & 255u)));
-    const float g = __fmaf_rn(omb, (float)((centre >> 8) & 255u), __fmul_rn(b, (float)((nb >> 8) & 255u)));
-    const float bl = __fmaf_rn(omb, (float)((centre >> 16) & 255u), __fmul_rn(b, (float)((nb >> 16) & 255u)));
+    const float r = __fmaf_rn(omb, fx_byte<0>(centre), __fmul_rn(b, fx_byte<0>(nb)));
+    const float g = __fmaf_rn(omb, fx_byte<1>(centre), __fmul_rn(b, fx_byte<1>(nb)));
+    const float bl = __fmaf_rn(omb, fx_byte<2>(centre), __fmul_rn(b, fx_byte<2>(nb)));
     return fx_pack(r, g, bl);
 }
 
