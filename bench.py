@@ -187,6 +187,11 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
+    # stdout carries the one JSON line only: whatever libraries write to file descriptor 1 meanwhile (NCCL prints
+    # its version banner there at N >= 4) goes to stderr; the line itself is written to the saved descriptor
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import raytracing_cuda_b200 as rt
@@ -397,7 +402,8 @@ def main():
                                 "sample": "%d x rows y%%%d==0 of the 4 frames (%d rays each), FXAA skipped, %.1f s" % (
                                     reps, y_step, rays, dt)}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if dist is not None:
         dist.destroy_process_group()
     return 0
