@@ -223,7 +223,7 @@ int rt_destroy(rt_context* ctx) {
     }
     RtBuildBuffers& b = ctx->bb;
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
-                    b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.flags, b.node_aux,
+                    b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.node_other, b.flags, b.node_aux,
                     b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists, ctx->d_order, ctx->d_lgrid};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -373,6 +373,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
         RT_CHECK(ctx, regrow(&b.children, c));
         RT_CHECK(ctx, regrow(&b.node_parent, c));
         RT_CHECK(ctx, regrow(&b.leaf_parent, c));
+        RT_CHECK(ctx, regrow(&b.node_other, c));
         RT_CHECK(ctx, regrow(&b.flags, c));
         RT_CHECK(ctx, regrow(&b.node_aux, c * 12));
         RT_CHECK(ctx, regrow(&b.nodes, c * 16));

@@ -133,10 +133,27 @@ __global__ void rt_setup_kernel(const float* __restrict__ objs, int n_objects, c
                                 unsigned int* __restrict__ bounds) {
     /* the block's objects (68 B each, array of structures) through shared memory: coalesced loads, and a
      * stride of 17 words per thread is free of bank conflicts */
-    __shared__ float s_obj[17 * RT_BUILD_THREADS];
+    __shared__ __align__(16) float s_obj[17 * RT_BUILD_THREADS];
     const int first = blockIdx.x * blockDim.x;
     const int here = min((int)blockDim.x, n_objects - first);
-    for (int k = threadIdx.x; k < 17 * here; k += blockDim.x) s_obj[k] = __ldg(objs + (size_t)first * 17 + k);
+    if (here == RT_BUILD_THREADS && blockDim.x == RT_BUILD_THREADS && ((uintptr_t)objs & 15) == 0) {
+        /* full block: 17,408 B = 1,088 float4 from a 16-byte aligned start, all of a thread's loads in flight at
+         * once (the word-by-word loop below kept one load per thread in flight: 71 % of the kernel's stalls) */
+        const float4* __restrict__ src = (const float4*)(objs + (size_t)first * 17);
+        float4 v[5];
+#pragma unroll
+        for (int q = 0; q < 5; q++) {
+            const int k = threadIdx.x + RT_BUILD_THREADS * q;
+            if (k < 17 * RT_BUILD_THREADS / 4) v[q] = __ldg(src + k);
+        }
+#pragma unroll
+        for (int q = 0; q < 5; q++) {
+            const int k = threadIdx.x + RT_BUILD_THREADS * q;
+            if (k < 17 * RT_BUILD_THREADS / 4) ((float4*)s_obj)[k] = v[q];
+        }
+    } else {
+        for (int k = threadIdx.x; k < 17 * here; k += blockDim.x) s_obj[k] = __ldg(objs + (size_t)first * 17 + k);
+    }
     __syncthreads();
     const int i = first + threadIdx.x;
     /* neutral elements for the warp-level bounds reduction */
@@ -203,50 +220,40 @@ rs_hist_kernel(const unsigned int* __restrict__ keys, int n, int shift, unsigned
     hist[threadIdx.x * n_blocks + blockIdx.x] = s_h[threadIdx.x];
 }
 
-/* exclusive scan of hist[256][n_blocks] (bin-major) in place, one block of 32 warps: warp w owns bins
- * 8w .. 8w+7.  Pass 1: bin totals (coalesced 32-wide reads); scan of the 256 totals; pass 2: running exclusive
- * scan inside each bin.  (The first version walked the flat array in 1024-element steps with four barriers
- * each: 61 us for 62,720 counters of a 1M-key sort, a third of the whole sort.) */
-__global__ void __launch_bounds__(1024) rs_scan_kernel(unsigned int* __restrict__ hist, int n_blocks) {
-    __shared__ unsigned int s_base[256];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int b = 8 * warp; b < 8 * warp + 8; b++) {
-        unsigned int sum = 0;
-        for (int j = lane; j < n_blocks; j += 32) sum += hist[(size_t)b * n_blocks + j];
-        sum = __reduce_add_sync(0xFFFFFFFFu, sum);
-        if (lane == 0) s_base[b] = sum;
-    }
-    __syncthreads();
-    if (warp == 0) {                             /* exclusive scan of the 256 bin totals: 8 per lane */
-        unsigned int v[8], run = 0;
+/* exclusive scan of every bin's row hist[bin][0 .. n_blocks) in place, one WARP per bin (32 blocks of 8 warps),
+ * bin totals to hist[256 n_blocks + bin]; the scatter kernel adds the exclusive scan of the 256 totals itself.
+ * Four independent 32-wide loads are in flight per step.  (History: a flat single-CTA scan with four barriers per
+ * 1024 counters took 61 us for the 62,720 counters of a 1M-key sort; one CTA with 8 bins per warp and two walks
+ * over every row 21 us -- 128 dependent L2 round trips per warp.) */
+__global__ void __launch_bounds__(256) rs_scan_kernel(unsigned int* __restrict__ hist, int n_blocks) {
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x * 8 + (threadIdx.x >> 5);
+    unsigned int* __restrict__ row = hist + (size_t)b * n_blocks;
+    unsigned int carry = 0;
+    for (int j0 = 0; j0 < n_blocks; j0 += 128) {
+        unsigned int v[4], s[4];
 #pragma unroll
-        for (int k = 0; k < 8; k++) { v[k] = s_base[8 * lane + k]; run += v[k]; }
-        unsigned int incl = run;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-            if (lane >= o) incl += t;
+        for (int q = 0; q < 4; q++) {
+            const int j = j0 + 32 * q + lane;
+            v[q] = j < n_blocks ? row[j] : 0u;
         }
-        unsigned int excl = incl - run;
 #pragma unroll
-        for (int k = 0; k < 8; k++) { s_base[8 * lane + k] = excl; excl += v[k]; }
-    }
-    __syncthreads();
-    for (int b = 8 * warp; b < 8 * warp + 8; b++) {
-        unsigned int carry = s_base[b];
-        for (int j0 = 0; j0 < n_blocks; j0 += 32) {
-            const int j = j0 + lane;
-            const unsigned int v = j < n_blocks ? hist[(size_t)b * n_blocks + j] : 0u;
-            unsigned int s = v;
+        for (int q = 0; q < 4; q++) {
+            s[q] = v[q];
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, s, o);
-                if (lane >= o) s += t;
+                const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, s[q], o);
+                if (lane >= o) s[q] += t;
             }
-            if (j < n_blocks) hist[(size_t)b * n_blocks + j] = carry + s - v;
-            carry += __shfl_sync(0xFFFFFFFFu, s, 31);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int j = j0 + 32 * q + lane;
+            if (j < n_blocks) row[j] = carry + s[q] - v[q];
+            carry += __shfl_sync(0xFFFFFFFFu, s[q], 31);
         }
     }
+    if (lane == 0) hist[(size_t)256 * n_blocks + b] = carry;
 }
 
 /* stable ranked scatter.  Warp w owns the contiguous chunk [w*512, (w+1)*512) of the block's
@@ -256,6 +263,7 @@ rs_scatter_kernel(const unsigned int* __restrict__ keys_in, const unsigned int* 
                   unsigned int* __restrict__ keys_out, unsigned int* __restrict__ vals_out, int n, int shift,
                   const unsigned int* __restrict__ hist, int n_blocks) {
     __shared__ unsigned int s_cnt[RS_WARPS][256];
+    __shared__ unsigned int s_tot[RS_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < RS_WARPS * 256; i += RS_THREADS) (&s_cnt[0][0])[i] = 0;
     __syncthreads();
@@ -283,10 +291,23 @@ rs_scatter_kernel(const unsigned int* __restrict__ keys_in, const unsigned int* 
         __syncwarp();
     }
     __syncthreads();
-    /* digit d = threadIdx.x: exclusive prefix over warps + global base */
+    /* digit d = threadIdx.x: exclusive prefix over warps + global base = (keys with a smaller digit: exclusive
+     * scan of the 256 bin totals, 8 warp scans + their totals through s_tot) + (this digit in earlier blocks) */
     {
         const unsigned int d = threadIdx.x;
-        unsigned int run = hist[d * n_blocks + blockIdx.x];
+        const unsigned int tot = hist[(size_t)256 * n_blocks + d];
+        unsigned int incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_tot[warp] = incl;
+        __syncthreads();
+        unsigned int before = incl - tot;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) before += w < warp ? s_tot[w] : 0u;
+        unsigned int run = before + hist[d * n_blocks + blockIdx.x];
 #pragma unroll
         for (int w = 0; w < RS_WARPS; w++) {
             const unsigned int c = s_cnt[w][d];
@@ -350,7 +371,7 @@ extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* val
     for (int pass = 0; pass < 4; pass++) {
         const int shift = pass * 8;
         rs_hist_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, n, shift, hist, n_blocks);
-        rs_scan_kernel<<<1, 1024, 0, stream>>>(hist, n_blocks);
+        rs_scan_kernel<<<32, 256, 0, stream>>>(hist, n_blocks);
         rs_scatter_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, vi, ko, vo, n, shift, hist, n_blocks);
         unsigned int* t = ki; ki = ko; ko = t;
         t = vi; vi = vo; vo = t;
@@ -358,7 +379,7 @@ extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* val
     return cudaGetLastError();   /* 4 passes: result is back in keys/vals */
 }
 
-extern "C" int rt_radix_hist_entries(int n) { return 256 * ((n + RS_TILE - 1) / RS_TILE); }
+extern "C" int rt_radix_hist_entries(int n) { return 256 * ((n + RS_TILE - 1) / RS_TILE) + 256; }   /* rows + bin totals */
 
 /* ------------------------------------------------------------------ hierarchy */
 
@@ -373,7 +394,8 @@ __device__ __forceinline__ int rt_delta(const unsigned int* __restrict__ keys, i
 /* children: >=0 internal node, <0 leaf slot (~c).  parent of internal node i in node_parent[i],
  * of leaf slot j in leaf_parent[j].  Root is internal node 0. */
 __global__ void rt_karras_kernel(const unsigned int* __restrict__ keys, int n, int2* __restrict__ children,
-                                 int* __restrict__ node_parent, int* __restrict__ leaf_parent) {
+                                 int* __restrict__ node_parent, int* __restrict__ leaf_parent,
+                                 int* __restrict__ node_other) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     if (i == 0) node_parent[0] = -1;
@@ -393,6 +415,7 @@ __global__ void rt_karras_kernel(const unsigned int* __restrict__ keys, int n, i
     }
     const int gamma = i + s * d + min(d, 0);
     const int lo = min(i, j), hi = max(i, j);
+    node_other[i] = j;                       /* node i covers the sorted leaves [min(i, j), max(i, j)] */
     int c0, c1;
     if (lo == gamma) { c0 = ~gamma; leaf_parent[gamma] = i; }
     else             { c0 = gamma; node_parent[gamma] = i; }
@@ -487,19 +510,102 @@ __device__ __forceinline__ void rt_refit_leaf(int j, int n, const unsigned int* 
     *depth_out = (int)height;                /* only the thread that reached the root gets here */
 }
 
-__global__ void rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
-                                const int* __restrict__ bvh_src, const float4* __restrict__ recs,
-                                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
-                                const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
-                                const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
-                                unsigned int* __restrict__ flags, float* __restrict__ nodes,
-                                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+/* Full-size refit.  A Karras node covers a contiguous range of sorted leaves (node_other: its other end), so a
+ * block of RT_BUILD_THREADS consecutive leaves owns every node whose range lies inside its own: those (255 of 256)
+ * are joined through shared memory -- both arrivals park their box there, block-scope fence, shared atomic --
+ * and only the nodes that straddle blocks take the global protocol of rt_refit_leaf (device-scope fence + L2
+ * atomic + 12 scalar stores per arrival, which held a 1M-leaf refit at 192 us).  node_other[i] < 0 (PLOC
+ * topology: ranges unknown) sends a node to the global protocol. */
+__global__ void __launch_bounds__(RT_BUILD_THREADS)
+rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
+                const int* __restrict__ bvh_src, const float4* __restrict__ recs,
+                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
+                const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
+                const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
+                const int* __restrict__ node_other, unsigned int* __restrict__ flags, float* __restrict__ nodes,
+                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
+    __shared__ unsigned int s_flags[RT_BUILD_THREADS];
+    __shared__ float s_box[RT_BUILD_THREADS][12];    /* per block-owned node: both children's exact (lo, hi) */
+    const int b0 = blockIdx.x * blockDim.x, b1 = min(b0 + (int)blockDim.x, n);
+    const int j = b0 + threadIdx.x;
+    s_flags[threadIdx.x] = 0u;
+    __syncthreads();
     if (j >= n) return;
     const float extent = fmaxf(fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), ord2f(bounds[4]) - ord2f(bounds[1])),
                                ord2f(bounds[5]) - ord2f(bounds[2]));
-    rt_refit_leaf<false>(j, n, sorted_vals, bvh_src, recs, prim_lo, prim_hi, extent, ord2f(bounds[6]), children,
-                         node_parent, leaf_parent, flags, nodes, node_aux, prims, depth_out);
+    const float maxabs = ord2f(bounds[6]);
+    const int k = (int)sorted_vals[j];
+    const int obj = bvh_src[k];
+    prims[3 * j] = recs[3 * obj];
+    prims[3 * j + 1] = recs[3 * obj + 1];
+    prims[3 * j + 2] = recs[3 * obj + 2];
+    if (n < 2) {
+        *depth_out = 0;
+        return;
+    }
+    const float4 plo = prim_lo[k], phi = prim_hi[k];
+    const float global_pad = 9.5367431640625e-07f * fmaxf(extent, maxabs);   /* 2^-20 */
+    const float kRel = 3.0517578125e-05f;                                     /* 2^-15 */
+    float3 lo, hi;
+    {
+        const float px = kRel * fmaxf(fabsf(plo.x), fabsf(phi.x)) + global_pad;
+        const float py = kRel * fmaxf(fabsf(plo.y), fabsf(phi.y)) + global_pad;
+        const float pz = kRel * fmaxf(fabsf(plo.z), fabsf(phi.z)) + global_pad;
+        lo = make_float3(plo.x - px, plo.y - py, plo.z - pz);
+        hi = make_float3(phi.x + px, phi.y + py, phi.z + pz);
+    }
+    int child = ~j;
+    int node = leaf_parent[j];
+    unsigned int height = 0;                 /* of the subtree being carried up (leaf = 0) */
+    while (node >= 0) {
+        /* the three topology words of this level travel together (one L2 round trip per level, not two) */
+        const int2 ch = __ldg(children + node);
+        const int other = __ldg(node_other + node);
+        const int parent = __ldg(node_parent + node);
+        const int which = (ch.x == child) ? 0 : 1;
+        const bool local = other >= 0 && min(node, other) >= b0 && max(node, other) < b1;
+        float* rec = nodes + 16 * (size_t)node;
+        if (local) {
+            /* traversal record of this child: centre / half-extent rounded outward (rt_store_child_box) + link;
+             * plain stores, read by nobody before the kernel ends */
+            const float grow = 1.0f + 4.76837158203125e-07f;   /* 1 + 2^-21 */
+            const float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
+            const float ex = fmaxf(hi.x - cx, cx - lo.x) * grow, ey = fmaxf(hi.y - cy, cy - lo.y) * grow,
+                        ez = fmaxf(hi.z - cz, cz - lo.z) * grow;
+            float2* r2 = (float2*)(rec + 6 * which);             /* 24-byte offset: 8-byte aligned */
+            r2[0] = make_float2(cx, cy); r2[1] = make_float2(cz, ex); r2[2] = make_float2(ey, ez);
+            rec[12 + which] = __int_as_float(which == 0 ? ch.x : ch.y);
+            const int ln = node - b0;        /* a node is an end of its own range: inside the block too */
+            volatile float* sb = s_box[ln] + 6 * which;
+            sb[0] = lo.x; sb[1] = lo.y; sb[2] = lo.z; sb[3] = hi.x; sb[4] = hi.y; sb[5] = hi.z;
+            __threadfence_block();
+            /* bit 0..7: arrivals, bits 8..: height of the first arrival's subtree */
+            const unsigned int old = atomicAdd(&s_flags[ln], 1u + (height << 8));
+            if (old == 0u) return;                           /* first arrival: the sibling will carry on */
+            height = max(height, old >> 8) + 1u;
+            volatile const float* ob = s_box[ln] + 6 * (which ^ 1);
+            lo = make_float3(fminf(lo.x, ob[0]), fminf(lo.y, ob[1]), fminf(lo.z, ob[2]));
+            hi = make_float3(fmaxf(hi.x, ob[3]), fmaxf(hi.y, ob[4]), fmaxf(hi.z, ob[5]));
+        } else {
+            float* aux = node_aux + 12 * (size_t)node;
+            rt_store_child_box<false>(rec, aux, which, lo, hi);
+            if (which == 0) __stcg(rec + 12, __int_as_float(ch.x));
+            else            __stcg(rec + 13, __int_as_float(ch.y));
+            __threadfence();
+            /* bit 0..7: arrivals, bits 8..: height of the first arrival's subtree */
+            const unsigned int old = atomicAdd(&flags[node], 1u + (height << 8));
+            if (old == 0u) return;                           /* first arrival: the sibling will carry on */
+            height = max(height, old >> 8) + 1u;
+            const float* oa = aux + 6 * (which ^ 1);
+            const float olx = __ldcg(oa + 0), oly = __ldcg(oa + 1), olz = __ldcg(oa + 2);
+            const float ohx = __ldcg(oa + 3), ohy = __ldcg(oa + 4), ohz = __ldcg(oa + 5);
+            lo = make_float3(fminf(lo.x, olx), fminf(lo.y, oly), fminf(lo.z, olz));
+            hi = make_float3(fmaxf(hi.x, ohx), fmaxf(hi.y, ohy), fmaxf(hi.z, ohz));
+        }
+        child = node;
+        node = parent;
+    }
+    *depth_out = (int)height;                /* only the thread that reached the root gets here */
 }
 
 /* Small scenes (<= RT_FUSED_MAX objects), topology unchanged: bounds + setup + refit in ONE single-CTA launch,
@@ -751,12 +857,14 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         cudaError_t e = rt_radix_sort_pairs(b->keys, b->vals, b->tmp_keys, b->tmp_vals, b->hist, n, force_radix, stream);
         if (e != cudaSuccess) return e;
         if (n >= 2) {
-            if (builder != 1 && n <= PLOC_MAX)
+            if (builder != 1 && n <= PLOC_MAX) {
+                /* PLOC nodes cover no contiguous leaf range: every join of the refit takes the global protocol */
+                cudaMemsetAsync(b->node_other, 0xFF, sizeof(int) * (size_t)(n - 1), stream);
                 rt_ploc_small_kernel<<<1, PLOC_MAX, 0, stream>>>(b->vals, n, b->prim_lo, b->prim_hi, b->children,
                                                                  b->node_parent, b->leaf_parent);
-            else
+            } else
                 rt_karras_kernel<<<(n - 1 + T - 1) / T, T, 0, stream>>>(b->keys, n, b->children, b->node_parent,
-                                                                        b->leaf_parent);
+                                                                        b->leaf_parent, b->node_other);
         }
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
@@ -766,7 +874,7 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         if (e != cudaSuccess) return e;
     }
     rt_refit_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
-                                                      b->children, b->node_parent, b->leaf_parent, b->flags, b->nodes,
-                                                      b->node_aux, b->prims, b->depth);
+                                                      b->children, b->node_parent, b->leaf_parent, b->node_other, b->flags,
+                                                      b->nodes, b->node_aux, b->prims, b->depth);
     return cudaGetLastError();
 }

@@ -106,6 +106,7 @@ struct RtBuildBuffers {
     unsigned int* bounds;
     unsigned int *keys, *vals, *tmp_keys, *tmp_vals, *hist;
     int2* children; int *node_parent, *leaf_parent;
+    int* node_other;   /* Karras: node i covers the sorted leaves between i and node_other[i]; -1: unknown (PLOC) */
     unsigned int* flags;
     float* nodes; float* node_aux; float4* prims;
     int* depth;
