@@ -127,7 +127,8 @@ int  rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard,
 /* Same, result copied to HOST memory (pinned or pageable); synchronous. */
 int  rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* shard,
                        unsigned int* out_host, int* hit_ids_host);
-/* The pre-FXAA image of the last rt_render (device pointer owned by ctx). */
+/* The pre-FXAA image of the last rt_render (device pointer owned by ctx; for a whole frame with alias = 0 the
+ * tracer writes the caller's out_dev directly and that pointer is returned). */
 int  rt_get_base_image(rt_context* ctx, unsigned int** base_dev);
 /* FXAA alone: in_dev -> out_dev (reference kernel.cu:262-403 with alias=true). */
 int  rt_fxaa(rt_context* ctx, const unsigned int* in_dev, unsigned int* out_dev,

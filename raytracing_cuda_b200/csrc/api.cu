@@ -95,6 +95,7 @@ struct rt_context {
     /* every write to the scene buffers completes before the last kernel enqueued by rt_render runs to its end:
      * the next frame's binning pre-pass may overlap that kernel (programmatic dependent launch, trace_small.cu) */
     bool scene_settled = false;
+    unsigned int* last_base = nullptr;       /* where the last frame's tracer wrote: d_base, or the caller's buffer */
     unsigned int* d_order = nullptr;         /* two order-history buffers of the persistent tracer (trace_small.cu) */
     size_t cap_order = 0;                    /* uints */
     int order_key[7] = {0, 0, 0, 0, 0, 0, 0};   /* frame size + shard the history belongs to */
@@ -481,6 +482,12 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
     if (fill_frame(ctx, frame, shard, &f) != RT_OK) return fail(ctx, RT_ERR_ARG, "bad shard");
     const bool timing = ctx->opt[RT_OPT_TIMING] != 0;
     const int count = ctx->opt[RT_OPT_COUNTERS] != 0;
+    /* AA off, whole frame: the reference's second kernel only copies baseImage to the result (kernel.cu:275-278),
+     * so the tracer writes the caller's buffer itself and no post kernel runs.  (Shards keep the copy: it is what
+     * confines a rank's stores into a shared / peer frame to its own tiles.) */
+    const bool direct = !frame->alias && f.n_shards <= 1;
+    unsigned int* const image = direct ? out_dev : ctx->d_base;
+    ctx->last_base = image;
     if (count) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(RtCountersDev), ctx->stream));
     if (timing) cudaEventRecord(ctx->ev[0], ctx->stream);
     /* RT_OPT_TRACE_IMPL: 0 = auto (shared-memory tracer when the scene fits), 1 = HBM-resident LBVH tracer,
@@ -522,7 +529,7 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
             ctx->order_cur = 1 - ctx->order_cur;
             memcpy(ctx->order_key, key, sizeof(key));
         }
-        RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
+        RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, image, hit_ids_dev, ctx->d_counters,
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
                                             ctx->scene_settled ? 1 : 0,
@@ -530,16 +537,18 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
                                             ctx->opt[RT_OPT_MIRROR_BINS] == 0, ctx->stream));
     }
     else {
-        RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, ctx->d_base, hit_ids_dev, ctx->d_counters,
+        RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, image, hit_ids_dev, ctx->d_counters,
                                       ctx->opt[RT_OPT_TRAVERSAL] == 1, count, ctx->stream));
     }
     if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }
     int rc = RT_OK;
     if (frame->alias) rc = run_fxaa(ctx, ctx->d_base, out_dev, frame->imgw, frame->imgh, shard);
-    else RT_CHECK(ctx, rt_launch_copy(ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, ctx->stream));
+    else if (!direct) RT_CHECK(ctx, rt_launch_copy(ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, ctx->stream));
     if (rc != RT_OK) return rc;
     if (timing) { cudaEventRecord(ctx->ev[3], ctx->stream); ctx->timing_valid = true; }
-    ctx->scene_settled = true;
+    /* `settled` promises the next frame that the stream ends in this context's own post kernel (its pre-pass and
+     * refit then overlap it); after a direct frame it ends in the tracer, which still reads what they write */
+    ctx->scene_settled = !direct;
     return RT_OK;
 }
 
@@ -565,7 +574,7 @@ int rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* sh
 
 int rt_get_base_image(rt_context* ctx, unsigned int** base_dev) {
     if (!ctx || !base_dev) return RT_ERR_ARG;
-    *base_dev = ctx->d_base;
+    *base_dev = ctx->last_base ? ctx->last_base : ctx->d_base;   /* AA off, whole frame: the caller's own buffer */
     return RT_OK;
 }
 
