@@ -369,6 +369,18 @@ def main():
     roofline_fp32 = {"bound": "fp32", "kernel": "rt_trace_small_kernel (+ rt_cull_tiles_kernel)", "achieved": flops_step / trace_s / 1e12,
                      "peak": fp32_peak, "unit": "TFLOP/s", "frac": flops_step / trace_s / 1e12 / max(fp32_peak, 1e-9),
                      "peak_source": "measured FFMA microbenchmark (rt_measure_fp32_peak); nominal 74.4"}
+    # what actually bounds the tracer: warp-instruction issue (4 schedulers per SM, one instruction per clock each).
+    # Instructions per launch from the committed ncu capture (static for this workload), time measured live.
+    winst = traffic.get("warp_inst_per_launch", {})
+    roofline_issue = None
+    if winst and clocks.get("sm_mhz"):
+        per_step = 4.0 * (winst.get("rt_trace_small_kernel", 0) + winst.get("rt_cull_tiles_kernel", 0))
+        n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+        issue_peak = n_sm * 4 * clocks["sm_mhz"] * 1e6
+        roofline_issue = {"bound": "issue", "kernel": "rt_trace_small_kernel (+ rt_cull_tiles_kernel)",
+                          "achieved": per_step / trace_s / 1e9, "peak": issue_peak / 1e9, "unit": "Gwarp-inst/s",
+                          "frac": per_step / trace_s / issue_peak,
+                          "source": "warp instructions: ncu smsp__inst_executed.sum (profiles/traffic.json); peak: SMs x 4 schedulers x SM clock under load"}
     roofline_fxaa = {"bound": "hbm", "kernel": "rt_fxaa_tma_kernel", "achieved": 8.0 * npx * 4 / fxaa_s / 1e9,
                      "peak": hbm_peak, "unit": "GB/s", "frac": 8.0 * npx * 4 / fxaa_s / 1e9 / hbm_peak,
                      "traffic": traffic.get("fxaa_bytes_per_step")}
@@ -382,7 +394,8 @@ def main():
                        "l2": "flushed by a 256 MiB write between steps"},
             "frames_per_s": world * 4 / (ms_per_step * 1e-3), "wall_ms_per_step_incl_flush": 1e3 * t_wall / args.steps,
             "kernel_ms_per_step": {"trace": trace_ms, "fxaa": fxaa_ms},
-            "roofline": roofline, "roofline_fp32": roofline_fp32, "roofline_fxaa": roofline_fxaa,
+            "roofline": roofline, "roofline_fp32": roofline_fp32, "roofline_issue": roofline_issue,
+            "roofline_fxaa": roofline_fxaa,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "launchKernel (host Object/Light arrays per frame) + frame copied to pinned host memory",
                     "frames_per_s": world * 4 * args.steps / float(t.item())},
