@@ -511,12 +511,15 @@ __device__ __forceinline__ void rt_refit_leaf(int j, int n, const unsigned int* 
 }
 
 /* Full-size refit.  A Karras node covers a contiguous range of sorted leaves (node_other: its other end), so a
- * block of RT_BUILD_THREADS consecutive leaves owns every node whose range lies inside its own: those (255 of 256)
+ * block of RT_REFIT_THREADS consecutive leaves owns every node whose range lies inside its own: those (255 of 256)
  * are joined through shared memory -- both arrivals park their box there, block-scope fence, shared atomic --
  * and only the nodes that straddle blocks take the global protocol of rt_refit_leaf (device-scope fence + L2
  * atomic + 12 scalar stores per arrival, which held a 1M-leaf refit at 192 us).  node_other[i] < 0 (PLOC
  * topology: ranges unknown) sends a node to the global protocol. */
-__global__ void __launch_bounds__(RT_BUILD_THREADS)
+#ifndef RT_REFIT_THREADS
+#define RT_REFIT_THREADS 256
+#endif
+__global__ void __launch_bounds__(RT_REFIT_THREADS)
 rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
                 const int* __restrict__ bvh_src, const float4* __restrict__ recs,
                 const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
@@ -524,8 +527,8 @@ rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
                 const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
                 const int* __restrict__ node_other, unsigned int* __restrict__ flags, float* __restrict__ nodes,
                 float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
-    __shared__ unsigned int s_flags[RT_BUILD_THREADS];
-    __shared__ float s_box[RT_BUILD_THREADS][12];    /* per block-owned node: both children's exact (lo, hi) */
+    __shared__ unsigned int s_flags[RT_REFIT_THREADS];
+    __shared__ float s_box[RT_REFIT_THREADS][12];    /* per block-owned node: both children's exact (lo, hi) */
     const int b0 = blockIdx.x * blockDim.x, b1 = min(b0 + (int)blockDim.x, n);
     const int j = b0 + threadIdx.x;
     s_flags[threadIdx.x] = 0u;
@@ -873,7 +876,7 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         cudaError_t e = cudaMemsetAsync(b->flags, 0, sizeof(unsigned int) * (size_t)(n - 1), stream);
         if (e != cudaSuccess) return e;
     }
-    rt_refit_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
+    rt_refit_kernel<<<(n + RT_REFIT_THREADS - 1) / RT_REFIT_THREADS, RT_REFIT_THREADS, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
                                                       b->children, b->node_parent, b->leaf_parent, b->node_other, b->flags,
                                                       b->nodes, b->node_aux, b->prims, b->depth);
     return cudaGetLastError();

@@ -27,7 +27,7 @@ struct RtGlobalScene {
     __device__ __forceinline__ RtGlobalScene(const RtSceneDev& s) : sc(s) {}
 #ifdef RT_NODEMAP
     unsigned int dbg[3] = {0, 0, 0};   /* debug variant: node tests of primary / bounce / shadow rays */
-    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, int, RtLocalCounters& cnt) {
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, bool, RtLocalCounters& cnt) {
         const unsigned int before = cnt.node_tests;
         const RtHit h = rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
         dbg[depth ? 1 : 0] += cnt.node_tests - before;
@@ -40,7 +40,7 @@ struct RtGlobalScene {
         return r;
     }
 #else
-    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int, int, RtLocalCounters& cnt) {
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int, bool, RtLocalCounters& cnt) {
         return rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
     }
     __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3&, int, RtLocalCounters& cnt) {

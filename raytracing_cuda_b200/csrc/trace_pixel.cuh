@@ -8,8 +8,8 @@
  * (kernel.cu:218).
  *
  * ACC is the scene accessor of the calling kernel:
- *     RtHit  closest(o, d, depth, via, cnt) closest hit of a ray of generation `depth`; via = RtHit.slot of the
- *                                           surface a depth-1 ray left (a primary ray's hit), 0 otherwise
+ *     RtHit  closest(o, d, depth, off_plane0, cnt)  closest hit of a ray of generation `depth`; off_plane0: the ray
+ *                                           is the bounce of a PRIMARY ray off plane 0 (the sea: mirror bins)
  *     bool   occluded(o, d, tmax, cnt)      any non-emissive hit with t < tmax (kernel.cu:188-193)
  *     vec3   normal(hit, P)                 surface normal at the hit (kernel.cu:66, 87, 123)
  *     void   material(idx, m0, m1)          (color.rgb, mirror) (shine, specular, emissive, type)
@@ -40,10 +40,10 @@ __device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDe
     vec3 d = rt_primary_dir(f, x, y);
     vec3 c = v3(0, 0, 0);
     int depth = 0;
-    int via = 0;
+    bool off_plane0 = false;
 
     for (;;) {
-        const RtHit h = acc.closest(o, d, depth, via, pc.t);
+        const RtHit h = acc.closest(o, d, depth, off_plane0, pc.t);
         if (depth == 0 && hit_ids) hit_ids[y * f.imgw + x] = (h.tag == RT_MISS) ? -1 : (int)(h.tag & RT_TAG_INDEX);
 
         if (h.tag == RT_MISS) {
@@ -98,7 +98,7 @@ __device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDe
             const vec3 rd = rt_normalize(vsub(d, vscale(N, k)));
             o = rt_along(P, rd, 0.001f);
             d = rd;
-            via = h.slot;
+            off_plane0 = depth == 0 && h.slot == ~0;
             depth++;
             if (COUNT) pc.n_mirror++;
             continue;

@@ -66,9 +66,6 @@ __device__ __forceinline__ void rs_push(unsigned int& sp, int v) {
     asm volatile("st.shared.u16 [%0], %1;" ::"r"(sp), "h"((short)v));
     sp += RT_SMALL_STACK_STRIDE;
 }
-__device__ __forceinline__ void rs_store(unsigned int sp, int v) {
-    asm volatile("st.shared.u16 [%0], %1;" ::"r"(sp), "h"((short)v));
-}
 __device__ __forceinline__ int rs_pop(unsigned int& sp) {
     short v;
     sp -= RT_SMALL_STACK_STRIDE;
@@ -119,12 +116,7 @@ __device__ __forceinline__ bool rs_traverse(const RtSmallShared& s, const vec3& 
             if (h0 | h1) {
                 const bool second_first = h1 && (!h0 || t1 < t0);
                 const int near = second_first ? c1 : c0;
-#ifndef RS_BRANCHLESS_PUSH
-                if (h0 && h1) rs_push(sp, c0 ^ c1 ^ near);     /* measured faster than the branch-free form below */
-#else
-                rs_store(sp, c0 ^ c1 ^ near);
-                sp += (h0 && h1) ? RT_SMALL_STACK_STRIDE : 0;
-#endif
+                if (h0 && h1) rs_push(sp, c0 ^ c1 ^ near);     /* measured faster than an unconditional store + select */
                 node = near;
                 continue;
             }
@@ -168,15 +160,15 @@ struct RtSmallScene {
         }
     }
     /* RtHit.slot: >= 0 leaf byte offset from `base`, < 0 ~plane index */
-    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, int via, RtLocalCounters& cnt) {
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, bool off_plane0, RtLocalCounters& cnt) {
         RtHit best;
         best.t = __int_as_float(0x7f800000);
         best.tag = RT_MISS;
         best.slot = 0;
         planes_closest(o, d, best, cnt);
-        /* primary ray: the tile's candidate list instead of the hierarchy; the ray a primary ray sends off plane 0
-         * (via = ~0): the tile's mirror list (see `mirror bins`) */
-        const unsigned short* cand = depth == 0 ? s.list : ((depth == 1 && via == ~0) ? s.mlist : nullptr);
+        /* primary ray: the tile's candidate list instead of the hierarchy; the ray a primary ray sends off plane 0:
+         * the tile's mirror list (see `mirror bins`) */
+        const unsigned short* cand = depth == 0 ? s.list : (off_plane0 ? s.mlist : nullptr);
         if (cand) {
             const int n = cand[0];
             if (n != 0xFFFF) {
@@ -232,9 +224,6 @@ struct RtSmallScene {
             }
         }
         RtHit dummy;
-#ifdef RS_DIAG_NO_SHADOW_BVH
-        return false;
-#endif
         if (!s.deep) return rs_traverse<true, COUNT>(s, o, d, dummy, tmax, cnt);
         {
             for (int j = 0; j < s.n_prims; j++) {
@@ -829,9 +818,6 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         }
         cls_end = c;
         by_cost = __shfl_sync(0xffffffffu, c, RS_CLASSES - 1) == n_fetch;
-#ifdef RS_DIAG_NO_READ
-        by_cost = false;
-#endif
     }
 
     RtSmallShared sh;
@@ -842,7 +828,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.base) : "r"(b0));
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.stack0) : "r"(s0));
     }
-    sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;   /* one slot above the top is scratch (rs_store) */
+    sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;
     sh.list = s_list[warp];
     sh.mlist = mirror_lists ? s_list[warp] + RT_SMALL_LIST : nullptr;
     sh.lgrid = lgrid;
