@@ -42,6 +42,12 @@ cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, uns
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
+size_t rt_lgb_bins(void);
+size_t rt_lgb_sums(void);
+cudaError_t rt_lgb_count(const RtSceneDev* sc, const float* light_pos, unsigned int* counts, unsigned int* offsets,
+                         unsigned int* sums, unsigned int* fail, cudaStream_t stream);
+cudaError_t rt_lgb_fill(const RtSceneDev* sc, const float* light_pos, unsigned int* counts, const unsigned int* offsets,
+                        unsigned int* entries, unsigned int cap, unsigned int* fail, cudaStream_t stream);
 int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_planes);
 cudaError_t rt_trace_small_init(void);
 cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
@@ -102,6 +108,13 @@ struct rt_context {
     int order_cur = 0;                       /* buffer holding it */
     unsigned short* d_tile_lists = nullptr;  /* per-tile primary candidate lists (trace_small.cu) */
     uint4* d_lgrid = nullptr;                /* light bins of the shared-memory tracer (trace_small.cu), RT_LGRID_BYTES */
+    /* light grid of big scenes (light_grid.cu): scratch + per light offsets / entries; rebuilt when stale */
+    unsigned int *d_lgb_counts = nullptr, *d_lgb_sums = nullptr, *d_lgb_fail = nullptr;
+    unsigned int* d_lgb_offsets[RT_LGB_LIGHTS] = {nullptr, nullptr};
+    unsigned int* d_lgb_entries[RT_LGB_LIGHTS] = {nullptr, nullptr};
+    size_t cap_lgb_entries[RT_LGB_LIGHTS] = {0, 0};
+    bool lgb_stale = true;
+    bool lgb_waited = false;                 /* a frame has been rendered since the grid went stale */
     size_t cap_tile_lists = 0;
     unsigned int* d_tile_counter = nullptr;  /* [0] next tile, [1] finished CTAs (persistent tracer; self re-arming) */
 
@@ -225,7 +238,8 @@ int rt_destroy(rt_context* ctx) {
     RtBuildBuffers& b = ctx->bb;
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
                     b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.node_other, b.flags, b.node_aux,
-                    b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists, ctx->d_order, ctx->d_lgrid};
+                    b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists, ctx->d_order, ctx->d_lgrid, ctx->d_lgb_counts, ctx->d_lgb_sums, ctx->d_lgb_fail, ctx->d_lgb_offsets[0],
+                    ctx->d_lgb_offsets[1], ctx->d_lgb_entries[0], ctx->d_lgb_entries[1]};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     delete ctx;
@@ -310,6 +324,8 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
         (n_lights > 0 && !lights) || (unsigned int)n_objects > RT_TAG_INDEX)
         return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (n_lights != ctx->n_lights || (n_lights > 0 && memcmp(ctx->lights, lights, sizeof(rtb_Light) * (size_t)n_lights) != 0))
+        ctx->lgb_stale = true, ctx->lgb_waited = false;   /* the light grid of a big scene follows the lights */
     for (int i = 0; i < n_lights; i++) ctx->lights[i] = lights[i];
     ctx->n_lights = n_lights;
 
@@ -325,6 +341,8 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
             if (objects[i].type != ctx->host_objs[i].type) { mode = 0; break; }
     }
     if (mode < 0) return RT_OK;
+    ctx->lgb_stale = true, ctx->lgb_waited = false;
+    for (int i = 0; i < RT_LGB_LIGHTS; i++) ctx->scene.lg_offsets[i] = ctx->scene.lg_entries[i] = nullptr;
     const bool settled_before = ctx->scene_settled;   /* the stream ends in this context's own FXAA / copy kernel */
     ctx->scene_settled = false;
 
@@ -467,6 +485,45 @@ static int fill_frame(rt_context* ctx, const rt_frame* fr, const rt_shard* sh, R
     return RT_OK;
 }
 
+/* Light grid of a big scene (light_grid.cu): per light count pass + scan, 8-byte read-back of (total, fail) -- the
+ * grid is rebuilt only when the scene or the lights changed, next to an LBVH build that already synchronises --
+ * then the fill pass.  A light whose lists would not fit the budget keeps traversing the hierarchy. */
+static int build_light_grid(rt_context* ctx) {
+    for (int i = 0; i < RT_LGB_LIGHTS; i++) ctx->scene.lg_offsets[i] = ctx->scene.lg_entries[i] = nullptr;
+    ctx->lgb_stale = false;
+    const int n = ctx->scene.n_bvh_prims;
+    if (n < 2) return RT_OK;
+    const size_t bins = rt_lgb_bins();
+    if (!ctx->d_lgb_counts) {
+        RT_CHECK(ctx, regrow(&ctx->d_lgb_counts, bins));
+        RT_CHECK(ctx, regrow(&ctx->d_lgb_sums, rt_lgb_sums()));
+        RT_CHECK(ctx, regrow(&ctx->d_lgb_fail, (size_t)1));
+    }
+    const size_t budget = (size_t)64 << 20;          /* entries per light: 256 MB */
+    const int lit = ctx->n_lights < RT_LGB_LIGHTS ? ctx->n_lights : RT_LGB_LIGHTS;
+    for (int li = 0; li < lit; li++) {
+        if (!ctx->d_lgb_offsets[li]) RT_CHECK(ctx, regrow(&ctx->d_lgb_offsets[li], bins + 1));
+        const float lp[3] = {ctx->lights[li].pos.x, ctx->lights[li].pos.y, ctx->lights[li].pos.z};
+        RT_CHECK(ctx, rt_lgb_count(&ctx->scene, lp, ctx->d_lgb_counts, ctx->d_lgb_offsets[li], ctx->d_lgb_sums,
+                                   ctx->d_lgb_fail, ctx->stream));
+        unsigned int total = 0, failed = 0;
+        RT_CHECK(ctx, cudaMemcpyAsync(&total, ctx->d_lgb_offsets[li] + bins, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CHECK(ctx, cudaMemcpyAsync(&failed, ctx->d_lgb_fail, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        if (failed || (size_t)total > budget) continue;
+        if ((size_t)total > ctx->cap_lgb_entries[li] || !ctx->d_lgb_entries[li]) {
+            const size_t c = (size_t)total + (size_t)total / 8 + 1024;
+            RT_CHECK(ctx, regrow(&ctx->d_lgb_entries[li], c));
+            ctx->cap_lgb_entries[li] = c;
+        }
+        RT_CHECK(ctx, rt_lgb_fill(&ctx->scene, lp, ctx->d_lgb_counts, ctx->d_lgb_offsets[li], ctx->d_lgb_entries[li],
+                                  (unsigned int)ctx->cap_lgb_entries[li], ctx->d_lgb_fail, ctx->stream));
+        ctx->scene.lg_offsets[li] = ctx->d_lgb_offsets[li];
+        ctx->scene.lg_entries[li] = ctx->d_lgb_entries[li];
+    }
+    return RT_OK;
+}
+
 int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_dev, int* hit_ids_dev) {
     if (!ctx || !frame || !out_dev || frame->imgw < 2 || frame->imgh < 2) return RT_ERR_ARG;
     if (!ctx->have_scene) return fail(ctx, RT_ERR_STATE, "rt_render before rt_set_scene");
@@ -501,7 +558,7 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
             RT_CHECK(ctx, regrow(&ctx->d_tile_lists, need));
             ctx->cap_tile_lists = need;
         }
-        if (!ctx->d_lgrid && ctx->opt[RT_OPT_SHADOW_BINS] == 0) RT_CHECK(ctx, regrow(&ctx->d_lgrid, RT_LGRID_BYTES / sizeof(uint4)));
+        if (!ctx->d_lgrid && ctx->opt[RT_OPT_SHADOW_BINS] != 1) RT_CHECK(ctx, regrow(&ctx->d_lgrid, RT_LGRID_BYTES / sizeof(uint4)));
         /* Order history: a frame files every patch under its measured cost; the next frame of the same size
          * and shard starts with the most expensive ones (frame-to-frame coherence of an interactive renderer;
          * the first frame of a kind walks bottom-up).  Pure scheduling: pixels do not depend on it. */
@@ -533,11 +590,28 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
                                             ctx->scene_settled ? 1 : 0,
-                                            ctx->opt[RT_OPT_SHADOW_BINS] == 0 ? ctx->d_lgrid : (uint4*)nullptr,
+                                            ctx->opt[RT_OPT_SHADOW_BINS] != 1 ? ctx->d_lgrid : (uint4*)nullptr,
                                             ctx->opt[RT_OPT_MIRROR_BINS] == 0, ctx->stream));
     }
     else {
-        RT_CHECK(ctx, rt_launch_trace(&ctx->scene, &f, image, hit_ids_dev, ctx->d_counters,
+        /* The grid costs ~2 ms to build for a million triangles and saves ~0.4 ms per 4K frame: it is built when a
+         * second frame finds scene and lights unchanged (RT_OPT_SHADOW_BINS 2: at once), so lights that move every
+         * frame never pay for it and keep traversing. */
+        const int sb = ctx->opt[RT_OPT_SHADOW_BINS];
+        bool grid = sb != 1 && ctx->opt[RT_OPT_TRAVERSAL] != 1;
+        if (grid && ctx->lgb_stale) {
+            if (sb == 2 || ctx->lgb_waited) {
+                const int rc = build_light_grid(ctx);
+                if (rc != RT_OK) return rc;
+            } else {
+                ctx->lgb_waited = true;
+                grid = false;
+            }
+        }
+        RtSceneDev sc = ctx->scene;
+        if (!grid)
+            for (int i = 0; i < RT_LGB_LIGHTS; i++) sc.lg_offsets[i] = sc.lg_entries[i] = nullptr;
+        RT_CHECK(ctx, rt_launch_trace(&sc, &f, image, hit_ids_dev, ctx->d_counters,
                                       ctx->opt[RT_OPT_TRAVERSAL] == 1, count, ctx->stream));
     }
     if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }

@@ -51,6 +51,11 @@
 #define RT_LGRID_G 64
 #define RT_LGRID_LIGHTS 4             /* lights with bins; further lights traverse the hierarchy */
 #define RT_LGRID_BYTES ((size_t)RT_LGRID_LIGHTS * 6 * RT_LGRID_G * RT_LGRID_G * 16)
+/* light grid of big scenes (light_grid.cu): cube map of RT_LGB_G x RT_LGB_G direction bins per face and light */
+#ifndef RT_LGB_G
+#define RT_LGB_G 2048
+#endif
+#define RT_LGB_LIGHTS 2               /* lights with a grid; further lights traverse the hierarchy */
 #define RT_SMALL_ORDER_CLASSES 8      /* patch cost classes of the tracer's order history */
 #define RT_SMALL_ORDER_HEAD 32        /* uints before the class lists of an order buffer: [0..7] class counts */
 #ifndef RT_SMALL_DYN_SMEM_MAX
@@ -68,6 +73,10 @@ struct RtSceneDev {
     int n_bvh_prims;
     int n_planes;
     int n_objects;
+    /* light grid of big scenes (light_grid.cu): per light with a grid, offsets[6 G G + 1] into entries (Morton slots
+     * of the possible occluders per direction bin); NULL: that light's shadow rays traverse the hierarchy */
+    const unsigned int* lg_offsets[RT_LGB_LIGHTS];
+    const unsigned int* lg_entries[RT_LGB_LIGHTS];
 };
 
 struct RtLightDev {

@@ -264,3 +264,73 @@ def test_terrain_bvh_equals_bruteforce():
     o = ou.oracle_render(objs, s.lights, f, gu.sky_small(), x_step=4, y_step=4, want_out=False)
     m = o["ids"][::4, ::4] != ida[::4, ::4]
     assert m.mean() <= 1e-3
+
+
+def _grid_on_off(r, f, objs, lights):
+    r.set_scene(objs, lights)
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 2)       # build the grid at once (0 waits for a second unchanged frame)
+    a = r.render_to_host(f, want_ids=False).copy()
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 1)
+    b = r.render_to_host(f, want_ids=False).copy()
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 0)
+    return a, b
+
+
+def test_light_grid_of_big_scenes_changes_tested_primitives_only():
+    """Shadow rays of the HBM tracer look their light's direction bin up in a cube-map grid (light_grid.cu: CSR lists
+    built by a quadtree descent per primitive with the cull geometry of the small scenes' light bins) instead of
+    traversing the LBVH (RT_OPT_SHADOW_BINS 0).  Conservative culling: every frame must equal the traversal's, and
+    the brute-force kernel's, bit for bit -- the terrain at several times of day (sun high, grazing, below the
+    horizon), lights moved into and under the terrain and next to triangles (a primitive spread over too many bins
+    switches that light's grid off), the built-in scene forced through the HBM tracer with random lights, three
+    lights (the third has no grid), a changed scene with unchanged lights."""
+    r = gu.renderer()
+    s = rt.Scene()
+    s.set_pose((324.4, 330.0, -84.0), 141.2, 30.0)
+    objs = rt.terrain_objects(128)
+    for hours in (14.0, 7.0, 18.5, 1.0, 5.9):
+        s.set_time(hours)
+        f = s.frame(320, 180)
+        f.alias = 0
+        a, b = _grid_on_off(r, f, objs, s.lights)
+        assert (a == b).all(), (hours, int((a != b).sum()))
+        if hours in (14.0, 18.5):
+            r.set_option(_lib.RT_OPT_TRAVERSAL, 1)
+            c = r.render_to_host(f, want_ids=False)
+            r.set_option(_lib.RT_OPT_TRAVERSAL, 0)
+            assert (a == c).all(), (hours, "brute force")
+    rng = np.random.default_rng(5)
+    s.set_time(14.0)
+    f = s.frame(256, 144)
+    f.alias = 0
+    for k in range(10):
+        lights = s.lights.copy()
+        for li in range(len(lights)):
+            lights[li]["pos"] = rng.uniform([-500, -50, -500], [800, 350, 700]) if k % 2 else \
+                rng.uniform([-2000, 300, -2000], [2000, 2500, 2000])
+        a, b = _grid_on_off(r, f, objs, lights)
+        assert (a == b).all(), (k, lights["pos"], int((a != b).sum()))
+    # the built-in scene through the HBM tracer: spheres, big triangles, lights anywhere
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 1)
+    f = s.configure(view=5, hours=14.0, imgw=320, imgh=180, alias=False)
+    for k in range(12):
+        lights = s.lights.copy()
+        if k >= 2:
+            for li in range(len(lights)):
+                lights[li]["pos"] = rng.uniform([-120, -20, -120], [120, 60, 120]) if k % 2 else \
+                    rng.uniform([-900, -600, -900], [900, 900, 900])
+        if k == 11:
+            lights = np.concatenate([lights, lights[:1]]).copy()
+            lights[2]["pos"] = [40.0, 80.0, -30.0]
+        a, b = _grid_on_off(r, f, s.objects, lights)
+        assert (a == b).all(), (k, int((a != b).sum()))
+    # same lights, other scene: the grid follows the scene
+    o2 = s.objects.copy()
+    o2[5]["pos"] += np.float32(3.0)
+    a, b = _grid_on_off(r, f, o2, s.lights)
+    assert (a == b).all()
+    # default policy: the first frame after a change traverses, the second builds the grid; all three agree
+    r.set_scene(s.objects, s.lights)
+    frames = [r.render_to_host(f, want_ids=False).copy() for _ in range(3)]
+    assert (frames[0] == frames[1]).all() and (frames[1] == frames[2]).all()
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
