@@ -275,6 +275,15 @@ def config4(r, sky, fh):
     grid_frame_ms = e0.elapsed_time(e1)
     rays, c = count_rays(r, f, out_local)
     full = out_local.clone()
+    # the whole 4K frame once more with the shadow rays traversing the hierarchy: must be the same pixels
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 1)
+    r.render(f, out_local)
+    r.synchronize()
+    grid_ok = bool(torch.equal(out_local, full))
+    t_trav = timed(lambda: r.render(f, out_local), 10)
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 0)
+    r.render(f, out_local)
+    r.synchronize()
     ms = timed(lambda: sharded_frame(r, f, w, h, out_local, packed, frame0, bufs, shard), 20)
     ok = composite_ok(r, f, w, h, out_local, packed, frame0, bufs, shard, full)
     # cross-check against the brute-force kernel (reference arithmetic over all primitives) on a small frame
@@ -288,6 +297,7 @@ def config4(r, sky, fh):
               % (cells, cells, len(objs), COMPOSE), "ms_per_frame": ms, "frames_per_s": 1e3 / ms, "Mrays_per_s": rays / ms / 1e3,
               "rays_per_frame": rays, "lbvh_build_ms_first": build_ms, "lbvh_build_ms": build_ms_warm,
               "light_grid_build_ms_incl_one_whole_frame": grid_frame_ms,
+              "light_grid_equals_traversal_whole_frame": grid_ok, "ms_per_whole_frame_traversal_only": t_trav,
               "node_tests_per_pixel": c["node_tests"] / (w * h), "tri_tests_per_pixel": c["tri_tests"] / (w * h),
               "composite_equals_single_gpu_frame": ok,
               "bvh_equals_bruteforce_96x54": bool((ia == ib).all() and (a == b).all())})
