@@ -25,11 +25,16 @@ __device__ __forceinline__ float fx_lum(unsigned int c) {
     return __fmul_rn(fminf(l, 255.0f), 0.0039215688593685626984f);
 }
 
+/* rgbToInt (reference kernel.cu:26-32: clamp to [0, 255], truncate, pack) for the blend of fx_blend, whose channels
+ * are convex combinations of two bytes: (1 - b) c + b n with b in [0, 1] lies in [0, 255.0001], so the clamps never
+ * act and truncation is all that is left.  v + 2^23 rounded TOWARDS ZERO leaves trunc(v) in the low mantissa bits
+ * (FADD.RZ, full rate; F2I issues at a quarter of that, like I2F); two PRMTs gather the three low bytes (bytes 1 and
+ * 2 of 0x4B0000xx are zero).  tests/test_numerics.py checks the identity for every byte pair and weight class. */
 __device__ __forceinline__ unsigned int fx_pack(float r, float g, float b) {
-    r = fmaxf(0.0f, fminf(r, 255.0f));
-    g = fmaxf(0.0f, fminf(g, 255.0f));
-    b = fmaxf(0.0f, fminf(b, 255.0f));
-    return (unsigned int)(((int)b << 16) | ((int)g << 8) | (int)r);
+    const unsigned int ri = __float_as_uint(__fadd_rz(r, 8388608.0f));
+    const unsigned int gi = __float_as_uint(__fadd_rz(g, 8388608.0f));
+    const unsigned int bi = __float_as_uint(__fadd_rz(b, 8388608.0f));
+    return __byte_perm(__byte_perm(ri, gi, 0x1140), bi, 0x3410);
 }
 
 /* Decide from the nine luminances.  Returns false when the pixel passes through
@@ -44,11 +49,13 @@ __device__ __forceinline__ bool fx_decide(float M, float E, float W, float N, fl
 
     float sum = __fadd_rn(__fadd_rn(__fadd_rn(E, W), S), N);
     sum = __fadd_rn(__fadd_rn(__fadd_rn(__fmaf_rn(sum, 2.0f, NE), NW), SE), SW);
-    /* (double)sum / 12.0 as the reference computes it (kernel.cu:372), by FMA correction of sum * RN(1/12):
-     * q0 + (sum - q0 * 12) * rc is the correctly rounded quotient (Markstein), 3 DFMA-class instructions
-     * instead of the ~30 of a DDIV; tests/test_numerics.py checks the identity with exact rationals */
-    const double sd = (double)sum, q0 = sd * (1.0 / 12.0);
-    float filter = (float)__fma_rn(__fma_rn(-q0, 12.0, sd), 1.0 / 12.0, q0);
+    /* (float)((double)sum / 12.0) as the reference computes it (kernel.cu:372) equals the correctly rounded FP32
+     * quotient: sum / 12 = m / 3 * 2^k is either exact or has the period-2 binary expansion of a third, which
+     * cannot round to a 24-bit midpoint at 53 bits, so rounding twice changes nothing.  The FP32 quotient by FMA
+     * correction of sum * RN(1/12) (Markstein): q0 + (sum - q0 * 12) * rc, three FP32 instructions and no
+     * conversion to and from FP64 (two quarter-rate F2F).  tests/test_numerics.py checks both steps exactly. */
+    const float q0 = __fmul_rn(sum, 0.083333335816860198974609375f);
+    float filter = __fmaf_rn(__fmaf_rn(-q0, 12.0f, sum), 0.083333335816860198974609375f, q0);
     float rc;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(contrast));
     filter = fminf(__fmul_rn(fabsf(__fadd_rn(filter, -M)), rc), 1.0f);

@@ -85,6 +85,67 @@ def test_fxaa_division_by_twelve_by_fma_correction():
         assert q == a / 12.0, a
 
 
+def _rn32(x):
+    """exact rational -> nearest float32 (ties to even), as a float"""
+    from fractions import Fraction as F
+    import math
+    if x == 0:
+        return 0.0
+    sgn = -1 if x < 0 else 1
+    x = abs(x)
+    e = math.floor(math.log2(float(x)))
+    while F(2) ** e > x:
+        e -= 1
+    while F(2) ** (e + 1) <= x:
+        e += 1
+    scale = F(2) ** (23 - e)
+    n = x * scale
+    fl = n.numerator // n.denominator
+    rem = n - fl
+    if rem > F(1, 2) or (rem == F(1, 2) and fl % 2 == 1):
+        fl += 1
+    return sgn * float(F(fl) / scale)
+
+
+def test_fxaa_division_by_twelve_in_fp32():
+    """fxaa_core.cuh computes the reference's (float)((double)sum / 12.0) (kernel.cu:372) entirely in FP32:
+    q = fma(fma(-q0, 12, sum), rc, q0), q0 = RN(sum rc), rc = RN32(1/12).  Both claims exactly: the FP32 sequence is the
+    correctly rounded quotient, and rounding via double first gives the same float."""
+    from fractions import Fraction as F
+    rng = np.random.default_rng(7)
+    rc = float(np.float32(1.0 / 12.0))
+    assert rc == 0.083333335816860198974609375
+    # the sums FXAA forms are sums of nine luminances k/255-like values; plus random floats over the range and beyond
+    vals = np.concatenate([rng.uniform(0, 12.5, 12000), rng.uniform(0, 0.05, 1500), rng.integers(0, 3060, 1500) / 255.0,
+                           [0.0, 12.0, 1.0, 3.0, 0.25, 11.999999, 2.8e-4]]).astype(np.float32)
+    for a32 in vals:
+        a = float(a32)
+        q0 = _rn32(F(a) * F(rc))
+        r = _rn32(F(a) - F(q0) * 12)
+        assert F(r) == F(a) - F(q0) * 12, a                      # the remainder is exact
+        q = _rn32(F(q0) + F(r) * F(rc))
+        want = float(np.float32(np.float64(a32) / 12.0))           # the reference: divide in double, round to float
+        assert q == want, a
+        assert q == _rn32(F(a) / 12), a                            # = the correctly rounded FP32 quotient
+
+
+def test_fxaa_pack_by_round_to_zero_add():
+    """fxaa_core.cuh fx_pack: the blend (1 - b) c + b n of two bytes never leaves [0, 255.0001], so the reference's
+    clamp + truncate (kernel.cu:26-32) is the low mantissa byte of v + 2^23 rounded towards zero.  Checked on the FP32
+    values the blend actually produces for every byte pair and a sweep of weights."""
+    c, n = np.meshgrid(np.arange(256, dtype=np.float32), np.arange(256, dtype=np.float32))
+    for b in np.concatenate([np.linspace(0, 1, 41), [1e-7, 0.5, 0.99999994]]).astype(np.float32):
+        omb = np.float32(1.0) - b
+        # fma(omb, c, b * n): emulate in float64 (products of a float32 and a byte are exact there, the sum is not
+        # rounded twice in any case that matters for a floor below 256: compare against the exact floor instead)
+        v = (omb.astype(np.float64) * c + (b * n).astype(np.float32).astype(np.float64)).astype(np.float32)
+        assert v.min() >= 0.0 and v.max() < 256.0
+        want = np.floor(np.minimum(np.maximum(v, 0.0), 255.0)).astype(np.uint32)     # clamp + truncate
+        # v + 2^23 towards zero: exact sum has at most 24 + 8 bits, truncation = floor for v >= 0
+        got = (np.floor(v.astype(np.float64)) + 8388608.0).astype(np.float32).view(np.uint32) & 255
+        assert (got == want).all(), b
+
+
 def test_fmodf_one_equals_x_minus_trunc():
     x = np.concatenate([np.random.default_rng(5).uniform(-3, 3, 20000), [0.0, 1.0, 1.9999999, -0.5]]).astype(np.float32)
     assert (np.fmod(x, np.float32(1.0)) == x - np.trunc(x)).all()
