@@ -294,8 +294,9 @@ def main():
     # ---- e2e through launchKernel with host inputs and a device->host read-back of every frame
     lib = _lib.load()
     from raytracing_cuda_b200.structs import Camera, Float3, Light, Object
-    pinned = [torch.empty(W * H, dtype=torch.int32).pin_memory() for _ in range(2)]
-    dev2 = [torch.empty(W * H, dtype=torch.int32, device="cuda") for _ in range(2)]
+    depth = max(2, int(os.environ.get("RTB_E2E_DEPTH", "3")))     # frames in flight (render + read-back pipeline)
+    pinned = [torch.empty(W * H, dtype=torch.int32).pin_memory() for _ in range(depth)]
+    dev2 = [torch.empty(W * H, dtype=torch.int32, device="cuda") for _ in range(depth)]
     copy_stream = torch.cuda.Stream()
     sky_ptrs = [sky[k].ctypes.data for k in range(4)]
 
@@ -303,7 +304,7 @@ def main():
         cam = Camera()
         C.memmove(C.byref(cam), C.byref(fr.cam), C.sizeof(Camera))
         skyv = (C.c_float * 4)(*fr.skyVars)
-        lib.launchKernel(dev2[i & 1].data_ptr(), W, H, cam, C.cast(objs.ctypes.data, C.POINTER(Object)),
+        lib.launchKernel(dev2[i % depth].data_ptr(), W, H, cam, C.cast(objs.ctypes.data, C.POINTER(Object)),
                          C.cast(lights.ctypes.data, C.POINTER(Light)), Float3(*fr.ambient), skyv, sky_ptrs[0],
                          sky_ptrs[1], sky_ptrs[2], sky_ptrs[3], SKY_W if args.sky == "synthetic" else sky.shape[2],
                          SKY_H if args.sky == "synthetic" else sky.shape[1], fr.dayTime, True)
@@ -311,7 +312,7 @@ def main():
         done.record(torch.cuda.default_stream())
         copy_stream.wait_event(done)
         with torch.cuda.stream(copy_stream):
-            pinned[i & 1].copy_(dev2[i & 1], non_blocking=True)
+            pinned[i % depth].copy_(dev2[i % depth], non_blocking=True)
         copied = torch.cuda.Event()
         copied.record(copy_stream)
         return copied
@@ -319,10 +320,10 @@ def main():
     pending = []
 
     def step_e2e(counter):
-        # two frames in flight: frame i is traced while frame i-1 is read back; the pipeline keeps flowing
-        # from one step into the next and is drained inside the timed region, after the last step
+        # `depth` frames in flight: frame i is traced while earlier frames are read back, the host runs ahead by the
+        # rest; the pipeline keeps flowing from one step into the next and is drained inside the timed region
         for _, objs, lights, fr in states:
-            if len(pending) >= 2:
+            if len(pending) >= depth:
                 pending.pop(0).synchronize()      # the buffer about to be reused has been read back
             pending.append(legacy_frame(counter[0], objs, lights, fr))
             counter[0] += 1
