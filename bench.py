@@ -58,12 +58,52 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index):
+    def __init__(self, gpu_index, uuid=None):
         self.gpu = gpu_index
+        self.uuid = uuid
         self.proc = None
         self.lines = []
+        self.nvml = None
+        self.samples = []          # (sm_mhz, sm_max_mhz, reasons bit mask) from NVML
+        self.stop_flag = False
+
+    def _nvml_loop(self):
+        # in-process NVML sampling every ~2 ms: the timed region is tens of milliseconds, an nvidia-smi process
+        # (100 ms period, slower to start on an 8-GPU box) can miss it altogether
+        n = self.nvml
+        while not self.stop_flag:
+            try:
+                sm = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+                try:
+                    rs = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                except Exception:
+                    rs = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                self.samples.append((float(sm), self.max_mhz, int(rs)))
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def start(self):
+        try:
+            import pynvml as n
+            n.nvmlInit()
+            self.handle = None
+            if self.uuid:
+                for cand in ("GPU-" + str(self.uuid), str(self.uuid)):
+                    try:
+                        self.handle = n.nvmlDeviceGetHandleByUUID(cand.encode() if hasattr(cand, "encode") else cand)
+                        break
+                    except Exception:
+                        self.handle = None
+            if self.handle is None:
+                self.handle = n.nvmlDeviceGetHandleByIndex(self.gpu)
+            self.max_mhz = float(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM))
+            self.nvml = n
+            self.thread = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
@@ -78,6 +118,18 @@ class ClockSampler:
             self.lines.append(line.strip())
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=1.0)
+            n = self.nvml
+            bits = {"hw_slowdown": getattr(n, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                    "hw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                    "sw_thermal_slowdown": getattr(n, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                    "sw_power_cap": getattr(n, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+            sm = [x[0] for x in self.samples]
+            reasons = sorted(k for k, b in bits.items() if any(x[2] & b for x in self.samples))
+            return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_mhz if sm else None,
+                    "reasons": reasons, "samples": len(sm), "source": "NVML, 2 ms period"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -257,7 +309,11 @@ def main():
         flush.fill_(1)
         step_device(False)
     barrier()
-    sampler = ClockSampler(local)
+    try:
+        dev_uuid = str(torch.cuda.get_device_properties(local).uuid)
+    except Exception:
+        dev_uuid = None
+    sampler = ClockSampler(local, dev_uuid)
     sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     trace_ms = fxaa_ms = 0.0
