@@ -169,6 +169,20 @@ def scene_states():
 
 # ------------------------------------------------------------------------------------ CPU legs
 
+def cpu_use_all_cores():
+    """The CPU legs run on all host threads: torchrun exports OMP_NUM_THREADS=1 to its workers, which would put the
+    reference's trace loop on one core.  Returns the thread count in use."""
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    os.environ["OMP_NUM_THREADS"] = str(n)       # for a runtime that has not started yet
+    try:
+        gomp = C.CDLL("libgomp.so.1")            # the runtime the oracle / reference builds link
+        gomp.omp_set_num_threads(C.c_int(n))
+        gomp.omp_get_max_threads.restype = C.c_int
+        return int(gomp.omp_get_max_threads())
+    except Exception:
+        return n
+
+
 def cpu_reference_step(states, sky, y_step):
     """One bounded sample of the step on the host cores.  Returns (rays traced, seconds, kind)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -204,7 +218,7 @@ def run_reference_arm(args):
     states = scene_states()
     sky = rt.synthetic_sky(SKY_W, SKY_H)
     y_step = 4
-    cores = os.cpu_count() or 1
+    cores = cpu_use_all_cores()
     rays = cpu_sample_rays(states, sky, y_step)          # also warms the page cache of the sky maps
     for _ in range(args.warmup):
         cpu_reference_step(states, sky, y_step)
@@ -461,13 +475,14 @@ def main():
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         y_step = 4
+        cpu_cores = cpu_use_all_cores()
         rays = cpu_sample_rays(states, sky, y_step)
         dt, reps, kind = 0.0, 0, "port"
         while dt < 10.0 and reps < 200:           # about 10 s of CPU work on the box's host cores
             d, kind = cpu_reference_step(states, sky, y_step)
             dt += d
             reps += 1
-        line["cpu_baseline"] = {"value": reps * rays / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count() or 1,
+        line["cpu_baseline"] = {"value": reps * rays / dt / 1e6, "unit": "Mrays/s", "cores": cpu_cores,
                                 "kind": kind,
                                 "sample": "%d x rows y%%%d==0 of the 4 frames (%d rays each), FXAA skipped, %.1f s" % (
                                     reps, y_step, rays, dt)}
