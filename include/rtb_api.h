@@ -45,6 +45,11 @@ void launchKernel(unsigned int* result, int imgw, int imgh, rtb_Camera cam,
                   float h_dayTime, bool alias);
 #endif
 
+/* The reference never frees what launchKernel allocates on its first call (kernel.cu:419-441).  Extension: destroy
+ * the process-global context behind launchKernel; the next call starts from scratch and reads its sky arguments
+ * again. */
+int  rtb_legacy_shutdown(void);
+
 /* ------------------------------------------------------------ handle API */
 
 typedef struct rt_context rt_context;
@@ -70,7 +75,8 @@ enum {
     RT_OPT_ORDER = 8,       /* work order of the shared-memory tracer on whole frames: 0 = most expensive patches of the previous frame of this size first (default; first frame bottom-up), 1 = always bottom-up.  Scheduling only: identical pixels */
     RT_OPT_SHADOW_BINS = 9, /* shadow rays: 0 = per-light direction bins (default; small scenes: rebuilt by every frame's pre-pass; big scenes: a CSR grid built once a second frame finds scene and lights unchanged), 1 = traverse the hierarchy, 2 = like 0, big scenes build the grid at once.  Which primitives get tested only: identical pixels */
     RT_OPT_MIRROR_BINS = 10, /* rays that primary rays send off plane 0 (the sea) in the shared-memory tracer: 0 = candidate lists of the bin's mirrored frustum (default), 1 = traverse the hierarchy.  Which primitives get tested only: identical pixels */
-    RT_OPT_N = 11
+    RT_OPT_LIGHT_BINS_REUSE = 11, /* light bins of the shared-memory tracer: 0 = rebuilt only when the scene or the lights changed since they were built (default; they do not depend on the camera), 1 = rebuilt by every frame's pre-pass.  Identical pixels */
+    RT_OPT_N = 12
 };
 
 /* One frame's uniforms: what launchKernel receives by value / as small host arrays. */
@@ -157,7 +163,12 @@ int  rt_unpack_tiles(rt_context* ctx, const unsigned int* packed_dev, int imgw, 
  *                rt_render(..., shard, rt_peer_frame_buffer(pf, seq), ...)
  *                rt_peer_frame_signal(rank, seq)
  *   the owner:   rt_peer_frame_wait(n_ranks, seq) ... use the frame ... rt_peer_frame_release(seq)
- * A wait that is not satisfied within 2 s sets the error word (rt_peer_frame_error) instead of hanging. */
+ * rt_render_peer(...) = acquire + rt_render into rt_peer_frame_buffer(pf, seq) + signal in ONE call: the frame's last
+ * kernel (FXAA / copy) carries both halves of the hand-shake, so a producer frame is three kernel launches.
+ * A wait that is not satisfied within the frame's timeout (default 10 s, rt_peer_frame_set_timeout; per process)
+ * sets the error word instead of hanging: 1 + k = the owner gave up on rank k, 0x100 + k = rank k gave up on the
+ * owner's release.  The frame is then INVALID (a producer that gave up stores nothing).  rt_peer_frame_error
+ * synchronises and reads the word -- check it before using a frame; it stays set until rt_peer_frame_reset_error. */
 #define RT_PEER_HANDLE_BYTES 64
 typedef struct rt_peer_frame rt_peer_frame;
 int  rt_peer_frame_create(rt_context* ctx, size_t n_pixels, int n_buffers, rt_peer_frame** out,
@@ -169,7 +180,11 @@ int  rt_peer_frame_acquire(rt_context* ctx, rt_peer_frame* pf, unsigned int seq)
 int  rt_peer_frame_signal(rt_context* ctx, rt_peer_frame* pf, int rank, unsigned int seq);
 int  rt_peer_frame_wait(rt_context* ctx, rt_peer_frame* pf, int n_ranks, unsigned int seq);
 int  rt_peer_frame_release(rt_context* ctx, rt_peer_frame* pf, unsigned int seq);
+int  rt_render_peer(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, rt_peer_frame* pf, int rank,
+                    unsigned int seq, int* hit_ids_dev);
+int  rt_peer_frame_set_timeout(rt_peer_frame* pf, unsigned int timeout_ms);
 int  rt_peer_frame_error(rt_context* ctx, rt_peer_frame* pf, unsigned int* err);
+int  rt_peer_frame_reset_error(rt_context* ctx, rt_peer_frame* pf);
 int  rt_peer_frame_close(rt_context* ctx, rt_peer_frame* pf);
 
 int  rt_synchronize(rt_context* ctx);
@@ -188,10 +203,9 @@ int  rt_measure_fp32_peak(rt_context* ctx, float* tflops);
 int  rt_bvh_info(rt_context* ctx, int* n_prims_in_bvh, int* n_nodes, int* n_planes);
 int  rt_bvh_download(rt_context* ctx, float* nodes16, int* sorted_prim_ids,
                      unsigned int* morton_sorted);
-/* Stand-alone key sort used by the builder (tests compare it with CUB):
+/* Stand-alone key sort used by the builder (tests compare it with a library sort):
  * sorts (key,val) pairs in DEVICE memory, stable, ascending. */
 int  rt_sort_pairs(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n);
-int  rt_sort_pairs_cub(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n);
 
 /* ----------------------------------------------------- host scene layer */
 

@@ -27,7 +27,7 @@
  *
  * Parity pinning: oracle/build_ref.py compiles the reference's own kernel.cu
  * text (kernel.cu:9-403) for the host under shim macros into
- * oracle/_ref/libref_trace_cpu.so; tests/test_oracle_vs_reference.py requires
+ * oracle/_ref/libref_trace_cpu.so; tests/test_oracle.py requires
  * this restatement to match it bit-for-bit (image, pre-FXAA image) and
  * tests/golden/ holds vectors generated from that reference build.
  */

@@ -19,6 +19,7 @@ RT_OPT_FORCE_RADIX = 7
 RT_OPT_ORDER = 8
 RT_OPT_SHADOW_BINS = 9
 RT_OPT_MIRROR_BINS = 10
+RT_OPT_LIGHT_BINS_REUSE = 11
 RT_PEER_HANDLE_BYTES = 64
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
@@ -30,6 +31,7 @@ _u8p = C.POINTER(C.c_ubyte)
 SIGNATURES = {
     "launchKernel": (None, [_P, C.c_int, C.c_int, Camera, C.POINTER(Object), C.POINTER(Light), Float3,
                             C.POINTER(C.c_float), _P, _P, _P, _P, C.c_int, C.c_int, C.c_float, C.c_bool]),
+    "rtb_legacy_shutdown": (C.c_int, []),
     "rt_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
     "rt_destroy": (C.c_int, [_P]),
     "rt_last_error": (C.c_char_p, [_P]),
@@ -53,7 +55,10 @@ SIGNATURES = {
     "rt_peer_frame_signal": (C.c_int, [_P, _P, C.c_int, C.c_uint]),
     "rt_peer_frame_wait": (C.c_int, [_P, _P, C.c_int, C.c_uint]),
     "rt_peer_frame_release": (C.c_int, [_P, _P, C.c_uint]),
+    "rt_render_peer": (C.c_int, [_P, C.POINTER(Frame), C.POINTER(Shard), _P, C.c_int, C.c_uint, _P]),
+    "rt_peer_frame_set_timeout": (C.c_int, [_P, C.c_uint]),
     "rt_peer_frame_error": (C.c_int, [_P, _P, C.POINTER(C.c_uint)]),
+    "rt_peer_frame_reset_error": (C.c_int, [_P, _P]),
     "rt_peer_frame_close": (C.c_int, [_P, _P]),
     "rt_present": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "rt_synchronize": (C.c_int, [_P]),
@@ -63,7 +68,6 @@ SIGNATURES = {
     "rt_bvh_info": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rt_bvh_download": (C.c_int, [_P, _P, _P, _P]),
     "rt_sort_pairs": (C.c_int, [_P, _P, _P, C.c_int]),
-    "rt_sort_pairs_cub": (C.c_int, [_P, _P, _P, C.c_int]),
     "rtb_scene_create": (_P, []),
     "rtb_scene_destroy": (None, [_P]),
     "rtb_scene_objects": (C.POINTER(Object), [_P, C.POINTER(C.c_int)]),

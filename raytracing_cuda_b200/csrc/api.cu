@@ -31,14 +31,13 @@ int rt_build_by_value(const RtBuildBuffers* b, int mode);
 cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned int* tmp_keys, unsigned int* tmp_vals,
                                 unsigned int* hist, int n, int force_radix, cudaStream_t stream);
 int rt_radix_hist_entries(int n);
-cudaError_t rt_cub_sort_pairs(unsigned int* keys, unsigned int* vals, int n, cudaStream_t stream);
 cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                             RtCountersDev* counters, int brute, int count, cudaStream_t stream);
 cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
-                                  unsigned int* order_w, int after_own_post, uint4* lgrid, int mirror_bins,
-                                  cudaStream_t stream);
+                                  unsigned int* order_w, int after_own_post, uint4* lgrid, int build_lgrid,
+                                  int mirror_bins, cudaStream_t stream);
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
@@ -51,21 +50,33 @@ cudaError_t rt_lgb_fill(const RtSceneDev* sc, const float* light_pos, unsigned i
 int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_planes);
 cudaError_t rt_trace_small_init(void);
 cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
-                                cudaStream_t stream);
+                                const RtPeerSync* peer, cudaStream_t stream);
 cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out, int w, int h,
-                               const rt_shard* sh, int n_sm, cudaStream_t stream);
+                               const rt_shard* sh, int n_sm, const RtPeerSync* peer, cudaStream_t stream);
 cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
-                           cudaStream_t stream);
+                           const RtPeerSync* peer, cudaStream_t stream);
 cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned int* packed, int w, int h, const rt_shard* sh,
                                  int unpack, cudaStream_t stream);
 cudaError_t rt_launch_ffma_peak(int n_sm, cudaStream_t stream, float* ms, double* flops);
 cudaError_t rt_launch_present(const unsigned int* in, unsigned int* out, int w, int h, int factor, int mode,
                               cudaStream_t stream);
 cudaError_t rt_launch_peer_signal(unsigned int* flags, int rank, unsigned int seq, cudaStream_t stream);
-cudaError_t rt_launch_peer_wait(unsigned int* flags, int n_ranks, unsigned int seq, cudaStream_t stream);
+cudaError_t rt_launch_peer_wait(unsigned int* flags, int n_ranks, unsigned int seq, unsigned int timeout_ms,
+                                cudaStream_t stream);
 cudaError_t rt_launch_peer_release(unsigned int* flags, unsigned int seq, cudaStream_t stream);
-cudaError_t rt_launch_peer_acquire(unsigned int* flags, unsigned int seq, cudaStream_t stream);
+cudaError_t rt_launch_peer_acquire(unsigned int* flags, unsigned int seq, unsigned int timeout_ms, cudaStream_t stream);
+cudaError_t rt_launch_peer_reset_error(unsigned int* flags, cudaStream_t stream);
 }
+
+/* The four sky maps of a device: 512 MiB for the reference's 8192x4096 maps, so contexts of one device share one
+ * block (rt_share_sky).  The block lives until its last user lets go of it; a user lets go only after its own
+ * stream has drained (rt_set_sky, rt_share_sky, rt_destroy), so no frame in flight can sample freed textures. */
+struct RtSkyBlock {
+    cudaArray_t arr[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaTextureObject_t tex[4] = {0, 0, 0, 0};
+    int device = 0;
+    int users = 1;
+};
 
 struct rt_context {
     int device = 0;
@@ -75,9 +86,7 @@ struct rt_context {
     int opt[RT_OPT_N] = {0};
 
     /* sky */
-    cudaArray_t sky_arr[4] = {nullptr, nullptr, nullptr, nullptr};
-    cudaTextureObject_t sky_tex[4] = {0, 0, 0, 0};
-    bool have_sky = false, own_sky = true;
+    RtSkyBlock* sky = nullptr;
 
     /* scene */
     std::vector<rtb_Object> host_objs;      /* last upload, for change classification */
@@ -108,6 +117,9 @@ struct rt_context {
     int order_cur = 0;                       /* buffer holding it */
     unsigned short* d_tile_lists = nullptr;  /* per-tile primary candidate lists (trace_small.cu) */
     uint4* d_lgrid = nullptr;                /* light bins of the shared-memory tracer (trace_small.cu), RT_LGRID_BYTES */
+    /* The light bins depend on the scene and the lights only, not on the camera: a frame that finds both unchanged
+     * since the bins were built (static scene, moving camera) reuses them and its pre-pass runs the screen bins alone. */
+    bool lgrid_valid = false;
     /* light grid of big scenes (light_grid.cu): scratch + per light offsets / entries; rebuilt when stale */
     unsigned int *d_lgb_counts = nullptr, *d_lgb_sums = nullptr, *d_lgb_fail = nullptr;
     unsigned int* d_lgb_offsets[RT_LGB_LIGHTS] = {nullptr, nullptr};
@@ -143,12 +155,34 @@ int fail(rt_context* ctx, int code, const char* msg) {
     return code;
 }
 
+/* Replace *p by a fresh allocation of `count` elements (contents are not kept).  The new block is obtained first:
+ * when that fails the old one -- and with it every capacity the caller recorded -- stays valid. */
 template <class T>
 cudaError_t regrow(T** p, size_t count) {
+    T* fresh = nullptr;
+    if (count != 0) {
+        const cudaError_t e = cudaMalloc((void**)&fresh, sizeof(T) * count);
+        if (e != cudaSuccess) return e;
+    }
     if (*p) cudaFree(*p);
-    *p = nullptr;
-    if (count == 0) return cudaSuccess;
-    return cudaMalloc((void**)p, sizeof(T) * count);
+    *p = fresh;
+    return cudaSuccess;
+}
+
+void sky_free(RtSkyBlock* b) {
+    for (int i = 0; i < 4; i++) {
+        if (b->tex[i]) cudaDestroyTextureObject(b->tex[i]);
+        if (b->arr[i]) cudaFreeArray(b->arr[i]);
+    }
+    delete b;
+}
+
+/* the context stops using its sky block: only after everything it has enqueued has run */
+void sky_release(rt_context* ctx) {
+    if (!ctx->sky) return;
+    cudaStreamSynchronize(ctx->stream);
+    if (--ctx->sky->users == 0) sky_free(ctx->sky);
+    ctx->sky = nullptr;
 }
 
 typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -188,12 +222,13 @@ bool make_fxaa_tmap(rt_context* ctx, const unsigned int* img, int w, int h) {
     return true;
 }
 
-int run_fxaa(rt_context* ctx, const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh) {
+int run_fxaa(rt_context* ctx, const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
+             const RtPeerSync* peer) {
     const bool shard_ok = !sh || sh->n_shards <= 1 || (sh->tile_w % 64 == 0 && sh->tile_h % 32 == 0);
     const bool tma_ok = ctx->opt[RT_OPT_FXAA_IMPL] == 0 && (w % 4 == 0) && (((uintptr_t)in) % 16 == 0) && shard_ok &&
                         make_fxaa_tmap(ctx, in, w, h);
-    if (tma_ok) RT_CHECK(ctx, rt_launch_fxaa_tma(&ctx->tmap, in, out, w, h, sh, ctx->n_sm, ctx->stream));
-    else        RT_CHECK(ctx, rt_launch_fxaa_smem(in, out, w, h, sh, ctx->stream));
+    if (tma_ok) RT_CHECK(ctx, rt_launch_fxaa_tma(&ctx->tmap, in, out, w, h, sh, ctx->n_sm, peer, ctx->stream));
+    else        RT_CHECK(ctx, rt_launch_fxaa_smem(in, out, w, h, sh, peer, ctx->stream));
     return RT_OK;
 }
 
@@ -217,12 +252,16 @@ int rt_create(int device, rt_context** out) {
     ctx->scene.root = RT_NODE_SENTINEL;
     if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
     cudaDeviceGetAttribute(&ctx->n_sm, cudaDevAttrMultiProcessorCount, device);
-    if (cudaMalloc((void**)&ctx->d_counters, sizeof(RtCountersDev)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
-    cudaMemset(ctx->d_counters, 0, sizeof(RtCountersDev));
-    if (cudaMalloc((void**)&ctx->d_tile_counter, 64 * sizeof(unsigned int)) != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
-    cudaMemset(ctx->d_tile_counter, 0, 64 * sizeof(unsigned int));
-    if (rt_trace_small_init() != cudaSuccess) { delete ctx; return RT_ERR_CUDA; }
-    for (int i = 0; i < 6; i++) cudaEventCreate(&ctx->ev[i]);
+    bool ok = cudaMalloc((void**)&ctx->d_counters, sizeof(RtCountersDev)) == cudaSuccess &&
+              cudaMemset(ctx->d_counters, 0, sizeof(RtCountersDev)) == cudaSuccess &&
+              cudaMalloc((void**)&ctx->d_tile_counter, 64 * sizeof(unsigned int)) == cudaSuccess &&
+              cudaMemset(ctx->d_tile_counter, 0, 64 * sizeof(unsigned int)) == cudaSuccess &&
+              rt_trace_small_init() == cudaSuccess;
+    for (int i = 0; i < 6 && ok; i++) ok = cudaEventCreate(&ctx->ev[i]) == cudaSuccess;
+    if (!ok) {
+        rt_destroy(ctx);       /* frees whatever has been allocated so far */
+        return RT_ERR_CUDA;
+    }
     *out = ctx;
     return RT_OK;
 }
@@ -231,10 +270,7 @@ int rt_destroy(rt_context* ctx) {
     if (!ctx) return RT_ERR_ARG;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
-    for (int i = 0; i < 4 && ctx->own_sky; i++) {
-        if (ctx->sky_tex[i]) cudaDestroyTextureObject(ctx->sky_tex[i]);
-        if (ctx->sky_arr[i]) cudaFreeArray(ctx->sky_arr[i]);
-    }
+    sky_release(ctx);
     RtBuildBuffers& b = ctx->bb;
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
                     b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.node_other, b.flags, b.node_aux,
@@ -251,6 +287,7 @@ const char* rt_last_error(rt_context* ctx) { return ctx ? ctx->err.c_str() : "nu
 int rt_set_option(rt_context* ctx, int key, int value) {
     if (!ctx || key < 0 || key >= RT_OPT_N) return RT_ERR_ARG;
     ctx->scene_settled = false;
+    ctx->lgrid_valid = false;
     if ((key == RT_OPT_BUILDER || key == RT_OPT_FORCE_RADIX) && ctx->opt[key] != value)
         ctx->have_scene = false;   /* the next rt_set_scene rebuilds the hierarchy */
     ctx->opt[key] = value;
@@ -266,46 +303,49 @@ int rt_set_stream(rt_context* ctx, void* cuda_stream) {
 
 int rt_set_sky(rt_context* ctx, const unsigned char* const tex[4], int w, int h) {
     if (!ctx || !tex || w <= 0 || h <= 0) return RT_ERR_ARG;
-    RT_CHECK(ctx, cudaSetDevice(ctx->device));
-    if (!ctx->own_sky) {
-        for (int i = 0; i < 4; i++) { ctx->sky_tex[i] = 0; ctx->sky_arr[i] = nullptr; }
-        ctx->own_sky = true;
-    }
-    for (int i = 0; i < 4; i++) {
+    for (int i = 0; i < 4; i++)
         if (!tex[i]) return fail(ctx, RT_ERR_ARG, "null sky map");
-        if (ctx->sky_tex[i]) { cudaDestroyTextureObject(ctx->sky_tex[i]); ctx->sky_tex[i] = 0; }
-        if (ctx->sky_arr[i]) { cudaFreeArray(ctx->sky_arr[i]); ctx->sky_arr[i] = nullptr; }
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    /* build the new block completely, then swap: a failure leaves the context with the maps it had */
+    RtSkyBlock* b = new RtSkyBlock;
+    b->device = ctx->device;
+    cudaError_t e = cudaSuccess;
+    for (int i = 0; i < 4 && e == cudaSuccess; i++) {
         cudaChannelFormatDesc desc = cudaCreateChannelDesc<uchar4>();
-        RT_CHECK(ctx, cudaMallocArray(&ctx->sky_arr[i], &desc, w, h));
-        RT_CHECK(ctx, cudaMemcpy2DToArray(ctx->sky_arr[i], 0, 0, tex[i], (size_t)w * 4, (size_t)w * 4, h,
-                                          cudaMemcpyHostToDevice));
+        e = cudaMallocArray(&b->arr[i], &desc, w, h);
+        if (e == cudaSuccess)
+            e = cudaMemcpy2DToArray(b->arr[i], 0, 0, tex[i], (size_t)w * 4, (size_t)w * 4, h, cudaMemcpyHostToDevice);
         cudaResourceDesc rd;
         memset(&rd, 0, sizeof(rd));
         rd.resType = cudaResourceTypeArray;
-        rd.res.array.array = ctx->sky_arr[i];
+        rd.res.array.array = b->arr[i];
         cudaTextureDesc td;
         memset(&td, 0, sizeof(td));
         td.addressMode[0] = td.addressMode[1] = cudaAddressModeClamp;
         td.filterMode = cudaFilterModePoint;
         td.readMode = cudaReadModeElementType;
         td.normalizedCoords = 1;
-        RT_CHECK(ctx, cudaCreateTextureObject(&ctx->sky_tex[i], &rd, &td, nullptr));
+        if (e == cudaSuccess) e = cudaCreateTextureObject(&b->tex[i], &rd, &td, nullptr);
     }
-    ctx->have_sky = true;
+    if (e != cudaSuccess) {
+        sky_free(b);
+        RT_CHECK(ctx, e);
+    }
+    sky_release(ctx);      /* drains this context's stream; sharers of the old block keep it alive */
+    ctx->sky = b;
     return RT_OK;
 }
 
 int rt_share_sky(rt_context* ctx, rt_context* owner) {
     if (!ctx || !owner || ctx == owner) return RT_ERR_ARG;
-    if (!owner->have_sky) return fail(ctx, RT_ERR_STATE, "owner has no sky maps");
+    if (!owner->sky) return fail(ctx, RT_ERR_STATE, "owner has no sky maps");
     if (owner->device != ctx->device) return fail(ctx, RT_ERR_ARG, "sky maps live on another device");
-    for (int i = 0; i < 4 && ctx->own_sky; i++) {
-        if (ctx->sky_tex[i]) cudaDestroyTextureObject(ctx->sky_tex[i]);
-        if (ctx->sky_arr[i]) cudaFreeArray(ctx->sky_arr[i]);
-    }
-    for (int i = 0; i < 4; i++) { ctx->sky_tex[i] = owner->sky_tex[i]; ctx->sky_arr[i] = nullptr; }
-    ctx->own_sky = false;
-    ctx->have_sky = true;
+    if (ctx->sky == owner->sky) return RT_OK;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RtSkyBlock* b = owner->sky;
+    b->users++;            /* before the release: the two may already share a block */
+    sky_release(ctx);
+    ctx->sky = b;
     return RT_OK;
 }
 
@@ -325,7 +365,7 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
         return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
     if (n_lights != ctx->n_lights || (n_lights > 0 && memcmp(ctx->lights, lights, sizeof(rtb_Light) * (size_t)n_lights) != 0))
-        ctx->lgb_stale = true, ctx->lgb_waited = false;   /* the light grid of a big scene follows the lights */
+        ctx->lgb_stale = true, ctx->lgb_waited = false, ctx->lgrid_valid = false;   /* light grid / light bins follow the lights */
     for (int i = 0; i < n_lights; i++) ctx->lights[i] = lights[i];
     ctx->n_lights = n_lights;
 
@@ -341,7 +381,11 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
             if (objects[i].type != ctx->host_objs[i].type) { mode = 0; break; }
     }
     if (mode < 0) return RT_OK;
-    ctx->lgb_stale = true, ctx->lgb_waited = false;
+    /* From here to the end the device copy is in flux: an error return leaves the context without a scene, so that
+     * rt_render refuses to run and the next rt_set_scene rebuilds everything instead of classifying the change
+     * against host data that never reached the device. */
+    ctx->have_scene = false;
+    ctx->lgb_stale = true, ctx->lgb_waited = false, ctx->lgrid_valid = false;
     for (int i = 0; i < RT_LGB_LIGHTS; i++) ctx->scene.lg_offsets[i] = ctx->scene.lg_entries[i] = nullptr;
     const bool settled_before = ctx->scene_settled;   /* the stream ends in this context's own FXAA / copy kernel */
     ctx->scene_settled = false;
@@ -473,10 +517,12 @@ static int fill_frame(rt_context* ctx, const rt_frame* fr, const rt_shard* sh, R
         f->lights[i].intensity = l.intensity;
         f->lights[i].cr = l.color.x; f->lights[i].cg = l.color.y; f->lights[i].cb = l.color.z;
     }
-    for (int i = 0; i < 4; i++) f->sky[i] = ctx->sky_tex[i];
+    for (int i = 0; i < 4; i++) f->sky[i] = ctx->sky->tex[i];
     f->sky_all4 = ctx->opt[RT_OPT_SKY_ALL4];
     if (sh && sh->n_shards > 1) {
-        if (sh->tile_w < 1 || sh->tile_h < 1 || sh->shard_id < 0 || sh->shard_id >= sh->n_shards) return RT_ERR_ARG;
+        /* tiles of at least 2x2 pixels: a pixel's 3x3 neighbourhood then spans at most 2x2 tiles, which is what
+         * rt_shard_needs (trace_common.cuh) tests */
+        if (sh->tile_w < 2 || sh->tile_h < 2 || sh->shard_id < 0 || sh->shard_id >= sh->n_shards) return RT_ERR_ARG;
         f->tile_w = sh->tile_w; f->tile_h = sh->tile_h;
         f->n_shards = sh->n_shards; f->shard_id = sh->shard_id; f->stride = sh->stride;
     } else {
@@ -524,10 +570,11 @@ static int build_light_grid(rt_context* ctx) {
     return RT_OK;
 }
 
-int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_dev, int* hit_ids_dev) {
+static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_dev,
+                       int* hit_ids_dev, const RtPeerSync* peer) {
     if (!ctx || !frame || !out_dev || frame->imgw < 2 || frame->imgh < 2) return RT_ERR_ARG;
     if (!ctx->have_scene) return fail(ctx, RT_ERR_STATE, "rt_render before rt_set_scene");
-    if (!ctx->have_sky) return fail(ctx, RT_ERR_STATE, "rt_render before rt_set_sky");
+    if (!ctx->sky) return fail(ctx, RT_ERR_STATE, "rt_render before rt_set_sky");
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
     const size_t npx = (size_t)frame->imgw * frame->imgh;
     if (npx > ctx->cap_base) {
@@ -542,7 +589,7 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
     /* AA off, whole frame: the reference's second kernel only copies baseImage to the result (kernel.cu:275-278),
      * so the tracer writes the caller's buffer itself and no post kernel runs.  (Shards keep the copy: it is what
      * confines a rank's stores into a shared / peer frame to its own tiles.) */
-    const bool direct = !frame->alias && f.n_shards <= 1;
+    const bool direct = !frame->alias && f.n_shards <= 1 && !peer;
     unsigned int* const image = direct ? out_dev : ctx->d_base;
     ctx->last_base = image;
     if (count) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(RtCountersDev), ctx->stream));
@@ -558,7 +605,12 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
             RT_CHECK(ctx, regrow(&ctx->d_tile_lists, need));
             ctx->cap_tile_lists = need;
         }
-        if (!ctx->d_lgrid && ctx->opt[RT_OPT_SHADOW_BINS] != 1) RT_CHECK(ctx, regrow(&ctx->d_lgrid, RT_LGRID_BYTES / sizeof(uint4)));
+        if (!ctx->d_lgrid && ctx->opt[RT_OPT_SHADOW_BINS] != 1) {
+            RT_CHECK(ctx, regrow(&ctx->d_lgrid, RT_LGRID_BYTES / sizeof(uint4)));
+            ctx->lgrid_valid = false;
+        }
+        const bool use_lgrid = ctx->opt[RT_OPT_SHADOW_BINS] != 1;
+        const bool build_lgrid = use_lgrid && !(ctx->lgrid_valid && ctx->opt[RT_OPT_LIGHT_BINS_REUSE] == 0);
         /* Order history: a frame files every patch under its measured cost; the next frame of the same size
          * and shard starts with the most expensive ones (frame-to-frame coherence of an interactive renderer;
          * the first frame of a kind walks bottom-up).  Pure scheduling: pixels do not depend on it. */
@@ -589,9 +641,9 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
         RT_CHECK(ctx, rt_launch_trace_small(&ctx->scene, &f, image, hit_ids_dev, ctx->d_counters,
                                             ctx->d_tile_counter, ctx->d_tile_lists, count,
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
-                                            ctx->scene_settled ? 1 : 0,
-                                            ctx->opt[RT_OPT_SHADOW_BINS] != 1 ? ctx->d_lgrid : (uint4*)nullptr,
-                                            ctx->opt[RT_OPT_MIRROR_BINS] == 0, ctx->stream));
+                                            ctx->scene_settled ? 1 : 0, use_lgrid ? ctx->d_lgrid : (uint4*)nullptr,
+                                            build_lgrid ? 1 : 0, ctx->opt[RT_OPT_MIRROR_BINS] == 0, ctx->stream));
+        if (use_lgrid) ctx->lgrid_valid = true;
     }
     else {
         /* The grid costs ~2 ms to build for a million triangles and saves ~0.4 ms per 4K frame: it is built when a
@@ -616,14 +668,18 @@ int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, uns
     }
     if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }
     int rc = RT_OK;
-    if (frame->alias) rc = run_fxaa(ctx, ctx->d_base, out_dev, frame->imgw, frame->imgh, shard);
-    else if (!direct) RT_CHECK(ctx, rt_launch_copy(ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, ctx->stream));
+    if (frame->alias) rc = run_fxaa(ctx, ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, peer);
+    else if (!direct) RT_CHECK(ctx, rt_launch_copy(ctx->d_base, out_dev, frame->imgw, frame->imgh, shard, peer, ctx->stream));
     if (rc != RT_OK) return rc;
     if (timing) { cudaEventRecord(ctx->ev[3], ctx->stream); ctx->timing_valid = true; }
     /* `settled` promises the next frame that the stream ends in this context's own post kernel (its pre-pass and
      * refit then overlap it); after a direct frame it ends in the tracer, which still reads what they write */
     ctx->scene_settled = !direct;
     return RT_OK;
+}
+
+int rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_dev, int* hit_ids_dev) {
+    return render_impl(ctx, frame, shard, out_dev, hit_ids_dev, nullptr);
 }
 
 int rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_host,
@@ -656,7 +712,7 @@ int rt_fxaa(rt_context* ctx, const unsigned int* in_dev, unsigned int* out_dev, 
             const rt_shard* shard) {
     if (!ctx || !in_dev || !out_dev || imgw < 1 || imgh < 1) return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
-    return run_fxaa(ctx, in_dev, out_dev, imgw, imgh, shard);
+    return run_fxaa(ctx, in_dev, out_dev, imgw, imgh, shard, nullptr);
 }
 
 int rt_shard_tile_count(const rt_shard* sh, int imgw, int imgh) {
@@ -681,6 +737,7 @@ struct rt_peer_frame {
     size_t n_pixels = 0;
     int n_buffers = 0;
     bool owner = false;
+    unsigned int timeout_ms = RT_PEER_TIMEOUT_MS_DEFAULT;
     unsigned int* flags() const { return base + (size_t)n_buffers * n_pixels; }
 };
 
@@ -732,7 +789,36 @@ unsigned int* rt_peer_frame_buffer(rt_peer_frame* pf, unsigned int seq) {
 int rt_peer_frame_acquire(rt_context* ctx, rt_peer_frame* pf, unsigned int seq) {
     if (!ctx || !pf) return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
-    RT_CHECK(ctx, rt_launch_peer_acquire(pf->flags(), seq - (unsigned int)pf->n_buffers, ctx->stream));
+    RT_CHECK(ctx, rt_launch_peer_acquire(pf->flags(), seq - (unsigned int)pf->n_buffers, pf->timeout_ms, ctx->stream));
+    return RT_OK;
+}
+
+/* acquire + sharded render into the frame's buffer + signal, the two halves of the hand-shake carried by the frame's
+ * last kernel (RtPeerSync): three launches per producer frame */
+int rt_render_peer(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, rt_peer_frame* pf, int rank,
+                   unsigned int seq, int* hit_ids_dev) {
+    if (!ctx || !pf || !frame || rank < 0 || rank >= 16) return RT_ERR_ARG;
+    if ((size_t)frame->imgw * (size_t)frame->imgh > pf->n_pixels) return fail(ctx, RT_ERR_ARG, "frame larger than the peer buffer");
+    RtPeerSync ps;
+    ps.flags = pf->flags();
+    ps.ticket = ctx->d_tile_counter + 48;      /* its own 32-byte sector of the context's counter block */
+    ps.acquire_seq = seq - (unsigned int)pf->n_buffers;
+    ps.seq = seq;
+    ps.rank = rank;
+    ps.timeout_ms = pf->timeout_ms;
+    return render_impl(ctx, frame, shard, rt_peer_frame_buffer(pf, seq), hit_ids_dev, &ps);
+}
+
+int rt_peer_frame_set_timeout(rt_peer_frame* pf, unsigned int timeout_ms) {
+    if (!pf || timeout_ms == 0) return RT_ERR_ARG;
+    pf->timeout_ms = timeout_ms;
+    return RT_OK;
+}
+
+int rt_peer_frame_reset_error(rt_context* ctx, rt_peer_frame* pf) {
+    if (!ctx || !pf) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, rt_launch_peer_reset_error(pf->flags(), ctx->stream));
     return RT_OK;
 }
 
@@ -746,7 +832,7 @@ int rt_peer_frame_signal(rt_context* ctx, rt_peer_frame* pf, int rank, unsigned 
 int rt_peer_frame_wait(rt_context* ctx, rt_peer_frame* pf, int n_ranks, unsigned int seq) {
     if (!ctx || !pf || n_ranks < 1 || n_ranks > 16) return RT_ERR_ARG;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
-    RT_CHECK(ctx, rt_launch_peer_wait(pf->flags(), n_ranks, seq, ctx->stream));
+    RT_CHECK(ctx, rt_launch_peer_wait(pf->flags(), n_ranks, seq, pf->timeout_ms, ctx->stream));
     return RT_OK;
 }
 
@@ -863,21 +949,13 @@ int rt_sort_pairs(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_de
     if (n <= 1) return RT_OK;
     RT_CHECK(ctx, cudaSetDevice(ctx->device));
     unsigned int *tk = nullptr, *tv = nullptr, *hist = nullptr;
-    RT_CHECK(ctx, cudaMalloc((void**)&tk, sizeof(unsigned int) * (size_t)n));
-    RT_CHECK(ctx, cudaMalloc((void**)&tv, sizeof(unsigned int) * (size_t)n));
-    RT_CHECK(ctx, cudaMalloc((void**)&hist, sizeof(unsigned int) * (size_t)rt_radix_hist_entries(n)));
-    cudaError_t e = rt_radix_sort_pairs(keys_dev, vals_dev, tk, tv, hist, n, 1, ctx->stream);
-    cudaStreamSynchronize(ctx->stream);
+    cudaError_t e = cudaMalloc((void**)&tk, sizeof(unsigned int) * (size_t)n);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&tv, sizeof(unsigned int) * (size_t)n);
+    if (e == cudaSuccess) e = cudaMalloc((void**)&hist, sizeof(unsigned int) * (size_t)rt_radix_hist_entries(n));
+    if (e == cudaSuccess) e = rt_radix_sort_pairs(keys_dev, vals_dev, tk, tv, hist, n, 1, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(tk); cudaFree(tv); cudaFree(hist);
     RT_CHECK(ctx, e);
-    return RT_OK;
-}
-
-int rt_sort_pairs_cub(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n) {
-    if (!ctx || n < 0) return RT_ERR_ARG;
-    if (n <= 1) return RT_OK;
-    RT_CHECK(ctx, cudaSetDevice(ctx->device));
-    RT_CHECK(ctx, rt_cub_sort_pairs(keys_dev, vals_dev, n, ctx->stream));
     return RT_OK;
 }
 
@@ -926,6 +1004,16 @@ void launchKernel(unsigned int* result, int imgw, int imgh, rtb_Camera cam, rtb_
 
 /* the context behind launchKernel (tests: options, counters) */
 rt_context* rt_legacy_context(void) { return g_legacy; }
+
+/* The reference never frees what launchKernel allocated (kernel.cu:419-441).  A host that wants the memory back, or
+ * other sky maps, calls this: the next launchKernel starts from scratch and reads its texture arguments again. */
+int rtb_legacy_shutdown(void) {
+    int rc = RT_OK;
+    if (g_legacy) rc = rt_destroy(g_legacy);
+    g_legacy = nullptr;
+    g_legacy_sky = false;
+    return rc;
+}
 
 void rtb_scene_launch(rtb_scene* s, unsigned int* out_dev, int imgw, int imgh, unsigned char* tex[4], int texw,
                       int texh) {

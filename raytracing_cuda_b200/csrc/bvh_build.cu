@@ -862,7 +862,8 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         if (n >= 2) {
             if (builder != 1 && n <= PLOC_MAX) {
                 /* PLOC nodes cover no contiguous leaf range: every join of the refit takes the global protocol */
-                cudaMemsetAsync(b->node_other, 0xFF, sizeof(int) * (size_t)(n - 1), stream);
+                e = cudaMemsetAsync(b->node_other, 0xFF, sizeof(int) * (size_t)(n - 1), stream);
+                if (e != cudaSuccess) return e;
                 rt_ploc_small_kernel<<<1, PLOC_MAX, 0, stream>>>(b->vals, n, b->prim_lo, b->prim_hi, b->children,
                                                                  b->node_parent, b->leaf_parent);
             } else

@@ -25,23 +25,39 @@
 
 #include "rt_device.h"
 #include "fxaa_core.cuh"
+#include "peer_sync.cuh"
 
 /* ------------------------------------------------------------------ plain shared-memory kernel */
 
 #define FX_BW 32
 #define FX_BH 8
 
+/* one thread of the CTA waits for the owner's release of the peer buffer (RtPeerSync); everybody learns the outcome */
+__device__ __forceinline__ bool fx_peer_acquire(const RtPeerSync& peer, bool leader) {
+    __shared__ int s_peer_ok;
+    if (leader)
+        s_peer_ok = rt_peer_spin(peer.flags, RT_PEER_FLAG_RELEASED, peer.acquire_seq, peer.timeout_ms,
+                                 0x100u + (unsigned int)peer.rank) ? 1 : 0;
+    __syncthreads();
+    return s_peer_ok != 0;
+}
+
 __global__ void __launch_bounds__(FX_BW * FX_BH)
 rt_fxaa_smem_kernel(const unsigned int* __restrict__ in, unsigned int* __restrict__ out, int w, int h,
-                    int tile_w, int tile_h, int n_shards, int shard_id, int stride) {
+                    int tile_w, int tile_h, int n_shards, int shard_id, int stride, const RtPeerSync peer) {
     __shared__ unsigned int s_px[FX_BH + 2][FX_BW + 2];
     __shared__ float s_lum[FX_BH + 2][FX_BW + 2];
     const int x0 = blockIdx.x * FX_BW - 1, y0 = blockIdx.y * FX_BH - 1;
+    const bool leader = threadIdx.x == 0 && threadIdx.y == 0;
+    const unsigned int n_ctas = gridDim.x * gridDim.y;
     if (n_shards > 1) {
         /* blocks that own no pixel of this shard leave before touching memory */
         const int px = blockIdx.x * FX_BW + threadIdx.x, py = blockIdx.y * FX_BH + threadIdx.y;
         const bool mine = px < w && py < h && rt_tile_owner(px, py, tile_w, tile_h, n_shards, stride) == shard_id;
-        if (!__syncthreads_or(mine)) return;
+        if (!__syncthreads_or(mine)) {
+            if (peer.flags) rt_peer_publish(peer, n_ctas, leader);
+            return;
+        }
     }
     for (int i = threadIdx.y * FX_BW + threadIdx.x; i < (FX_BH + 2) * (FX_BW + 2); i += FX_BW * FX_BH) {
         const int ly = i / (FX_BW + 2), lx = i % (FX_BW + 2);
@@ -52,21 +68,23 @@ rt_fxaa_smem_kernel(const unsigned int* __restrict__ in, unsigned int* __restric
         s_lum[ly][lx] = fx_lum(c);
     }
     __syncthreads();
+    const bool may_store = peer.flags ? fx_peer_acquire(peer, leader) : true;
     const int x = blockIdx.x * FX_BW + threadIdx.x, y = blockIdx.y * FX_BH + threadIdx.y;
-    if (x >= w || y >= h) return;
-    if (n_shards > 1 && rt_tile_owner(x, y, tile_w, tile_h, n_shards, stride) != shard_id) return;
-    const int lx = threadIdx.x + 1, ly = threadIdx.y + 1;
-    const unsigned int centre = s_px[ly][lx];
-    unsigned int result = centre;
-    if (x > 0 && y > 0 && x + 1 < w && y + 1 < h) {
-        float b;
-        int dx, dy;
-        if (fx_decide(s_lum[ly][lx], s_lum[ly][lx + 1], s_lum[ly][lx - 1], s_lum[ly - 1][lx], s_lum[ly + 1][lx],
-                      s_lum[ly - 1][lx + 1], s_lum[ly - 1][lx - 1], s_lum[ly + 1][lx + 1], s_lum[ly + 1][lx - 1],
-                      b, dx, dy))
-            result = fx_blend(centre, s_px[ly + dy][lx + dx], b);
+    if (may_store && x < w && y < h && (n_shards <= 1 || rt_tile_owner(x, y, tile_w, tile_h, n_shards, stride) == shard_id)) {
+        const int lx = threadIdx.x + 1, ly = threadIdx.y + 1;
+        const unsigned int centre = s_px[ly][lx];
+        unsigned int result = centre;
+        if (x > 0 && y > 0 && x + 1 < w && y + 1 < h) {
+            float b;
+            int dx, dy;
+            if (fx_decide(s_lum[ly][lx], s_lum[ly][lx + 1], s_lum[ly][lx - 1], s_lum[ly - 1][lx], s_lum[ly + 1][lx],
+                          s_lum[ly - 1][lx + 1], s_lum[ly - 1][lx - 1], s_lum[ly + 1][lx + 1], s_lum[ly + 1][lx - 1],
+                          b, dx, dy))
+                result = fx_blend(centre, s_px[ly + dy][lx + dx], b);
+        }
+        out[(size_t)y * w + x] = result;
     }
-    out[(size_t)y * w + x] = result;
+    if (peer.flags) rt_peer_publish(peer, n_ctas, leader);
 }
 
 /* ------------------------------------------------------------------ TMA-staged persistent kernel */
@@ -177,7 +195,7 @@ __device__ __forceinline__ void fx_filter_tile(const unsigned int* __restrict__ 
 __global__ void __launch_bounds__(FX_THREADS)
 rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned int* __restrict__ in,
                    unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride, int kx,
-                   int ky) {
+                   int ky, const RtPeerSync peer) {
     __shared__ __align__(128) unsigned int s_px[2][FX_STAGE_WORDS];
     __shared__ float s_lum[FX_BOXH][FX_BOXW];
     __shared__ __align__(8) uint64_t s_bar[2];
@@ -202,6 +220,9 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         fx_mbar_expect_tx(&s_bar[0], FX_STAGE_BYTES);
         fx_tma_load_2d(&s_px[0][0], &in_map, tx * FX_TW - FX_HALO_X, ty * FX_TH - 1, &s_bar[0]);
     }
+    /* peer frame: the owner must have released the buffer before the first store; the first tile is already on its
+     * way into shared memory meanwhile.  A wait that gave up leaves the buffer alone (error word set). */
+    const bool may_store = peer.flags ? fx_peer_acquire(peer, tid == 0) : true;
     uint32_t phases = 0;   /* bit s = parity to wait for on stage s */
     int stage = 0;
     /* whole frames: the next tile by addition (k advances by gridDim.x), no division in the loop */
@@ -231,8 +252,9 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
             __syncthreads();
             /* tiles that touch no frame border skip the per-pixel bounds and border tests */
             const bool inner = tx > 0 && ty > 0 && (tx + 1) * FX_TW < w && (ty + 1) * FX_TH < h;
-            if (inner) fx_filter_tile<true>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
-            else       fx_filter_tile<false>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
+            if (!may_store) ;
+            else if (inner) fx_filter_tile<true>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
+            else            fx_filter_tile<false>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
         }
         __syncthreads();   /* everyone is done with s_px[stage] and s_lum before they are refilled */
         k = kn;
@@ -241,15 +263,24 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         have = have_next;
         stage ^= 1;
     }
+    if (peer.flags) rt_peer_publish(peer, gridDim.x, tid == 0);
 }
 
 /* pass-through when AA is off (reference kernel.cu:275-278), shard-aware */
 __global__ void rt_copy_kernel(const unsigned int* __restrict__ in, unsigned int* __restrict__ out, int w, int h,
-                               int tile_w, int tile_h, int n_shards, int shard_id, int stride) {
+                               int tile_w, int tile_h, int n_shards, int shard_id, int stride, const RtPeerSync peer) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
-    if (x >= w || y >= h) return;
-    if (n_shards > 1 && rt_tile_owner(x, y, tile_w, tile_h, n_shards, stride) != shard_id) return;
-    out[(size_t)y * w + x] = in[(size_t)y * w + x];
+    const bool leader = threadIdx.x == 0 && threadIdx.y == 0;
+    const bool mine = x < w && y < h && (n_shards <= 1 || rt_tile_owner(x, y, tile_w, tile_h, n_shards, stride) == shard_id);
+    if (!peer.flags) {
+        if (mine) out[(size_t)y * w + x] = in[(size_t)y * w + x];
+        return;
+    }
+    const unsigned int v = mine ? in[(size_t)y * w + x] : 0u;
+    if (__syncthreads_or(mine)) {
+        if (fx_peer_acquire(peer, leader) && mine) out[(size_t)y * w + x] = v;
+    }
+    rt_peer_publish(peer, gridDim.x * gridDim.y, leader);
 }
 
 /* The reference's `factor` knob (main.cpp:40-47): the frame is rendered at factor x the window size and the
@@ -302,19 +333,26 @@ __global__ void rt_pack_tiles_kernel(const unsigned int* __restrict__ frame, uns
     }
 }
 
+static RtPeerSync fx_peer_arg(const RtPeerSync* peer) {
+    RtPeerSync p = {nullptr, nullptr, 0u, 0u, 0, 0u};
+    if (peer) p = *peer;
+    return p;
+}
+
 extern "C" cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h,
-                                           const rt_shard* sh, cudaStream_t stream) {
+                                           const rt_shard* sh, const RtPeerSync* peer, cudaStream_t stream) {
     dim3 block(FX_BW, FX_BH, 1), grid((w + FX_BW - 1) / FX_BW, (h + FX_BH - 1) / FX_BH, 1);
     if (sh && sh->n_shards > 1)
         rt_fxaa_smem_kernel<<<grid, block, 0, stream>>>(in, out, w, h, sh->tile_w, sh->tile_h, sh->n_shards,
-                                                        sh->shard_id, sh->stride);
+                                                        sh->shard_id, sh->stride, fx_peer_arg(peer));
     else
-        rt_fxaa_smem_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0);
+        rt_fxaa_smem_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0, fx_peer_arg(peer));
     return cudaGetLastError();
 }
 
 extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out,
-                                          int w, int h, const rt_shard* sh, int n_sm, cudaStream_t stream) {
+                                          int w, int h, const rt_shard* sh, int n_sm, const RtPeerSync* peer,
+                                          cudaStream_t stream) {
     const int tiles_x = (w + FX_TW - 1) / FX_TW, tiles_y = (h + FX_TH - 1) / FX_TH;
     int n = 1, id = 0, st = 0, kx = 1, ky = 1;
     int slots = tiles_x * tiles_y;
@@ -336,19 +374,19 @@ extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned
     cfg.stream = stream;
     cfg.attrs = pdl;
     cfg.numAttrs = 1;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, rt_fxaa_tma_kernel, *map, in, out, w, h, n, id, st, kx, ky);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, rt_fxaa_tma_kernel, *map, in, out, w, h, n, id, st, kx, ky, fx_peer_arg(peer));
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
 extern "C" cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
-                                      cudaStream_t stream) {
+                                      const RtPeerSync* peer, cudaStream_t stream) {
     dim3 block(32, 8, 1), grid((w + 31) / 32, (h + 7) / 8, 1);
     if (sh && sh->n_shards > 1)
         rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, sh->tile_w, sh->tile_h, sh->n_shards, sh->shard_id,
-                                                   sh->stride);
+                                                   sh->stride, fx_peer_arg(peer));
     else
-        rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0);
+        rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, 1, 1, 1, 0, 0, fx_peer_arg(peer));
     return cudaGetLastError();
 }
 

@@ -44,7 +44,23 @@
 #define RT_PEER_FLAG_UINTS 256
 #define RT_PEER_FLAG_DONE(k) (8 * (k))     /* frame number rank k (< 16) has finished */
 #define RT_PEER_FLAG_RELEASED 128          /* frame number the owner has released */
-#define RT_PEER_FLAG_ERROR 136             /* set by a wait that gave up */
+#define RT_PEER_FLAG_ERROR 136             /* set by a wait that gave up: 1 + k = the owner waiting for rank k,
+                                            * 0x100 + k = rank k waiting for the owner's release */
+#define RT_PEER_TIMEOUT_MS_DEFAULT 10000u
+
+/* Hand-shake of a rank's sharded frame with the owner of a peer frame, carried by the frame's LAST kernel (FXAA or
+ * copy, fxaa.cu) instead of one-thread kernels around it: before its first store into the peer buffer every CTA
+ * waits until the owner has released the buffer's previous use (flags[RELEASED] >= acquire_seq), and the last CTA to
+ * finish (ticket counter in this GPU's memory) publishes flags[DONE(rank)] = seq behind a system-scope fence.
+ * flags == NULL: no hand-shake. */
+struct RtPeerSync {
+    unsigned int* flags;       /* flag block behind the owner's frames (peer mapping, or local on the owner) */
+    unsigned int* ticket;      /* this context's CTA ticket counter (self re-arming) */
+    unsigned int acquire_seq;  /* wait for released >= this */
+    unsigned int seq;          /* publish this */
+    int rank;
+    unsigned int timeout_ms;
+};
 #define RT_BYVALUE_MAX 304             /* objects passed in kernel parameters (68 B each) by the per-frame refit */
 /* light bins of the small-scene tracer (trace_small.cu): per light a cube map of RT_LGRID_G x RT_LGRID_G direction
  * bins per face, each bin one uint4 = 8 ushorts: [0] count (0xFFFF: too many, traverse), [1..7] leaf offsets */

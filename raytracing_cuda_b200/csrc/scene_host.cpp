@@ -328,27 +328,30 @@ void calc_sky_vars(rtb_scene* s) {
     if (d > 4 && d < 6)   { k[0] = (d - 4) / 2;  k[3] = 1.0f - k[0]; }
 }
 
-/* reference scene.cpp:758-776 */
+/* Sun and moon (reference scene.cpp:758-776) as two ends of one arm: the arm turns once a day in a circle of radius
+ * dayNightDistance that is tilted by -45 degrees about the vertical and centred on (-500, 0, 500); noon-ish phase
+ * offset -120 degrees.  Both point lights shine with |height of the sun| / radius, and the two emissive spheres
+ * ride along.  Float expression shapes are the reference's (x * -1 is an exact negation, (-p) + c == c + (-p)), so the
+ * states stay bit-identical to its compiled scene.cpp (tests/test_scene_host.py). */
 void move_lights(rtb_scene* s) {
-    float a = to_rad(fmodf((s->dayNightTime / 24.0f) * 360 - 120, 360));
-    s->lights[0].pos = rot_y(vscale(v3(cosf(a), sinf(a), 0), s->dayNightDistance), to_rad(-45));
-    s->lights[1].pos = vscale(s->lights[0].pos, -1);
-    const float o = 500;
-    const vec3 offset = v3(-o, 0, o);
-    s->lights[0].pos = vadd(s->lights[0].pos, offset);
-    s->lights[1].pos = vadd(s->lights[1].pos, offset);
-    s->objects[s->vecLight[0]].pos = s->lights[0].pos;
-    s->objects[s->vecLight[1]].pos = s->lights[1].pos;
-    float val = fabsf(s->lights[0].pos.y) / s->dayNightDistance;
-    s->lights[0].color = vscale(v3(1, 1, 1), val);
-    s->lights[1].color = vscale(s->lights[0].color, 1);
+    const vec3 centre = v3(-500.0f, 0.0f, 500.0f);
+    const float phase = to_rad(fmodf((s->dayNightTime / 24.0f) * 360 - 120, 360));
+    const vec3 arm = rot_y(vscale(v3(cosf(phase), sinf(phase), 0), s->dayNightDistance), to_rad(-45));
+    const vec3 body[2] = {vadd(arm, centre), vadd(vscale(arm, -1), centre)};
+    const float glow = fabsf(body[0].y) / s->dayNightDistance;
+    for (int k = 0; k < 2; k++) {
+        s->lights[k].pos = body[k];
+        s->lights[k].color = v3(glow, glow, glow);
+        s->objects[s->vecLight[k]].pos = body[k];
+    }
 }
 
+/* "HH:MM\n" of the day clock; minutes from the truncated hundredths of an hour, as reference scene.cpp:732 prints */
 void write_clock(rtb_scene* s) {
-    /* reference scene.cpp:732 */
-    float t = s->dayNightTime;
-    snprintf(s->clock, sizeof(s->clock), "%02d:%02d\n", (int)t,
-             (int)(((int)(t * 100) % 100) / 100.0 * 60));
+    const int hours = (int)s->dayNightTime;
+    const int hundredths = (int)(s->dayNightTime * 100) % 100;
+    const int minutes = (int)(hundredths / 100.0 * 60);
+    snprintf(s->clock, sizeof(s->clock), "%02d:%02d\n", hours, minutes);
 }
 
 }  // namespace

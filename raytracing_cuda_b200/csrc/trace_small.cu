@@ -831,7 +831,8 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
                                              int* hit_ids, RtCountersDev* counters, unsigned int* tile_counter,
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
                                              const unsigned int* order_r, unsigned int* order_w,
-                                             int after_own_post, uint4* lgrid, int mirror_bins, cudaStream_t stream) {
+                                             int after_own_post, uint4* lgrid, int build_lgrid, int mirror_bins,
+                                             cudaStream_t stream) {
     /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel.
      * after_own_post: the previous operation on the stream is the FXAA / copy kernel of this context's previous
      * frame (nothing this frame reads is still being written): the pre-pass overlaps it, see rt_cull_tiles_kernel */
@@ -855,7 +856,8 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.numAttrs = 1;
     const int cull_blocks = (bins + 7) / 8;
     const int lit = f->n_lights < RT_LGRID_LIGHTS ? f->n_lights : RT_LGRID_LIGHTS;    /* lights with bins */
-    cfg.gridDim = dim3(cull_blocks + (lgrid ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
+    /* build_lgrid = 0: the light bins in `lgrid` are still those of this scene and these lights (api.cu) */
+    cfg.gridDim = dim3(cull_blocks + (lgrid && build_lgrid ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
     cfg.blockDim = dim3(256, 1, 1);
     cfg.dynamicSmemBytes = 0;
     cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins,

@@ -175,9 +175,8 @@ class Renderer:
                                               keys.ctypes.data if len(keys) else None), "rt_bvh_download")
         return nodes, ids, keys
 
-    def sort_pairs(self, keys_dev, vals_dev, n, use_cub=False):
-        fn = self._lib.rt_sort_pairs_cub if use_cub else self._lib.rt_sort_pairs
-        self._check(fn(self._h, _ptr(keys_dev), _ptr(vals_dev), int(n)), "rt_sort_pairs")
+    def sort_pairs(self, keys_dev, vals_dev, n):
+        self._check(self._lib.rt_sort_pairs(self._h, _ptr(keys_dev), _ptr(vals_dev), int(n)), "rt_sort_pairs")
 
 
 def rays_per_frame(counters):

@@ -12,9 +12,12 @@ Two ways to use N GPUs, one process per GPU:
 
 The numpy pack/unpack below restate the CUDA kernels for the CPU (gloo) tests of this logic.
 """
+import ctypes as C
+
 import numpy as np
 
-from .renderer import default_stride, make_shard  # noqa: F401
+from . import _lib
+from .renderer import _ptr, default_stride, make_shard  # noqa: F401
 
 
 def tile_grid(imgw, imgh, tile_w, tile_h):
@@ -117,9 +120,6 @@ class PeerFrame:
     """
 
     def __init__(self, renderer, rank, world, n_pixels, exchange, owner_rank=0, n_buffers=2):
-        import ctypes as C
-
-        from . import _lib
         self.r, self.rank, self.world, self.owner_rank = renderer, rank, world, owner_rank
         self.n_pixels, self.n_buffers = int(n_pixels), int(n_buffers)
         self._lib = renderer._lib
@@ -138,23 +138,48 @@ class PeerFrame:
     def buffer_ptr(self, seq):
         return self._lib.rt_peer_frame_buffer(self._pf, seq)
 
-    def render(self, frame, shard, seq, hit_ids=None):
+    def render(self, frame, shard, seq, hit_ids=None, fused=True):
+        """This rank's tiles of frame `seq` into the owner's buffer.  fused (default): rt_render_peer -- the frame's
+        last kernel waits for the buffer and signals completion itself, three launches in all; else the hand-shake
+        as two one-thread kernels around a plain rt_render."""
         r = self.r
+        if fused:
+            r._check(self._lib.rt_render_peer(r._h, C.byref(frame), C.byref(shard), self._pf, self.rank, seq,
+                                              _ptr(hit_ids)), "rt_render_peer")
+            return
         r._check(self._lib.rt_peer_frame_acquire(r._h, self._pf, seq), "rt_peer_frame_acquire")
         r.render(frame, self.buffer_ptr(seq), hit_ids=hit_ids, shard=shard)
         r._check(self._lib.rt_peer_frame_signal(r._h, self._pf, self.rank, seq), "rt_peer_frame_signal")
 
-    def wait(self, seq):
+    def wait(self, seq, check=True):
+        """Owner: every rank has finished frame `seq` (asynchronous on the context's stream).  check=True also
+        synchronises and raises if any wait of the hand-shake gave up -- the frame is invalid then; a caller that
+        pipelines frames passes check=False and calls check() before it uses a frame."""
         self.r._check(self._lib.rt_peer_frame_wait(self.r._h, self._pf, self.world, seq), "rt_peer_frame_wait")
+        if check:
+            self.check()
+
+    def check(self):
+        e = self.error()
+        if e:
+            who = ("the owner gave up waiting for rank %d" % (e - 1)) if e < 0x100 else \
+                ("rank %d gave up waiting for the owner's release" % (e - 0x100))
+            raise _lib.RtError("peer frame invalid: %s (error word 0x%x); reset_error() re-arms it" % (who, e))
 
     def release(self, seq):
         self.r._check(self._lib.rt_peer_frame_release(self.r._h, self._pf, seq), "rt_peer_frame_release")
 
+    def set_timeout(self, ms):
+        """Give-up time of this process's waits (default 10 s): raise it when ranks start far apart."""
+        self.r._check(self._lib.rt_peer_frame_set_timeout(self._pf, int(ms)), "rt_peer_frame_set_timeout")
+
     def error(self):
-        import ctypes as C
         e = C.c_uint(0)
         self.r._check(self._lib.rt_peer_frame_error(self.r._h, self._pf, C.byref(e)), "rt_peer_frame_error")
         return e.value
+
+    def reset_error(self):
+        self.r._check(self._lib.rt_peer_frame_reset_error(self.r._h, self._pf), "rt_peer_frame_reset_error")
 
     def tensor(self, seq):
         """The frame buffer of `seq` as a torch int32 tensor (valid in this process; on the owner it is local)."""

@@ -8,7 +8,7 @@ import raytracing_cuda_b200 as rt  # noqa: E402
 from raytracing_cuda_b200 import sharding  # noqa: E402
 
 handle = bytes.fromhex(sys.argv[1])
-w, h, tw, th = (int(v) for v in sys.argv[2:6])
+w, h, tw, th, fused = (int(v) for v in sys.argv[2:7])
 r = rt.Renderer(0)
 r.set_sky(rt.synthetic_sky(256, 128))
 s = rt.Scene()
@@ -18,7 +18,7 @@ pf = sharding.PeerFrame(r, 1, 2, w * h, lambda _: handle)
 shard = rt.make_shard(2, 1, tw, th)
 print("ready", flush=True)
 for seq in (1, 2, 3):
-    pf.render(f, shard, seq)
+    pf.render(f, shard, seq, fused=bool(fused))
 r.synchronize()
 err = pf.error()
 pf.close()
