@@ -11,6 +11,7 @@ oracle/_ref/libref_scene.so            the reference's scene.cpp as it lies unde
 oracle/_ref/libref_trace_cpu.so        the reference's kernel.cu:9-403 (device functions and both
                                        kernels) compiled for the HOST under ref_shims/cpu_cuda_shim.h,
                                        + ref_trace_cpu_wrap.inc
+oracle/_ref/backgrounds/*.png          the reference's four sky maps (data, copied as they are)
 oracle/_ref/libref_kernel_sm100.so     the reference's kernel.cu rebuilt for sm_100 with the minimum
                                        patch CUDA 12.9 needs (texture references -> texture objects,
                                        explicit float casts at kernel.cu:163) and a primary hit-id tap;
@@ -231,6 +232,22 @@ def build_ref_kernel_gpu(force=False):
     return out
 
 
+def copy_backgrounds(force=False):
+    """The four sky maps the reference loads at start-up (scene.cpp:626-632; 4.3 MB of PNG, data not source) ->
+    git-ignored oracle/_ref/backgrounds/, so that they travel to the GPU box like the .so files: the parity tests
+    and bench.py then sample the reference's real inputs."""
+    src = os.path.join(REF, "backgrounds")
+    dst = os.path.join(OUT, "backgrounds")
+    if not os.path.isdir(src):
+        return None
+    os.makedirs(dst, exist_ok=True)
+    for name in ("morning.png", "day.png", "evening.png", "night.png"):
+        a, b = os.path.join(src, name), os.path.join(dst, name)
+        if force or not os.path.isfile(b) or os.path.getsize(a) != os.path.getsize(b):
+            shutil.copyfile(a, b)
+    return dst
+
+
 def build_all(force=False, gpu_ref=True):
     built = {"oracle": build_oracle(force)}
     if have_reference():
@@ -239,6 +256,7 @@ def build_all(force=False, gpu_ref=True):
         built["ref_trace_cpu"] = build_ref_trace_cpu(force)
         if gpu_ref:
             built["ref_kernel_gpu"] = build_ref_kernel_gpu(force)
+        built["backgrounds"] = copy_backgrounds(force)
     return built
 
 

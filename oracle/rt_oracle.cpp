@@ -371,4 +371,17 @@ int oracle_check_hit(const rtb_Object* object, const float* origin, const float*
     return hit ? 1 : 0;
 }
 
+/* the primary ray of pixel (x, y) exactly as oracle_render builds it (reference kernel.cu:244-253): near-tie
+ * analysis of hit-id differences (tests, tools/near_ties.py) */
+void oracle_primary_ray(const rtb_Camera* cam, int imgw, int imgh, int x, int y, float* origin, float* dir) {
+    const V3 LD = from(cam->LD), LU = from(cam->LU), RD = from(cam->RD), RU = from(cam->RU);
+    float partX = (float)x / (float)(imgw - 1);
+    float partY = (float)y / (float)(imgh - 1);
+    V3 vd = add(LD, scale(sub(RD, LD), partX));
+    V3 vu = add(LU, scale(sub(RU, LU), partX));
+    V3 d = normalize(sub(vu, scale(sub(vu, vd), partY)));
+    origin[0] = cam->pos.x; origin[1] = cam->pos.y; origin[2] = cam->pos.z;
+    dir[0] = d.x; dir[1] = d.y; dir[2] = d.z;
+}
+
 }  // extern "C"

@@ -7,7 +7,7 @@ Needs /root/reference (through oracle/build_ref.py -> oracle/_ref/*.so):
                        animate() run (time advancing, colour lag) -- reference scene.cpp:100-126, 444-488,
                        666-687, 758-816
   - frames.npz       : images, pre-FXAA images and primary hit ids rendered by the reference's kernel.cu
-                       text compiled for the host (oracle/_ref/libref_trace_cpu.so) at 192x108 for both
+                       text compiled for the host (oracle/_ref/libref_trace_cpu.so) at 320x180 for both
                        views x 4 times of day, FXAA on, with the package's procedural 512x256 sky maps
                        (the reference's PNG assets do not travel to the GPU box)
   - fxaa.npz         : the reference FXAA kernel text on a random-noise and a hard-edge image
@@ -30,7 +30,7 @@ import raytracing_cuda_b200 as rt  # noqa: E402
 
 TIMES = [6.0, 14.0, 18.0, 1.0, 9.3, 17.5, 21.1, 4.7, 0.0, 23.99]
 SEAS = [-4.5, 3.5]
-FRAME_W, FRAME_H = 192, 108
+FRAME_W, FRAME_H = 320, 180
 SKY_W, SKY_H = 512, 256
 
 

@@ -95,6 +95,25 @@ def oracle_check_hit(obj, origin, direction):
     return _check_hit(oracle_lib().oracle_check_hit, obj, origin, direction)
 
 
+def near_tie_report(objects, frame, ids_a, ids_b):
+    """For every pixel where two primary-hit-id buffers differ: (x, y, id_a, id_b, t_a, t_b) with the distances the
+    oracle's checkHit gives both objects along the oracle's primary ray (nan: that object is not hit at all)."""
+    lib = oracle_lib()
+    cam = Camera()
+    C.memmove(C.byref(cam), C.byref(frame.cam), C.sizeof(Camera))
+    org, d = (C.c_float * 3)(), (C.c_float * 3)()
+    rows = []
+    for y, x in np.argwhere(ids_a != ids_b):
+        lib.oracle_primary_ray(C.byref(cam), C.c_int(frame.imgw), C.c_int(frame.imgh), C.c_int(int(x)), C.c_int(int(y)),
+                               org, d)
+        ts = []
+        for i in (int(ids_a[y, x]), int(ids_b[y, x])):
+            hit, t = (False, 0.0) if i < 0 else oracle_check_hit(objects[i], tuple(org), tuple(d))[:2]
+            ts.append(t if hit else float("nan"))
+        rows.append((int(x), int(y), int(ids_a[y, x]), int(ids_b[y, x]), ts[0], ts[1]))
+    return rows
+
+
 def ref_check_hit(obj, origin, direction):
     lib = ref_lib("trace_cpu")
     lib.ref_cpu_check_hit.restype = C.c_int

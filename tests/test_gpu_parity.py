@@ -1,6 +1,5 @@
-"""GPU parity of the CUDA hot path (through the C-ABI) against the oracle, the reference goldens and --
-when oracle/_ref/libref_kernel_sm100.so travelled with the snapshot -- the reference's own kernel
-rebuilt for sm_100.
+"""GPU parity of the CUDA hot path (through the C-ABI) against the oracle and the reference goldens.  (Against the
+reference's own kernel rebuilt for sm_100: tests/test_gpu_reference_kernel.py.)
 
 Gates (BASELINE.json north_star): primary hit ids equal except near-tie pixels; 8-bit RGB within 1 LSB
 on >= 99.9 % of pixels and PSNR >= 50 dB."""
@@ -53,14 +52,12 @@ def test_gpu_vs_reference_golden_frames(view, tod):
     FR = np.load(os.path.join(ou.GOLDEN, "frames.npz"))
     r = gu.renderer()
     s = rt.Scene()
-    f = s.configure(view=view, hours=rt.TIME_PRESETS[tod], imgw=192, imgh=108, alias=True)
+    f = s.configure(view=view, hours=rt.TIME_PRESETS[tod], imgw=320, imgh=180, alias=True)
     img, ids = gu.render(r, s, f)
     key = "v%d_%s" % (view, tod)
-    # 192x108 with FXAA on: silhouette pixels are ~5 % of so small an image and the CPU golden (IEEE
-    # divides) and the GPU (the reference's fast-math shapes) pick different FXAA neighbours at a few of
-    # them (measured 0.9987-0.9999); the north_star gate proper is applied at >= 320x180 below and against
-    # the reference kernel at 1280x720
-    _gate(img, FR[key + "_out"], ids, FR[key + "_ids"].astype(np.int32), key, within=0.998)
+    # goldens: the reference's kernel.cu text compiled for the HOST (IEEE divides, libm) at 320x180; the north_star
+    # gates apply unrelaxed (the comparison with the reference's own GPU kernel is tests/test_gpu_reference_kernel.py)
+    _gate(img, FR[key + "_out"], ids, FR[key + "_ids"].astype(np.int32), key)
     f.alias = 0
     img0, _ = gu.render(r, s, f)
     _gate(img0, FR[key + "_base"], what=key + " base")
@@ -480,48 +477,3 @@ def test_reference_launch_drives_the_drop_in():
     f = s.configure(view=6, hours=14.0, imgw=w, imgh=h, alias=True)
     o = ou.oracle_render(s.objects, s.lights, f, sky)
     _gate(got, o["out"], what="reference launch() -> drop-in")
-
-
-# ---------------------------------------------------------------- the reference kernel itself
-
-def _ref_gpu():
-    lib = ou.ref_lib("kernel_sm100")
-    if lib is None:
-        pytest.skip("oracle/_ref/libref_kernel_sm100.so did not travel")
-    lib.launchKernel.argtypes = _lib.SIGNATURES["launchKernel"][1]
-    lib.launchKernel.restype = None
-    return lib
-
-
-def test_against_rebuilt_reference_kernel():
-    """Ground truth of the north_star: the reference's own kernel.cu rebuilt for sm_100 on this GPU."""
-    import torch
-    ref = _ref_gpu()
-    ref.ref_set_hit_buffer.argtypes = [C.c_void_p, C.c_int]
-    s = rt.Scene()
-    # the reference sizes its scratch image by the TEXTURE dimensions (kernel.cu:441): the sky maps must
-    # have at least as many texels as the frame has pixels, or its own kernel writes out of bounds
-    sky = rt.synthetic_sky(2048, 1024)
-    r = rt.Renderer(0)
-    r.set_sky(sky)
-    w, h = 1280, 720
-    out = torch.zeros(w * h, dtype=torch.int32, device="cuda")
-    hit = torch.full((w * h,), -2, dtype=torch.int32, device="cuda")
-    ref.ref_set_hit_buffer(hit.data_ptr(), w)
-    stats = []
-    for view in (5, 6):
-        for tod, hours in rt.TIME_PRESETS.items():
-            f = s.configure(view=view, hours=hours, imgw=w, imgh=h, alias=True)
-            _legacy_call(ref, out.data_ptr(), s, f, sky)
-            torch.cuda.synchronize()
-            ref_img = out.cpu().numpy().view(np.uint32).reshape(h, w).copy()
-            ref_ids = hit.cpu().numpy().reshape(h, w).copy()
-            img, ids = gu.render(r, s, f)
-            m = _gate(img, ref_img, ids, ref_ids, "ref kernel v%d %s" % (view, tod))
-            m["id_mismatch"] = int((ids != ref_ids).sum())
-            stats.append((view, tod, m))
-    r.close()
-    os.makedirs(os.path.join(ou.ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ou.ROOT, "gpurun_out", "parity_vs_reference_kernel.txt"), "w") as fh:
-        for view, tod, m in stats:
-            fh.write("view %d %-9s 1280x720 FXAA on: %s\n" % (view, tod, m))

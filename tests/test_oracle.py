@@ -14,7 +14,7 @@ from raytracing_cuda_b200.structs import OBJECT_DTYPE, PLANE, SPHERE, TRIANGLE
 
 FR = np.load(os.path.join(ou.GOLDEN, "frames.npz"))
 FX = np.load(os.path.join(ou.GOLDEN, "fxaa.npz"))
-W, H = 192, 108
+W, H = 320, 180
 
 
 def _obj(type_, pos=(0, 0, 0), size=(0, 0, 0), third=(0, 0, 0)):
