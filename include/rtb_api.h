@@ -133,6 +133,25 @@ int  rt_render(rt_context* ctx, const rt_frame* frame, const rt_shard* shard,
 /* Same, result copied to HOST memory (pinned or pageable); synchronous. */
 int  rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* shard,
                        unsigned int* out_host, int* hit_ids_host);
+/* Asynchronous read-back (replaces the display hand-off of reference main.cpp:141-165 for a headless consumer):
+ * device -> host copies run on a stream of the context's own, so the copy of one frame hides behind the rendering
+ * of the next ones.  slot in [0, RT_MAX_SLOTS) names one frame in flight; out_host should be page-locked
+ * (rt_host_alloc) -- a pageable target turns the copy synchronous.
+ *   rt_render_to_host_async  render into the slot's own device frame, then copy it to out_host
+ *   rt_readback_async        copy a device frame the caller rendered itself (rt_render, launchKernel on this
+ *                            context's stream) once everything enqueued so far has run; the caller keeps src_dev
+ *                            untouched until rt_wait_slot
+ *   rt_wait_slot             returns when the slot's last copy has landed in host memory */
+#define RT_MAX_SLOTS 8
+int  rt_render_to_host_async(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_host,
+                             int slot);
+int  rt_readback_async(rt_context* ctx, const unsigned int* src_dev, size_t n_pixels, unsigned int* dst_host, int slot);
+int  rt_wait_slot(rt_context* ctx, int slot);
+int  rt_host_alloc(void** out, size_t bytes);
+int  rt_host_free(void* p);
+/* the process-global context behind launchKernel (NULL before its first call): options, counters, read-back slots */
+rt_context* rt_legacy_context(void);
+
 /* The pre-FXAA image of the last rt_render (device pointer owned by ctx; for a whole frame with alias = 0 the
  * tracer writes the caller's out_dev directly and that pointer is returned). */
 int  rt_get_base_image(rt_context* ctx, unsigned int** base_dev);
@@ -273,6 +292,12 @@ void rtb_sky_synthetic(int which, int w, int h, unsigned char* out);
  * host pixels -> binary PPM / PNG.  Return 0 on success. */
 int  rtb_write_ppm(const char* path, const unsigned int* pixels, int w, int h);
 int  rtb_write_png(const char* path, const unsigned int* pixels, int w, int h);
+/* frame `index` of a sequence dump: <prefix><index, six digits>.ppm (format 0) / .png (format 1) */
+int  rtb_write_frame(const char* prefix, int index, int format, const unsigned int* pixels, int w, int h);
+/* Image input (replaces stbi_load(path, &w, &h, &n, 4), reference scene.cpp:626-632): PNG file -> RGBA8 rows, top
+ * row first.  out = NULL queries *w, *h; capacity = bytes at out (>= 4 w h).  8-bit grey / grey+alpha / RGB / RGBA /
+ * palette, non-interlaced; anything else RT_ERR_UNSUPPORTED. */
+int  rtb_read_png(const char* path, int* w, int* h, unsigned char* out, size_t capacity);
 
 #ifdef __cplusplus
 }

@@ -14,7 +14,8 @@ oracle/_ref/libref_trace_cpu.so        the reference's kernel.cu:9-403 (device f
 oracle/_ref/backgrounds/*.png          the reference's four sky maps (data, copied as they are)
 oracle/_ref/libref_kernel_sm100.so     the reference's kernel.cu rebuilt for sm_100 with the minimum
                                        patch CUDA 12.9 needs (texture references -> texture objects,
-                                       explicit float casts at kernel.cu:163) and a primary hit-id tap;
+                                       explicit float casts at kernel.cu:163), 1 MiB of slack in front of
+                                       baseImage for its out-of-bounds FXAA halo loads, and a primary hit-id tap;
                                        flags as the reference's vcxproj:66-67 (--use_fast_math)
 
 Reference sources are read where they lie and are never copied into the repo: the
@@ -209,7 +210,15 @@ def build_ref_kernel_gpu(force=False):
     a = text.index("        int mem_size = sizeof(uchar4) * w * h;")
     b = text.index('        getLastCudaError("Error texture\\n");')
     text = text[:a] + GPU_TEX_INIT + text[b:]
-    # (iv) primary hit-id tap
+    # (iv) slack in front of baseImage: the reference's FXAA halo loads run out of bounds at the image edges
+    # (operator precedence at kernel.cu:318-319: index down to -(imgw + 1)); the values only ever feed border pixels,
+    # which pass through, but with the 128 MiB allocation the real 8192x4096 maps ask for (kernel.cu:441) the address
+    # in front of it is unmapped on this driver and the load faults.  1 MiB in front keeps the reads inside.
+    old = "cudaMalloc(&baseImage, w * h * sizeof(unsigned int));"
+    assert text.count(old) == 1
+    text = text.replace(old, "{ unsigned int* raw_; cudaMalloc(&raw_, (size_t)w * h * sizeof(unsigned int) + (2u << 20)); "
+                             "cudaMemset(raw_, 0, 1u << 20); baseImage = raw_ + (1u << 18); }")
+    # (v) primary hit-id tap
     text = text.replace("bool init = false;",
                         "bool init = false;\n__constant__ int* g_hitIds;\n__constant__ int g_hitW;", 1)
     tap = ("    if (depth == 0 && g_hitIds) g_hitIds[(blockIdx.y * blockDim.y + threadIdx.y) * g_hitW + "

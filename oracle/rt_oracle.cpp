@@ -373,10 +373,10 @@ int oracle_check_hit(const rtb_Object* object, const float* origin, const float*
 
 /* the primary ray of pixel (x, y) exactly as oracle_render builds it (reference kernel.cu:244-253): near-tie
  * analysis of hit-id differences (tests, tools/near_ties.py) */
-void oracle_primary_ray(const rtb_Camera* cam, int imgw, int imgh, int x, int y, float* origin, float* dir) {
+void oracle_primary_ray(const rtb_Camera* cam, int imgw, int imgh, float x, float y, float* origin, float* dir) {
     const V3 LD = from(cam->LD), LU = from(cam->LU), RD = from(cam->RD), RU = from(cam->RU);
-    float partX = (float)x / (float)(imgw - 1);
-    float partY = (float)y / (float)(imgh - 1);
+    float partX = x / (float)(imgw - 1);       /* x, y may be fractional: sub-pixel probes around a pixel centre */
+    float partY = y / (float)(imgh - 1);
     V3 vd = add(LD, scale(sub(RD, LD), partX));
     V3 vu = add(LU, scale(sub(RU, LU), partX));
     V3 d = normalize(sub(vu, scale(sub(vu, vd), partY)));

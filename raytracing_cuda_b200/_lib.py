@@ -21,6 +21,7 @@ RT_OPT_SHADOW_BINS = 9
 RT_OPT_MIRROR_BINS = 10
 RT_OPT_LIGHT_BINS_REUSE = 11
 RT_PEER_HANDLE_BYTES = 64
+RT_MAX_SLOTS = 8
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
                  "plane_tests", "sky_lookups", "shadow_skipped")
@@ -43,6 +44,12 @@ SIGNATURES = {
     "rt_set_scene": (C.c_int, [_P, _P, C.c_int, _P, C.c_int]),
     "rt_render": (C.c_int, [_P, C.POINTER(Frame), C.POINTER(Shard), _P, _P]),
     "rt_render_to_host": (C.c_int, [_P, C.POINTER(Frame), C.POINTER(Shard), _P, _P]),
+    "rt_render_to_host_async": (C.c_int, [_P, C.POINTER(Frame), C.POINTER(Shard), _P, C.c_int]),
+    "rt_readback_async": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_int]),
+    "rt_wait_slot": (C.c_int, [_P, C.c_int]),
+    "rt_host_alloc": (C.c_int, [C.POINTER(_P), C.c_size_t]),
+    "rt_host_free": (C.c_int, [_P]),
+    "rt_legacy_context": (_P, []),
     "rt_get_base_image": (C.c_int, [_P, C.POINTER(_P)]),
     "rt_fxaa": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.POINTER(Shard)]),
     "rt_shard_tile_count": (C.c_int, [C.POINTER(Shard), C.c_int, C.c_int]),
@@ -93,6 +100,8 @@ SIGNATURES = {
     "rtb_sky_synthetic": (None, [C.c_int, C.c_int, C.c_int, _P]),
     "rtb_write_ppm": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
     "rtb_write_png": (C.c_int, [C.c_char_p, _P, C.c_int, C.c_int]),
+    "rtb_write_frame": (C.c_int, [C.c_char_p, C.c_int, C.c_int, _P, C.c_int, C.c_int]),
+    "rtb_read_png": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), _P, C.c_size_t]),
 }
 
 _lib = None

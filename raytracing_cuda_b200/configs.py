@@ -11,10 +11,8 @@ import numpy as np
 
 from .scene import POSES, TIME_PRESETS, Scene, load_sky_pngs, synthetic_sky, terrain_objects
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-# the reference's own sky maps (scene.cpp:626-632), copied next to the reference builds by oracle/build_ref.py
-REF_BACKGROUNDS = os.path.join(ROOT, "oracle", "_ref", "backgrounds")
 SKY_W, SKY_H = 8192, 4096                       # size of the reference's maps; the procedural stand-in matches it
+SKY_NAMES = ("morning", "day", "evening", "night")     # texture1..4 of reference scene.cpp:626-632
 
 CONFIG3_SEA_LEVELS = (-4.5, -2.5, -0.5, 1.5, 3.5, 5.5, 7.5, 9.5, 11.5)
 CONFIG4_CELLS = 708
@@ -29,15 +27,11 @@ def copy_frame(f):
     return g
 
 
-def have_reference_sky():
-    return all(os.path.isfile(os.path.join(REF_BACKGROUNDS, n + ".png")) for n in ("morning", "day", "evening", "night"))
-
-
-def sky_maps(prefer_reference=True):
-    """(maps uint8[4][h][w][4], label): the reference's four PNGs when they travelled with the snapshot, else the
-    procedural stand-in of the same size."""
-    if prefer_reference and have_reference_sky():
-        return load_sky_pngs(REF_BACKGROUNDS), "reference sky maps"
+def sky_maps(directory=None):
+    """(maps uint8[4][h][w][4], label): the four PNGs the reference loads (backgrounds/morning|day|evening|night.png,
+    scene.cpp:626-632) from `directory` when they are all there, else the procedural stand-in of the same size."""
+    if directory and all(os.path.isfile(os.path.join(directory, n + ".png")) for n in SKY_NAMES):
+        return load_sky_pngs(directory), "reference sky maps"
     return synthetic_sky(SKY_W, SKY_H), "synthetic"
 
 

@@ -78,6 +78,17 @@ struct RtSkyBlock {
     int users = 1;
 };
 
+/* One slot of the asynchronous read-back pipeline: a device staging frame (rt_render_to_host_async) and the two events
+ * that order tracer stream -> copy stream -> host. */
+#define RT_MAX_SLOTS 8
+struct RtSlot {
+    unsigned int* dev = nullptr;
+    size_t cap = 0;                 /* pixels */
+    cudaEvent_t ready = nullptr;    /* the frame is complete on the context's stream */
+    cudaEvent_t copied = nullptr;   /* the frame has reached host memory */
+    bool used = false;
+};
+
 struct rt_context {
     int device = 0;
     int n_sm = 148;
@@ -137,6 +148,10 @@ struct rt_context {
 
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool timing_valid = false, build_timed = false;
+
+    /* asynchronous read-back: device -> pinned host copies on a stream of their own, RT_MAX_SLOTS frames in flight */
+    cudaStream_t copy_stream = nullptr;
+    RtSlot slots[RT_MAX_SLOTS];
 };
 
 namespace {
@@ -278,6 +293,12 @@ int rt_destroy(rt_context* ctx) {
                     ctx->d_lgb_offsets[1], ctx->d_lgb_entries[0], ctx->d_lgb_entries[1]};
     for (void* p : ptrs) if (p) cudaFree(p);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    for (RtSlot& sl : ctx->slots) {
+        if (sl.dev) cudaFree(sl.dev);
+        if (sl.ready) cudaEventDestroy(sl.ready);
+        if (sl.copied) cudaEventDestroy(sl.copied);
+    }
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     delete ctx;
     return RT_OK;
 }
@@ -700,6 +721,77 @@ int rt_render_to_host(rt_context* ctx, const rt_frame* frame, const rt_shard* sh
         RT_CHECK(ctx, cudaMemcpyAsync(hit_ids_host, ctx->d_stage_ids, npx * 4, cudaMemcpyDeviceToHost, ctx->stream));
     RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return RT_OK;
+}
+
+/* ---------------------------------------------------------------- asynchronous read-back
+ * The reference hands the finished frame to the display without it ever leaving the device (mapped PBO,
+ * main.cpp:141-165).  A headless consumer wants it in host memory; so that the copy of frame i (8.3 MB at 1080p:
+ * about as long over PCIe as the frame takes to render) hides behind the rendering of frames i+1.., copies run on
+ * a stream of their own: slot k = one frame in flight.
+ *   rt_render_to_host_async(ctx, frame, shard, pinned, k)    render into the slot's staging frame, then copy
+ *   rt_readback_async(ctx, dev, n, pinned, k)                copy a frame the caller rendered itself (launchKernel)
+ *   rt_wait_slot(ctx, k)                                     the slot's frame is in host memory */
+
+static int slot_prepare(rt_context* ctx, int slot) {
+    if (slot < 0 || slot >= RT_MAX_SLOTS) return fail(ctx, RT_ERR_ARG, "slot out of range");
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->copy_stream) RT_CHECK(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    RtSlot& sl = ctx->slots[slot];
+    if (!sl.ready) RT_CHECK(ctx, cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
+    if (!sl.copied) RT_CHECK(ctx, cudaEventCreateWithFlags(&sl.copied, cudaEventDisableTiming));
+    return RT_OK;
+}
+
+int rt_readback_async(rt_context* ctx, const unsigned int* src_dev, size_t n_pixels, unsigned int* dst_host, int slot) {
+    if (!ctx || !src_dev || !dst_host || n_pixels == 0) return RT_ERR_ARG;
+    int rc = slot_prepare(ctx, slot);
+    if (rc != RT_OK) return rc;
+    RtSlot& sl = ctx->slots[slot];
+    RT_CHECK(ctx, cudaEventRecord(sl.ready, ctx->stream));
+    RT_CHECK(ctx, cudaStreamWaitEvent(ctx->copy_stream, sl.ready, 0));
+    RT_CHECK(ctx, cudaMemcpyAsync(dst_host, src_dev, n_pixels * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->copy_stream));
+    RT_CHECK(ctx, cudaEventRecord(sl.copied, ctx->copy_stream));
+    sl.used = true;
+    return RT_OK;
+}
+
+int rt_render_to_host_async(rt_context* ctx, const rt_frame* frame, const rt_shard* shard, unsigned int* out_host,
+                            int slot) {
+    if (!ctx || !frame || !out_host) return RT_ERR_ARG;
+    int rc = slot_prepare(ctx, slot);
+    if (rc != RT_OK) return rc;
+    RtSlot& sl = ctx->slots[slot];
+    const size_t npx = (size_t)frame->imgw * frame->imgh;
+    /* the staging frame is rewritten: its previous copy must have drained (device-side wait, the host runs on) */
+    if (sl.used) RT_CHECK(ctx, cudaStreamWaitEvent(ctx->stream, sl.copied, 0));
+    if (npx > sl.cap) {
+        RT_CHECK(ctx, regrow(&sl.dev, npx));
+        sl.cap = npx;
+    }
+    if (shard && shard->n_shards > 1) RT_CHECK(ctx, cudaMemsetAsync(sl.dev, 0, npx * 4, ctx->stream));
+    rc = rt_render(ctx, frame, shard, sl.dev, nullptr);
+    if (rc != RT_OK) return rc;
+    return rt_readback_async(ctx, sl.dev, npx, out_host, slot);
+}
+
+int rt_wait_slot(rt_context* ctx, int slot) {
+    if (!ctx || slot < 0 || slot >= RT_MAX_SLOTS) return RT_ERR_ARG;
+    RtSlot& sl = ctx->slots[slot];
+    if (!sl.used) return RT_OK;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaEventSynchronize(sl.copied));
+    return RT_OK;
+}
+
+/* page-locked host memory for the read-back targets (a pageable target makes cudaMemcpyAsync synchronous) */
+int rt_host_alloc(void** out, size_t bytes) {
+    if (!out || bytes == 0) return RT_ERR_ARG;
+    return cudaHostAlloc(out, bytes, cudaHostAllocDefault) == cudaSuccess ? RT_OK : RT_ERR_CUDA;
+}
+
+int rt_host_free(void* p) {
+    if (!p) return RT_OK;
+    return cudaFreeHost(p) == cudaSuccess ? RT_OK : RT_ERR_CUDA;
 }
 
 int rt_get_base_image(rt_context* ctx, unsigned int** base_dev) {

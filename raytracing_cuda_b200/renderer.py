@@ -38,9 +38,51 @@ def default_stride(n_shards):
     return s
 
 
-class Renderer:
-    def __init__(self, device=0, stream=None):
+class PinnedFrames:
+    """n page-locked host frames of n_pixels uint32 (rt_host_alloc): targets of the asynchronous read-back."""
+
+    def __init__(self, n, n_pixels):
         self._lib = _lib.load()
+        self._ptrs = []
+        self.frames = []
+        for _ in range(n):
+            p = C.c_void_p()
+            if self._lib.rt_host_alloc(C.byref(p), int(n_pixels) * 4) != _lib.RT_OK:
+                self.close()
+                raise _lib.RtError("rt_host_alloc(%d bytes) failed" % (int(n_pixels) * 4))
+            self._ptrs.append(p)
+            buf = (C.c_uint32 * int(n_pixels)).from_address(p.value)
+            self.frames.append(np.frombuffer(buf, dtype=np.uint32))
+
+    def __getitem__(self, i):
+        return self.frames[i]
+
+    def __len__(self):
+        return len(self.frames)
+
+    def close(self):
+        self.frames = []
+        for p in self._ptrs:
+            self._lib.rt_host_free(p)
+        self._ptrs = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Renderer:
+    def __init__(self, device=0, stream=None, handle=None):
+        self._lib = _lib.load()
+        if handle is not None:          # a context somebody else owns (rt_legacy_context): never destroyed here
+            self._h = C.c_void_p(handle)
+            self.device = int(device)
+            self._keep = []
+            self._borrowed = True
+            return
+        self._borrowed = False
         h = C.c_void_p()
         rc = self._lib.rt_create(int(device), C.byref(h))
         if rc != _lib.RT_OK:
@@ -54,8 +96,17 @@ class Renderer:
 
     def close(self):
         if getattr(self, "_h", None):
-            self._lib.rt_destroy(self._h)
+            if not self._borrowed:
+                self._lib.rt_destroy(self._h)
             self._h = None
+
+    @classmethod
+    def legacy(cls):
+        """The process-global context behind launchKernel (after its first call), e.g. for its read-back slots."""
+        h = _lib.load().rt_legacy_context()
+        if not h:
+            raise _lib.RtError("launchKernel has not been called yet")
+        return cls(handle=h)
 
     def __del__(self):
         try:
@@ -110,6 +161,55 @@ class Renderer:
                     "rt_render_to_host")
         img = out.reshape(frame.imgh, frame.imgw)
         return (img, ids.reshape(frame.imgh, frame.imgw)) if want_ids else img
+
+    def render_to_host_async(self, frame, out_host, slot, shard=None):
+        """Render + copy to the (page-locked) host frame `out_host` on the context's copy stream; wait_slot(slot)
+        before reading it.  Up to RT_MAX_SLOTS frames in flight."""
+        self._check(self._lib.rt_render_to_host_async(self._h, C.byref(frame),
+                                                      C.byref(shard) if shard is not None else None, _ptr(out_host),
+                                                      int(slot)), "rt_render_to_host_async")
+
+    def readback_async(self, src_dev, n_pixels, out_host, slot):
+        self._check(self._lib.rt_readback_async(self._h, _ptr(src_dev), int(n_pixels), _ptr(out_host), int(slot)),
+                    "rt_readback_async")
+
+    def wait_slot(self, slot):
+        self._check(self._lib.rt_wait_slot(self._h, int(slot)), "rt_wait_slot")
+
+    def render_sequence(self, states, prefix, fmt="png", depth=3, on_frame=None):
+        """Frame-sequence dump: states = iterable of (objects, lights, frame); frame i is written to
+        <prefix><i:06d>.<fmt> while frames i+1 .. i+depth-1 are being rendered and read back.  Returns the count."""
+        depth = max(1, min(int(depth), _lib.RT_MAX_SLOTS))
+        pinned = None
+        pending = []                                   # (index, slot, w, h)
+        n = 0
+
+        def retire():
+            i, slot, w, h = pending.pop(0)
+            self.wait_slot(slot)
+            if on_frame is not None:
+                on_frame(i, pinned[slot][:w * h].reshape(h, w))
+            rc = self._lib.rtb_write_frame(str(prefix).encode(), i, 1 if fmt == "png" else 0,
+                                           pinned[slot].ctypes.data, w, h)
+            if rc != _lib.RT_OK:
+                raise _lib.RtError("rtb_write_frame(%s, %d) failed rc=%d" % (prefix, i, rc))
+
+        for i, (objs, lights, f) in enumerate(states):
+            npx = f.imgw * f.imgh
+            if pinned is None or len(pinned[0]) < npx:
+                while pending:
+                    retire()
+                pinned = PinnedFrames(depth, npx)
+            if len(pending) == depth:
+                retire()
+            self.set_scene(objs, lights)
+            slot = i % depth
+            self.render_to_host_async(f, pinned[slot], slot)
+            pending.append((i, slot, f.imgw, f.imgh))
+            n += 1
+        while pending:
+            retire()
+        return n
 
     def base_image_ptr(self):
         p = C.c_void_p()

@@ -185,14 +185,24 @@ def synthetic_sky(w, h):
     return out
 
 
-def load_sky_pngs(directory):
-    """The reference's own sky maps (reference scene.cpp:626-632), decoded with Pillow."""
-    import os
+def read_png(path):
+    """PNG file -> uint8 [h][w][4] RGBA (csrc/image_out.cpp rtb_read_png: what stbi_load(path, ..., 4) returns in the
+    reference, scene.cpp:626-632)."""
+    lib = _lib.load()
+    w, h = C.c_int(), C.c_int()
+    p = str(path).encode()
+    rc = lib.rtb_read_png(p, C.byref(w), C.byref(h), None, 0)
+    if rc != 0:
+        raise ValueError("rtb_read_png(%s): rc=%d" % (path, rc))
+    out = np.empty((h.value, w.value, 4), dtype=np.uint8)
+    rc = lib.rtb_read_png(p, C.byref(w), C.byref(h), out.ctypes.data, out.nbytes)
+    if rc != 0:
+        raise ValueError("rtb_read_png(%s): rc=%d" % (path, rc))
+    return out
 
-    from PIL import Image
-    Image.MAX_IMAGE_PIXELS = None
-    maps = []
-    for name in ("morning", "day", "evening", "night"):
-        im = Image.open(os.path.join(directory, name + ".png")).convert("RGBA")
-        maps.append(np.asarray(im, dtype=np.uint8))
-    return np.ascontiguousarray(np.stack(maps))
+
+def load_sky_pngs(directory):
+    """The reference's own sky maps in the order of its texture1..4 (reference scene.cpp:626-632)."""
+    import os
+    return np.ascontiguousarray(np.stack([read_png(os.path.join(directory, name + ".png"))
+                                          for name in ("morning", "day", "evening", "night")]))

@@ -16,6 +16,8 @@ from raytracing_cuda_b200.structs import (CAMERA_DTYPE, LIGHT_DTYPE, OBJECT_DTYP
 ORACLE_SO = os.path.join(ROOT, "oracle", "liboracle.so")
 REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+# the reference's own sky maps (scene.cpp:626-632), copied next to the reference builds by oracle/build_ref.py
+REF_BACKGROUNDS = os.path.join(REF_DIR, "backgrounds")
 
 _cache = {}
 
@@ -95,22 +97,39 @@ def oracle_check_hit(obj, origin, direction):
     return _check_hit(oracle_lib().oracle_check_hit, obj, origin, direction)
 
 
-def near_tie_report(objects, frame, ids_a, ids_b):
-    """For every pixel where two primary-hit-id buffers differ: (x, y, id_a, id_b, t_a, t_b) with the distances the
-    oracle's checkHit gives both objects along the oracle's primary ray (nan: that object is not hit at all)."""
+def near_tie_report(objects, frame, ids_a, ids_b, radii=(1.0 / 256, 1.0 / 64, 1.0 / 16, 1.0 / 4)):
+    """For every pixel where two primary-hit-id buffers differ (a = the implementation under test, b = the CPU oracle):
+    (x, y, id_a, id_b, t_a, t_b, flip) with the distances the oracle's checkHit gives both objects along the oracle's
+    primary ray (nan: not hit), and `flip` = the smallest probe radius in pixels at which the oracle ITSELF, choosing
+    between just these two objects, picks id_a for one of the eight rays around the pixel centre (inf: never).
+    A small flip radius is what a near tie is: the pixel centre sits on the boundary between the two answers."""
     lib = oracle_lib()
+    lib.oracle_primary_ray.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p, C.c_void_p]
     cam = Camera()
     C.memmove(C.byref(cam), C.byref(frame.cam), C.sizeof(Camera))
     org, d = (C.c_float * 3)(), (C.c_float * 3)()
+
+    def winner(px, py, ia, ib):
+        lib.oracle_primary_ray(C.byref(cam), frame.imgw, frame.imgh, px, py, org, d)
+        best, best_t, ts = -1, float("inf"), []
+        for i in sorted({ia, ib}):                       # increasing index, strict '<': the reference's tie rule
+            hit, t = (False, 0.0) if i < 0 else oracle_check_hit(objects[i], tuple(org), tuple(d))[:2]
+            ts.append((i, t if hit else float("nan")))
+            if hit and t < best_t:
+                best, best_t = i, t
+        return best, dict(ts)
+
     rows = []
     for y, x in np.argwhere(ids_a != ids_b):
-        lib.oracle_primary_ray(C.byref(cam), C.c_int(frame.imgw), C.c_int(frame.imgh), C.c_int(int(x)), C.c_int(int(y)),
-                               org, d)
-        ts = []
-        for i in (int(ids_a[y, x]), int(ids_b[y, x])):
-            hit, t = (False, 0.0) if i < 0 else oracle_check_hit(objects[i], tuple(org), tuple(d))[:2]
-            ts.append(t if hit else float("nan"))
-        rows.append((int(x), int(y), int(ids_a[y, x]), int(ids_b[y, x]), ts[0], ts[1]))
+        ia, ib = int(ids_a[y, x]), int(ids_b[y, x])
+        _, ts = winner(float(x), float(y), ia, ib)
+        flip = float("inf")
+        for rad in radii:
+            probes = [(dx * rad, dy * rad) for dx in (-1, 0, 1) for dy in (-1, 0, 1) if dx or dy]
+            if any(winner(x + dx, y + dy, ia, ib)[0] == ia for dx, dy in probes):
+                flip = rad
+                break
+        rows.append((int(x), int(y), ia, ib, ts.get(ia, float("nan")), ts.get(ib, float("nan")), flip))
     return rows
 
 

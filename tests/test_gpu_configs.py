@@ -55,20 +55,18 @@ def _lattice_only(ids, sel):
     return out
 
 
-def _assert_near_ties(rows, rel=2e-4):
-    """Every differing primary hit id must be a near tie: the two objects' hit distances along that pixel's primary ray
-    agree to `rel` (relative) -- or one of them is grazed so finely that the CPU arithmetic misses it altogether."""
-    for x, y, ia, ib, ta, tb in rows:
-        if np.isnan(ta) or np.isnan(tb):
-            continue                                   # an edge-on graze: hit in one arithmetic, missed in the other
-        assert abs(ta - tb) <= rel * max(abs(ta), abs(tb), 1.0), (x, y, ia, ib, ta, tb)
+def _assert_near_ties(rows, radius=1.0 / 16):
+    """Every differing primary hit id must be a near tie: within `radius` of a pixel of the pixel centre the CPU oracle
+    itself gives the other answer (a shared edge or a silhouette crossing the centre; see ou.near_tie_report)."""
+    for row in rows:
+        assert row[-1] <= radius, row
 
 
 @pytest.mark.parametrize("view", [5, 6])
 def test_hit_id_differences_vs_cpu_oracle_are_near_ties(view):
     """GPU (the reference kernel's --use_fast_math shapes: MUFU reciprocals, fused multiply-adds) against the CPU
     oracle (IEEE divides, no FMA) at 1280x720: the handful of differing primary hit ids are listed, and each one
-    must be a tie between two primitives within 2e-4 relative distance (shared edges of the low-poly meshes).
+    must be a near tie: the oracle itself flips to the GPU's answer within 1/16 of a pixel of the pixel centre.
     Against the reference's own GPU kernel the ids agree exactly (tests/test_gpu_reference_kernel.py)."""
     r = gu.renderer()
     s = rt.Scene()
@@ -83,6 +81,7 @@ def test_hit_id_differences_vs_cpu_oracle_are_near_ties(view):
         rows_all += [(view, tod) + row for row in rows]
     os.makedirs(os.path.join(ou.ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ou.ROOT, "gpurun_out", "near_tie_pixels_view%d.txt" % view), "w") as fh:
-        fh.write("# view tod x y id_gpu id_cpu t_gpu_object t_cpu_object (CPU oracle distances along the CPU primary ray)\n")
+        fh.write("# view tod x y id_gpu id_cpu t_gpu_object t_cpu_object (CPU oracle distances along the CPU primary ray) "
+                 "flip_radius_px (the oracle gives the GPU's answer this close to the pixel centre)\n")
         for row in rows_all:
             fh.write(" ".join(str(v) for v in row) + "\n")

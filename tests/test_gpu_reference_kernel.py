@@ -39,7 +39,7 @@ class _World:
         lib.launchKernel.restype = None
         lib.ref_set_hit_buffer.argtypes = [C.c_void_p, C.c_int]
         self.ref = lib
-        self.sky, self.sky_label = configs.sky_maps()
+        self.sky, self.sky_label = configs.sky_maps(ou.REF_BACKGROUNDS)
         self.r = rt.Renderer(0)
         self.r.set_sky(self.sky)
         self.stats = []

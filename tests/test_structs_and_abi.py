@@ -75,3 +75,42 @@ def test_image_writers(product_lib, tmp_path):
     want = np.stack([img & 255, (img >> 8) & 255, (img >> 16) & 255], -1).astype(np.uint8)
     assert (np.asarray(Image.open(png).convert("RGB")) == want).all()
     assert (np.asarray(Image.open(ppm).convert("RGB")) == want).all()
+
+
+def test_png_reader_matches_pillow_and_round_trips(product_lib, tmp_path):
+    """rtb_read_png stands in for stbi_load(path, &w, &h, &n, 4) (reference scene.cpp:626-632): RGBA8 rows, top row
+    first, whatever the file holds.  Checked against Pillow on RGBA / RGB / grey / grey+alpha / palette files written
+    with adaptive row filters, against the writer of this library, and on bad input."""
+    import raytracing_cuda_b200 as rt
+    from PIL import Image
+    rng = np.random.default_rng(3)
+    yy, xx = np.mgrid[0:37, 0:53]
+    smooth = ((xx * 5 + yy * 3) & 255).astype(np.uint8)          # gradients make the encoder pick every filter type
+    for mode, arr in (("RGBA", np.stack([smooth, 255 - smooth, rng.integers(0, 256, smooth.shape, dtype=np.uint8), smooth // 2], -1)),
+                      ("RGB", np.stack([smooth, 255 - smooth, smooth // 3], -1)),
+                      ("L", smooth), ("LA", np.stack([smooth, 255 - smooth], -1)),
+                      ("P", smooth)):
+        im = Image.fromarray(arr, mode=mode)
+        if mode == "P":
+            im.putpalette([(i * 37) & 255 for i in range(256 * 3)])
+        path = str(tmp_path / ("in_%s.png" % mode))
+        im.save(path, optimize=True)
+        got = rt.read_png(path)
+        assert got.shape == (37, 53, 4)
+        assert (got == np.asarray(Image.open(path).convert("RGBA"))).all(), mode
+    img = (np.arange(48 * 32, dtype=np.uint32).reshape(32, 48) * 2654435761 & 0xFFFFFF).astype(np.uint32)
+    assert product_lib.rtb_write_frame(str(tmp_path / "seq_").encode(), 7, 1, img.ctypes.data, 48, 32) == 0
+    back = rt.read_png(str(tmp_path / "seq_000007.png"))
+    assert (back[..., 0] == (img & 255)).all() and (back[..., 2] == ((img >> 16) & 255)).all() and (back[..., 3] == 255).all()
+    assert product_lib.rtb_write_frame(str(tmp_path / "seq_").encode(), 8, 0, img.ctypes.data, 48, 32) == 0
+    assert (tmp_path / "seq_000008.ppm").exists()
+    (tmp_path / "bad.png").write_bytes(b"not a png at all, just bytes" * 4)
+    import pytest
+    with pytest.raises(ValueError):
+        rt.read_png(str(tmp_path / "bad.png"))
+    with pytest.raises(ValueError):
+        rt.read_png(str(tmp_path / "missing.png"))
+    im16 = Image.fromarray((np.arange(64, dtype=np.uint16) * 1000).reshape(8, 8))
+    im16.save(str(tmp_path / "deep.png"))
+    with pytest.raises(ValueError):
+        rt.read_png(str(tmp_path / "deep.png"))
