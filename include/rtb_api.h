@@ -102,6 +102,10 @@ enum {
     RT_CNT_RAYS_PRIMARY = 0, RT_CNT_RAYS_SHADOW = 1, RT_CNT_RAYS_MIRROR = 2,
     RT_CNT_NODE_TESTS = 3, RT_CNT_TRI_TESTS = 4, RT_CNT_SPHERE_TESTS = 5,
     RT_CNT_PLANE_TESTS = 6, RT_CNT_SKY_LOOKUPS = 7, RT_CNT_SHADOW_SKIPPED = 8,
+    /* triangle tests by exit (reference kernel.cu:100-123): u outside / v outside / through to t (hit or t < 0) /
+     * hits; the remaining RT_CNT_TRI_TESTS were culled by det < 0.001.  Sphere tests that hit (kernel.cu:49-66). */
+    RT_CNT_TRI_EXIT_U = 9, RT_CNT_TRI_EXIT_V = 10, RT_CNT_TRI_FULL = 11, RT_CNT_TRI_ACCEPT = 12,
+    RT_CNT_SPHERE_HITS = 13,
     RT_CNT_COUNT = 16
 };
 
@@ -212,6 +216,8 @@ int  rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]);
  * bins of 8 ushorts: [0] count or 0xFFFF = too many, [1..7] leaf offsets); returns the bytes copied, 0 if none,
  * -RT_ERR_* on an error */
 long long rt_debug_light_bins(rt_context* ctx, void* out, size_t bytes);
+/* kernels this library has launched in this process so far (all contexts): callers difference it around a region */
+unsigned long long rt_launch_count(void);
 /* ms of the last frame's kernels (RT_OPT_TIMING=1): [0]=trace [1]=fxaa [2]=bvh build/refit */
 int  rt_get_timings(rt_context* ctx, float out_ms[3]);
 /* FP32 FFMA throughput of the device in TFLOP/s (2 flops per FFMA), measured with a register-resident

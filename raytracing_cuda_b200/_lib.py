@@ -24,7 +24,8 @@ RT_PEER_HANDLE_BYTES = 64
 RT_MAX_SLOTS = 8
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
-                 "plane_tests", "sky_lookups", "shadow_skipped")
+                 "plane_tests", "sky_lookups", "shadow_skipped", "tri_exit_u", "tri_exit_v", "tri_full", "tri_accept",
+                 "sphere_hits")
 
 # every symbol include/rtb_api.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
@@ -71,6 +72,7 @@ SIGNATURES = {
     "rt_synchronize": (C.c_int, [_P]),
     "rt_get_counters": (C.c_int, [_P, C.POINTER(C.c_ulonglong)]),
     "rt_debug_light_bins": (C.c_longlong, [_P, C.c_void_p, C.c_size_t]),
+    "rt_launch_count": (C.c_ulonglong, []),
     "rt_get_timings": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "rt_bvh_info": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rt_bvh_download": (C.c_int, [_P, _P, _P, _P]),

@@ -89,6 +89,8 @@ struct RtSlot {
     bool used = false;
 };
 
+unsigned long long g_rt_launches = 0;      /* RT_LAUNCHED (rt_device.h) */
+
 struct rt_context {
     int device = 0;
     int n_sm = 148;
@@ -995,6 +997,8 @@ long long rt_debug_light_bins(rt_context* ctx, void* out, size_t bytes) {
     if (cudaMemcpy(out, ctx->d_lgrid, n, cudaMemcpyDeviceToHost) != cudaSuccess) return -(long long)RT_ERR_CUDA;
     return (long long)n;
 }
+
+unsigned long long rt_launch_count(void) { return __atomic_load_n(&g_rt_launches, __ATOMIC_RELAXED); }
 
 int rt_get_timings(rt_context* ctx, float out_ms[3]) {
     if (!ctx || !out_ms) return RT_ERR_ARG;

@@ -364,6 +364,7 @@ extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* val
     if (n <= 1) return cudaSuccess;
     if (n <= SS_MAX && !force_radix) {
         rs_small_sort_kernel<<<1, 1024, 0, stream>>>(keys, vals, n);
+        RT_LAUNCHED(1);
         return cudaGetLastError();
     }
     const int n_blocks = (n + RS_TILE - 1) / RS_TILE;
@@ -373,6 +374,7 @@ extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* val
         rs_hist_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, n, shift, hist, n_blocks);
         rs_scan_kernel<<<32, 256, 0, stream>>>(hist, n_blocks);
         rs_scatter_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, vi, ko, vo, n, shift, hist, n_blocks);
+        RT_LAUNCHED(3);
         unsigned int* t = ki; ki = ko; ko = t;
         t = vi; vi = vo; vo = t;
     }
@@ -836,6 +838,7 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
             cfg.stream = stream;
             cfg.attrs = pdl;
             cfg.numAttrs = 1;
+            RT_LAUNCHED(1);
             return cudaLaunchKernelEx(&cfg, rt_fused_refit_byvalue_kernel, blk, b->n_objects, (const int*)b->plane_idx,
                                       b->n_planes, b->mats, b->recs, b->planes, b->bvh_src, b->prim_lo, b->prim_hi,
                                       b->bounds, (const unsigned int*)b->vals, n, (const int2*)b->children,
@@ -846,9 +849,11 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
                                                                b->recs, b->planes, b->bvh_src, b->prim_lo, b->prim_hi,
                                                                b->bounds, b->vals, n, b->children, b->node_parent,
                                                                b->leaf_parent, b->nodes, b->prims, b->depth);
+        RT_LAUNCHED(1);
         return cudaGetLastError();
     }
     rt_bounds_init_kernel<<<1, 32, 0, stream>>>(b->bounds);
+    RT_LAUNCHED(1 + (b->n_objects > 0 ? 1 : 0));
     if (b->n_objects > 0)
         rt_setup_kernel<<<(b->n_objects + T - 1) / T, T, 0, stream>>>(b->objs, b->n_objects, b->plane_idx, b->n_planes,
                                                                       b->mats, b->recs, b->planes, b->bvh_src,
@@ -857,6 +862,7 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
     if (n <= 0) return cudaGetLastError();
     if (mode == 0) {
         rt_morton_kernel<<<(n + T - 1) / T, T, 0, stream>>>(b->prim_lo, b->prim_hi, n, b->bounds, b->keys, b->vals);
+        RT_LAUNCHED(1 + (n >= 2 ? 1 : 0));       /* Morton codes + hierarchy (PLOC or Karras) */
         cudaError_t e = rt_radix_sort_pairs(b->keys, b->vals, b->tmp_keys, b->tmp_vals, b->hist, n, force_radix, stream);
         if (e != cudaSuccess) return e;
         if (n >= 2) {
@@ -877,6 +883,7 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         cudaError_t e = cudaMemsetAsync(b->flags, 0, sizeof(unsigned int) * (size_t)(n - 1), stream);
         if (e != cudaSuccess) return e;
     }
+    RT_LAUNCHED(1);
     rt_refit_kernel<<<(n + RT_REFIT_THREADS - 1) / RT_REFIT_THREADS, RT_REFIT_THREADS, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
                                                       b->children, b->node_parent, b->leaf_parent, b->node_other, b->flags,
                                                       b->nodes, b->node_aux, b->prims, b->depth);

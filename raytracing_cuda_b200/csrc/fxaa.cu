@@ -342,6 +342,7 @@ static RtPeerSync fx_peer_arg(const RtPeerSync* peer) {
 extern "C" cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h,
                                            const rt_shard* sh, const RtPeerSync* peer, cudaStream_t stream) {
     dim3 block(FX_BW, FX_BH, 1), grid((w + FX_BW - 1) / FX_BW, (h + FX_BH - 1) / FX_BH, 1);
+    RT_LAUNCHED(1);
     if (sh && sh->n_shards > 1)
         rt_fxaa_smem_kernel<<<grid, block, 0, stream>>>(in, out, w, h, sh->tile_w, sh->tile_h, sh->n_shards,
                                                         sh->shard_id, sh->stride, fx_peer_arg(peer));
@@ -374,6 +375,7 @@ extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned
     cfg.stream = stream;
     cfg.attrs = pdl;
     cfg.numAttrs = 1;
+    RT_LAUNCHED(1);
     const cudaError_t e = cudaLaunchKernelEx(&cfg, rt_fxaa_tma_kernel, *map, in, out, w, h, n, id, st, kx, ky, fx_peer_arg(peer));
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
@@ -382,6 +384,7 @@ extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned
 extern "C" cudaError_t rt_launch_copy(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
                                       const RtPeerSync* peer, cudaStream_t stream) {
     dim3 block(32, 8, 1), grid((w + 31) / 32, (h + 7) / 8, 1);
+    RT_LAUNCHED(1);
     if (sh && sh->n_shards > 1)
         rt_copy_kernel<<<grid, block, 0, stream>>>(in, out, w, h, sh->tile_w, sh->tile_h, sh->n_shards, sh->shard_id,
                                                    sh->stride, fx_peer_arg(peer));
@@ -394,6 +397,7 @@ extern "C" cudaError_t rt_launch_present(const unsigned int* in, unsigned int* o
                                          cudaStream_t stream) {
     dim3 block(32, 8, 1), grid((w + 31) / 32, (h + 7) / 8, 1);
     rt_present_kernel<<<grid, block, 0, stream>>>(in, out, w, h, factor, mode);
+    RT_LAUNCHED(1);
     return cudaGetLastError();
 }
 
@@ -403,6 +407,7 @@ extern "C" cudaError_t rt_launch_pack_tiles(const unsigned int* frame, unsigned 
     const int per_row = (tiles_x + sh->n_shards - 1) / sh->n_shards;
     int chunks = (sh->tile_w * sh->tile_h + 2047) / 2048;
     if (chunks > 64) chunks = 64;
+    RT_LAUNCHED(1);
     rt_pack_tiles_kernel<<<dim3(per_row * tiles_y, chunks, 1), 256, 0, stream>>>(frame, packed, w, h, sh->tile_w, sh->tile_h,
                                                                 sh->n_shards, sh->shard_id, sh->stride, unpack);
     return cudaGetLastError();

@@ -162,6 +162,7 @@ extern "C" cudaError_t rt_lgb_count(const RtSceneDev* sc, const float* light_pos
     rt_lgb_sums_kernel<<<n_sums, LGB_SCAN_THREADS, 0, stream>>>(counts, bins, sums);
     rt_lgb_scan_sums_kernel<<<1, 1024, 0, stream>>>(sums, n_sums);
     rt_lgb_offsets_kernel<<<n_sums, LGB_SCAN_THREADS, 0, stream>>>(counts, bins, sums, n_sums, offsets);
+    RT_LAUNCHED(4);
     return cudaGetLastError();
 }
 
@@ -172,6 +173,7 @@ extern "C" cudaError_t rt_lgb_fill(const RtSceneDev* sc, const float* light_pos,
     cudaError_t e = cudaMemsetAsync(counts, 0, sizeof(unsigned int) * rt_lgb_bins(), stream);
     if (e != cudaSuccess) return e;
     const int n = sc->n_bvh_prims;
+    RT_LAUNCHED(1);
     rt_lgb_bin_kernel<1><<<(n + 255) / 256, 256, 0, stream>>>(*sc, light_pos[0], light_pos[1], light_pos[2], counts,
                                                             offsets, entries, cap, fail);
     return cudaGetLastError();

@@ -5,6 +5,8 @@
  */
 #include <cuda_runtime.h>
 
+#include "rt_device.h"
+
 #define PK_ITERS 4096
 #define PK_CHAINS 8
 
@@ -34,6 +36,7 @@ extern "C" cudaError_t rt_launch_ffma_peak(int n_sm, cudaStream_t stream, float*
     for (int rep = 0; rep < 5; rep++) {
         cudaEventRecord(a, stream);
         rt_ffma_peak_kernel<<<grid, block, 0, stream>>>(d, 0.999f, 0.001f);
+        RT_LAUNCHED(1);
         cudaEventRecord(b, stream);
         cudaEventSynchronize(b);
         float t = 0.f;

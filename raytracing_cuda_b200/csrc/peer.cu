@@ -52,23 +52,28 @@ __global__ void rt_peer_reset_error_kernel(unsigned int* flags) { rt_peer_store(
 
 extern "C" cudaError_t rt_launch_peer_signal(unsigned int* flags, int rank, unsigned int seq, cudaStream_t stream) {
     rt_peer_signal_kernel<<<1, 1, 0, stream>>>(flags, rank, seq);
+    RT_LAUNCHED(1);
     return cudaGetLastError();
 }
 extern "C" cudaError_t rt_launch_peer_wait(unsigned int* flags, int n_ranks, unsigned int seq, unsigned int timeout_ms,
                                            cudaStream_t stream) {
     rt_peer_wait_kernel<<<1, 32, 0, stream>>>(flags, n_ranks, seq, timeout_ms);
+    RT_LAUNCHED(1);
     return cudaGetLastError();
 }
 extern "C" cudaError_t rt_launch_peer_release(unsigned int* flags, unsigned int seq, cudaStream_t stream) {
     rt_peer_release_kernel<<<1, 1, 0, stream>>>(flags, seq);
+    RT_LAUNCHED(1);
     return cudaGetLastError();
 }
 extern "C" cudaError_t rt_launch_peer_acquire(unsigned int* flags, unsigned int seq, unsigned int timeout_ms,
                                               cudaStream_t stream) {
     rt_peer_acquire_kernel<<<1, 1, 0, stream>>>(flags, seq, timeout_ms);
+    RT_LAUNCHED(1);
     return cudaGetLastError();
 }
 extern "C" cudaError_t rt_launch_peer_reset_error(unsigned int* flags, cudaStream_t stream) {
     rt_peer_reset_error_kernel<<<1, 1, 0, stream>>>(flags);
+    RT_LAUNCHED(1);
     return cudaGetLastError();
 }

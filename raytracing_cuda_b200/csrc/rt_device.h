@@ -78,6 +78,10 @@ struct RtPeerSync {
 #define RT_SMALL_DYN_SMEM_MAX (24 * 1024)
 #endif
 
+/* kernels this library has launched in this process (rt_launch_count, api.cu): every launcher adds what it enqueued */
+extern "C" unsigned long long g_rt_launches;
+#define RT_LAUNCHED(n) ((void)__atomic_fetch_add(&g_rt_launches, (unsigned long long)(n), __ATOMIC_RELAXED))
+
 struct RtSceneDev {
     const float4* nodes;
     const float4* prims;

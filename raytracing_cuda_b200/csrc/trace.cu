@@ -108,7 +108,7 @@ rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restric
     if (x >= f.imgw || y >= f.imgh) return;
     if (!rt_shard_needs(f, x, y)) return;
 
-    RtPixelCounters pc = {{0, 0, 0, 0}, 0, 0, 0, 0};
+    RtPixelCounters pc = {{0, 0, 0, 0, 0, 0, 0, 0, 0}, 0, 0, 0, 0};
     RtGlobalScene<BRUTE, COUNT> acc(sc);
 #ifdef RT_TIMEMAP
     unsigned long long tm_t0;
@@ -134,6 +134,7 @@ extern "C" cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f
                                        cudaStream_t stream) {
     dim3 block(RT_TRACE_THREADS, 1, 1);
     dim3 grid((f->imgw + 31) / 32, (f->imgh + 7) / 8, 1);
+    RT_LAUNCHED(1);
     if (brute) {
         if (count) rt_trace_kernel<true, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters);
         else       rt_trace_kernel<true, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters);

@@ -22,7 +22,30 @@ struct RtHit {
 
 struct RtLocalCounters {
     unsigned int node_tests, tri_tests, sphere_tests, plane_tests;
+    /* triangle tests by how far they got (rt_hit_triangle_tier; the rest of tri_tests was culled by det < 0.001) and
+     * sphere tests that hit: the flop model of SURVEY 8d charges a test by its exit */
+    unsigned int tri_exit_u, tri_exit_v, tri_full, tri_accept, sphere_hits;
 };
+
+/* instrumented leaf tests: the same arithmetic, plus the counts */
+__device__ __forceinline__ bool rt_count_triangle(const vec3& o, const vec3& d, const vec3& v0, const vec3& e1,
+                                                  const vec3& e2, float& t, RtLocalCounters& cnt) {
+    int tier;
+    const bool hit = rt_hit_triangle_tier(o, d, v0, e1, e2, t, tier);
+    cnt.tri_tests++;
+    cnt.tri_exit_u += tier == 1;
+    cnt.tri_exit_v += tier == 2;
+    cnt.tri_full += tier >= 3;
+    cnt.tri_accept += tier == 4;
+    return hit;
+}
+__device__ __forceinline__ bool rt_count_sphere(const vec3& o, const vec3& d, const vec3& c, float r2, float& t,
+                                                RtLocalCounters& cnt) {
+    const bool hit = rt_hit_sphere(o, d, c, r2, t);
+    cnt.sphere_tests++;
+    cnt.sphere_hits += hit;
+    return hit;
+}
 
 #define RT_MISS 0xFFFFFFFFu
 
@@ -45,7 +68,7 @@ __device__ __forceinline__ bool rt_test_record(const float4* __restrict__ rec, c
     const float4 q1 = __ldg(rec + 1);
     tag = __float_as_uint(q0.w);
     if (tag & RT_TAG_SPHERE) {
-        if (COUNT) cnt.sphere_tests++;
+        if (COUNT) return rt_count_sphere(o, d, f4xyz(q0), q1.y, t, cnt);
         return rt_hit_sphere(o, d, f4xyz(q0), q1.y, t);
     }
     if (tag & RT_TAG_PLANE) {
@@ -53,7 +76,7 @@ __device__ __forceinline__ bool rt_test_record(const float4* __restrict__ rec, c
         return rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t);
     }
     const float4 q2 = __ldg(rec + 2);
-    if (COUNT) cnt.tri_tests++;
+    if (COUNT) return rt_count_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t, cnt);
     return rt_hit_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t);
 }
 

@@ -121,10 +121,11 @@ __device__ __forceinline__ void rt_flush_counters(const RtPixelCounters& pc, uns
                                                   RtCountersDev* __restrict__ counters) {
     const unsigned int mask = __activemask();
     const bool leader = (threadIdx.x & 31) == (unsigned int)(__ffs(mask) - 1);
-    const unsigned int vals[9] = {n_pixels, pc.n_shadow, pc.n_mirror, pc.t.node_tests, pc.t.tri_tests,
-                                  pc.t.sphere_tests, pc.t.plane_tests, pc.n_sky, pc.n_shadow_skipped};
+    const unsigned int vals[14] = {n_pixels, pc.n_shadow, pc.n_mirror, pc.t.node_tests, pc.t.tri_tests,
+                                   pc.t.sphere_tests, pc.t.plane_tests, pc.n_sky, pc.n_shadow_skipped,
+                                   pc.t.tri_exit_u, pc.t.tri_exit_v, pc.t.tri_full, pc.t.tri_accept, pc.t.sphere_hits};
 #pragma unroll
-    for (int k = 0; k < 9; k++) {
+    for (int k = 0; k < 14; k++) {
         const unsigned int s = __reduce_add_sync(mask, vals[k]);
         if (leader) atomicAdd(&counters->v[k], (unsigned long long)s);
     }

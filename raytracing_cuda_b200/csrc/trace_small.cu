@@ -79,11 +79,11 @@ __device__ __forceinline__ bool rs_test_record(unsigned int rec, const vec3& o, 
     const float4 q1 = rs_lds128(rec + 16);
     tag = __float_as_uint(q0.w);
     if (tag & RT_TAG_SPHERE) {
-        if (count) cnt.sphere_tests++;
+        if (count) return rt_count_sphere(o, d, f4xyz(q0), q1.y, t, cnt);
         return rt_hit_sphere(o, d, f4xyz(q0), q1.y, t);
     }
     const float4 q2 = rs_lds128(rec + 32);
-    if (count) cnt.tri_tests++;
+    if (count) return rt_count_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t, cnt);
     return rt_hit_triangle(o, d, f4xyz(q0), f4xyz(q1), f4xyz(q2), t);
 }
 
@@ -693,7 +693,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     sh.root = n > 1 ? 0 : ~prims_off;
     RtSmallScene<COUNT> acc(sh);
 
-    RtPixelCounters pc = {{0, 0, 0, 0}, 0, 0, 0, 0};
+    RtPixelCounters pc = {{0, 0, 0, 0, 0, 0, 0, 0, 0}, 0, 0, 0, 0};
     unsigned int n_pixels = 0;
 
     u0 = __shfl_sync(0xffffffffu, u0, 0);
@@ -860,6 +860,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.gridDim = dim3(cull_blocks + (lgrid && build_lgrid ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
     cfg.blockDim = dim3(256, 1, 1);
     cfg.dynamicSmemBytes = 0;
+    RT_LAUNCHED(2);                              /* pre-pass + tracer */
     cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins,
                                        sharded ? work_list : (unsigned int*)nullptr, tile_counter + RS_CNT_TILES, tiles_x,
                                        tiles_y, after_own_post ? 0 : 1, lgrid, cull_blocks, mirror_lists);

@@ -169,7 +169,7 @@ def sharded_frame(r, f, w, h, out_local, packed, frame0, bufs, shard):
         seq = _peer["seq"]
         pf.render(f, shard, seq)
         if rank == 0:
-            pf.wait(seq)
+            pf.wait(seq, check=False)
             _peer["last"] = seq
             pf.release(seq)          # (a consumer would use pf.tensor(seq) between wait and release)
         return
@@ -194,7 +194,7 @@ def composite_ok(r, f, w, h, out_local, packed, frame0, bufs, shard, full):
         pf.render(f, shard, seq)
         ok = True
         if rank == 0:
-            pf.wait(seq)
+            pf.wait(seq, check=False)
             torch.cuda.synchronize()
             ok = bool(torch.equal(pf.tensor(seq), full)) and pf.error() == 0
             pf.release(seq)
