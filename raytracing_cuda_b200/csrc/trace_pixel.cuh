@@ -13,6 +13,8 @@
  *     bool   occluded(o, d, tmax, cnt)      any non-emissive hit with t < tmax (kernel.cu:188-193)
  *     vec3   normal(hit, P)                 surface normal at the hit (kernel.cu:66, 87, 123)
  *     void   material(idx, m0, m1)          (color.rgb, mirror) (shine, specular, emissive, type)
+ *     bool   defers(depth, off_plane0)      rt_trace_chain<DEFER>: hand this ray to a compacted batch instead of
+ *                                           tracing it here (only accessors used with DEFER need it)
  *
  * Exact work-saving shortcuts (bit-identical results):
  *   - a shadow ray is traced only if N.L > 0: the reference's shadow loop can
@@ -31,16 +33,28 @@ struct RtPixelCounters {
     unsigned int n_shadow, n_mirror, n_sky, n_shadow_skipped;
 };
 
-/* s_pending: [RTB_MAX_DEPTH][blockDim.x] float4, this thread's column is s_pending[depth * stride + tid] */
-template <class ACC, bool COUNT>
-__device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDev& f, int x, int y,
-                                                       float4* __restrict__ s_pending, int stride, int tid,
-                                                       int* __restrict__ hit_ids, RtPixelCounters& pc) {
-    vec3 o = v3(f.pos[0], f.pos[1], f.pos[2]);
-    vec3 d = rt_primary_dir(f, x, y);
+/* A ray of a pixel's chain: generation `depth` (0 = primary), and whether it is the bounce of a PRIMARY ray off
+ * plane 0 (the sea: mirror bins).  Together with the s_pending entries below `depth` this is everything a pixel's
+ * continuation needs, which is what lets a ray move to another thread (ray compaction, trace_small.cu). */
+struct RtRay {
+    vec3 o, d;
+    int depth;
+    bool off_plane0;
+};
+
+/* Runs a pixel's chain of rays from `ray` on.  Returns true when the pixel is finished (`rgba` holds the packed
+ * colour, the recursion unwound through s_pending, reference kernel.cu:218).  With DEFER, returns false as soon
+ * as the NEXT ray of the chain is one the accessor wants to hand to a compacted batch (acc.defers: it would
+ * traverse the hierarchy): `ray` then describes that ray and s_pending[0 .. ray.depth) the colours waiting for it.
+ * s_pending: [RTB_MAX_DEPTH][blockDim.x] float4, this thread's column is s_pending[depth * stride + tid]. */
+template <class ACC, bool COUNT, bool DEFER>
+__device__ __forceinline__ bool rt_trace_chain(ACC& acc, const RtFrameDev& f, int x, int y, RtRay& ray,
+                                               float4* __restrict__ s_pending, int stride, int tid,
+                                               int* __restrict__ hit_ids, RtPixelCounters& pc, unsigned int& rgba) {
+    vec3 o = ray.o, d = ray.d;
     vec3 c = v3(0, 0, 0);
-    int depth = 0;
-    bool off_plane0 = false;
+    int depth = ray.depth;
+    bool off_plane0 = ray.off_plane0;
 
     for (;;) {
         const RtHit h = acc.closest(o, d, depth, off_plane0, pc.t);
@@ -101,6 +115,15 @@ __device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDe
             off_plane0 = depth == 0 && h.slot == ~0;
             depth++;
             if (COUNT) pc.n_mirror++;
+            if constexpr (DEFER) {
+                if (acc.defers(depth, off_plane0)) {
+                    ray.o = o;
+                    ray.d = d;
+                    ray.depth = depth;
+                    ray.off_plane0 = off_plane0;
+                    return false;
+                }
+            }
             continue;
         }
         /* no bounce (kR <= 0), or trace<5> returned black (kernel.cu:222-225): refColor = 0 */
@@ -113,7 +136,23 @@ __device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDe
         c = vadd(vscale(c, pk.w), vscale(v3(pk.x, pk.y, pk.z), 1 - pk.w));
     }
     c = vscale(c, 255.0f);
-    return rt_pack(c.x, c.y, c.z);
+    rgba = rt_pack(c.x, c.y, c.z);
+    return true;
+}
+
+/* the whole pixel on one thread: primary ray of pixel (x, y), then its chain to the end */
+template <class ACC, bool COUNT>
+__device__ __forceinline__ unsigned int rt_trace_pixel(ACC& acc, const RtFrameDev& f, int x, int y,
+                                                       float4* __restrict__ s_pending, int stride, int tid,
+                                                       int* __restrict__ hit_ids, RtPixelCounters& pc) {
+    RtRay ray;
+    ray.o = v3(f.pos[0], f.pos[1], f.pos[2]);
+    ray.d = rt_primary_dir(f, x, y);
+    ray.depth = 0;
+    ray.off_plane0 = false;
+    unsigned int rgba = 0;
+    rt_trace_chain<ACC, COUNT, false>(acc, f, x, y, ray, s_pending, stride, tid, hit_ids, pc, rgba);
+    return rgba;
 }
 
 /* one atomic per warp and counter, not per thread */

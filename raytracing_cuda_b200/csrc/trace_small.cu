@@ -19,7 +19,13 @@
  *     ends on cheap sky patches; no CTA barrier in the loop.  Every pixel tests just its bin's list for its primary ray;
  *   - shadow and mirror rays traverse the shared-memory LBVH with a per-thread stack of
  *     16-bit entries in shared memory (no local memory, sentinel at the bottom), child links
- *     pre-scaled to byte offsets so that a node fetch is one add + four LDS.128.
+ *     pre-scaled to byte offsets so that a node fetch is one add + four LDS.128;
+ *   - ray compaction: a ray of the second or a later generation that has to TRAVERSE the hierarchy (no
+ *     candidate list covers it) is not traced by the lane that spawned it.  The lane parks the ray -- origin,
+ *     direction, pixel, generation and the colours waiting for it -- in a queue in the CTA's shared memory
+ *     (ballot + popc slot assignment) and its warp goes on to the next patch; any warp of the CTA that finds 32
+ *     rays waiting pops them and runs one generation of all of them as a FULL warp (traversal, shading, shadow
+ *     rays; what bounces again is parked again).  Per-ray arithmetic is untouched, so pixels do not change.
  *
  * Conservative culling: the tile is grown by one pixel on every side and each plane test
  * gets a world-space pad (2^-13 of the largest coordinate in play), both orders of
@@ -47,6 +53,7 @@
  * node or leaf fetch is one add + LDS.128s with immediate offsets.  Node and leaf links are byte offsets from
  * the start of the staged scene (`base`): node i -> 64 i, leaf slot j -> ~(64 n_nodes + 48 j). */
 struct RtSmallShared {
+    bool defer;              /* rays that would traverse the hierarchy are handed to a compacted batch (rt_trace_chain) */
     unsigned int base;       /* shared address of the staged nodes (leaf records follow them) */
     unsigned int stack0;     /* shared address of this thread's stack column */
     const unsigned short* list;   /* primary candidates of the current tile: [0] count, then leaf byte offsets */
@@ -234,6 +241,10 @@ struct RtSmallScene {
             }
         }
         return false;
+    }
+    /* rt_trace_chain<DEFER>: a ray of generation >= 1 that no candidate list covers (it would traverse) */
+    __device__ __forceinline__ bool defers(int depth, bool off_plane0) const {
+        return s.defer && depth >= 1 && !(off_plane0 && s.mlist && s.mlist[0] != 0xFFFF);
     }
     __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) {
         if (h.slot < 0) return f4xyz(rs_lds128(s.base - RS_PLANES_BYTES + 32 * (~h.slot) + 16));
@@ -598,9 +609,86 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
     rs_griddep_wait();
 }
 
+/* ---------------------------------------------------------------- ray queue (compaction)
+ * RS_Q_CAP parked rays per CTA, structure of arrays of float4: [0] (o.xyz, pixel index) [1] (d.xyz, generation)
+ * [2..5] the colours (phong.rgb, kR) of generations 0..3 waiting for the ray's result (s_pending of the lane that
+ * parked it).  A stack under a CTA-wide spin lock taken by whole warps: pushes and pops are a few shared-memory
+ * accesses per lane, so the lock is held for a few hundred cycles at most.  qctl[0] = lock, qctl[1] = count. */
+#define RS_Q_CAP 64
+#define RS_Q_FIELDS (2 + RTB_MAX_DEPTH)
+
+__device__ __forceinline__ void rs_q_lock(unsigned int* qctl, int lane) {
+    if (lane == 0)
+        while (atomicCAS(qctl, 0u, 1u) != 0u) __nanosleep(32);
+    __syncwarp();
+    __threadfence_block();
+}
+__device__ __forceinline__ void rs_q_unlock(unsigned int* qctl, int lane) {
+    __threadfence_block();
+    __syncwarp();
+    if (lane == 0) atomicExch(qctl, 0u);
+}
+
+/* All 32 lanes call.  Lanes with `parked` offer their ray; as many as fit are stored (lowest lanes first).  Returns
+ * whether THIS lane's ray was stored; a lane that offered and got false keeps its ray. */
+__device__ __forceinline__ bool rs_q_push(float4* __restrict__ q, unsigned int* qctl, int lane, bool parked,
+                                          const RtRay& ray, int pixel, const float4* __restrict__ s_pending, int tid) {
+    const unsigned int m = __ballot_sync(0xffffffffu, parked);
+    if (m == 0u) return false;
+    const int rank = __popc(m & ((1u << lane) - 1u));
+    rs_q_lock(qctl, lane);
+    int base = 0, take = 0;
+    if (lane == 0) {
+        const int cnt = (int)((volatile unsigned int*)qctl)[1];
+        take = min(__popc(m), RS_Q_CAP - cnt);
+        base = cnt;
+        ((volatile unsigned int*)qctl)[1] = (unsigned int)(cnt + take);
+    }
+    base = __shfl_sync(0xffffffffu, base, 0);
+    take = __shfl_sync(0xffffffffu, take, 0);
+    const bool stored = parked && rank < take;
+    if (stored) {
+        const int slot = base + rank;
+        q[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __int_as_float(pixel));
+        q[RS_Q_CAP + slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __int_as_float(ray.depth));
+        for (int dd = 0; dd < ray.depth; dd++) q[(2 + dd) * RS_Q_CAP + slot] = s_pending[dd * RT_SMALL_THREADS + tid];
+    }
+    rs_q_unlock(qctl, lane);
+    return stored;
+}
+
+/* All 32 lanes call.  Up to 32 parked rays leave the queue, one per lane from lane 0 up; returns whether this lane
+ * got one (its waiting colours are then in this thread's s_pending column). */
+__device__ __forceinline__ bool rs_q_pop(const float4* __restrict__ q, unsigned int* qctl, int lane, RtRay& ray,
+                                         int& pixel, float4* __restrict__ s_pending, int tid) {
+    rs_q_lock(qctl, lane);
+    int base = 0, n = 0;
+    if (lane == 0) {
+        const int cnt = (int)((volatile unsigned int*)qctl)[1];
+        n = min(32, cnt);
+        base = cnt - n;
+        ((volatile unsigned int*)qctl)[1] = (unsigned int)base;
+    }
+    base = __shfl_sync(0xffffffffu, base, 0);
+    n = __shfl_sync(0xffffffffu, n, 0);
+    const bool have = lane < n;
+    if (have) {
+        const int slot = base + lane;
+        const float4 a = q[slot], b = q[RS_Q_CAP + slot];
+        ray.o = v3(a.x, a.y, a.z);
+        ray.d = v3(b.x, b.y, b.z);
+        ray.depth = __float_as_int(b.w);
+        ray.off_plane0 = false;          /* the candidate lists of the warp that parked it are not ours: traverse */
+        pixel = __float_as_int(a.w);
+        for (int dd = 0; dd < ray.depth; dd++) s_pending[dd * RT_SMALL_THREADS + tid] = q[(2 + dd) * RS_Q_CAP + slot];
+    }
+    rs_q_unlock(qctl, lane);
+    return have;
+}
+
 /* ---------------------------------------------------------------- tracer */
 
-template <bool COUNT>
+template <bool COUNT, bool COMPACT>
 __global__ void __launch_bounds__(RT_SMALL_THREADS, RT_SMALL_CTAS_PER_SM)
 rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
                       int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters,
@@ -613,6 +701,8 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
     __shared__ unsigned short s_list[RT_SMALL_WARPS][2 * RT_SMALL_LIST];   /* per-warp primary + mirror candidates */
+    __shared__ __align__(16) float4 s_queue[COMPACT ? RS_Q_FIELDS * RS_Q_CAP : 1];   /* parked rays (ray compaction) */
+    __shared__ unsigned int s_qctl[2];
     extern __shared__ __align__(16) unsigned char smem[];
 
     const int tid = threadIdx.x;
@@ -628,6 +718,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
 
     unsigned int u0 = 0;
     if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
+    if (COMPACT && tid < 2) s_qctl[tid] = 0u;
 
     /* stage the scene: links become byte offsets from the start of the nodes */
     for (int i = tid; i < 4 * n_nodes; i += RT_SMALL_THREADS) {
@@ -683,6 +774,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.base) : "r"(b0));
         asm volatile("mov.u32 %0, %1;" : "=r"(sh.stack0) : "r"(s0));
     }
+    sh.defer = false;
     sh.deep = force_linear || __ldg(sc.depth) > RT_SMALL_STACK;
     sh.list = s_list[warp];
     sh.mlist = mirror_lists ? s_list[warp] + RT_SMALL_LIST : nullptr;
@@ -701,65 +793,176 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     unsigned long long tl_t0, tl_t1 = 0, tl_units = 0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t0));
 #endif
-    while (u0 < n_fetch) {
-        unsigned int q = 0;                       /* patch id = 4 * tile + patch */
-        if (by_cost) {
-            const int j = __popc(__ballot_sync(0xffffffffu, lane < RS_CLASSES && u0 >= cls_end));
-            const unsigned int start = __shfl_sync(0xffffffffu, cls_end, (j + 31) & 31);   /* end of the class before */
-            const unsigned int idx = u0 - (j ? start : 0u);
-            q = __ldcg(order_r + RS_ORDER_HEAD + (size_t)(RS_CLASSES - 1 - j) * n_fetch + idx);
+    if constexpr (!COMPACT) {
+        /* every lane follows its own pixel's chain of rays to the end (the default: see RT_OPT_COMPACTION) */
+        while (u0 < n_fetch) {
+            unsigned int q = 0;                       /* patch id = 4 * tile + patch */
+            if (by_cost) {
+                const int j = __popc(__ballot_sync(0xffffffffu, lane < RS_CLASSES && u0 >= cls_end));
+                const unsigned int start = __shfl_sync(0xffffffffu, cls_end, (j + 31) & 31);   /* end of the class before */
+                const unsigned int idx = u0 - (j ? start : 0u);
+                q = __ldcg(order_r + RS_ORDER_HEAD + (size_t)(RS_CLASSES - 1 - j) * n_fetch + idx);
+            }
+            else {
+                const unsigned int slot = n_tiles - 1u - u0 / RT_SMALL_PATCHES;
+                q = RT_SMALL_PATCHES * (listed ? __ldg(work_list + slot) : slot) + (RT_SMALL_PATCHES - 1u - u0 % RT_SMALL_PATCHES);
+            }
+            const unsigned int tile = q / RT_SMALL_PATCHES;
+            const int p = (int)(q % RT_SMALL_PATCHES);
+            const unsigned int unit_t0 = (unsigned int)clock();
+            const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
+            const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
+            const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
+            const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
+            s_list[warp][lane] = entry;
+            if (mirror_lists) s_list[warp][RT_SMALL_LIST + lane] = __ldg(mirror_lists + (size_t)bin * RT_SMALL_LIST + lane);
+            __syncwarp();
+            {
+                const int x = x0 + (p % (RT_SMALL_TILE_W / 8)) * 8 + (lane & 7);
+                const int y = y0 + (p / (RT_SMALL_TILE_W / 8)) * 4 + (lane >> 3);
+    #ifdef RS_COSTMAP
+                unsigned long long cm_t0;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cm_t0));
+    #endif
+                if (x < f.imgw && y < f.imgh && rt_shard_needs(f, x, y)) {
+                    image[y * f.imgw + x] = rt_trace_pixel<RtSmallScene<COUNT>, COUNT>(acc, f, x, y, s_pending,
+                                                                                      RT_SMALL_THREADS, tid, hit_ids, pc);
+                    n_pixels++;
+                }
+    #ifdef RS_COSTMAP
+                __syncwarp();   /* debug variant: ns spent on the patch, stored over the hit id of its first pixel */
+                if (lane == 0 && hit_ids && x < f.imgw && y < f.imgh) {
+                    unsigned long long cm_t1;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cm_t1));
+                    hit_ids[y * f.imgw + x] = (int)(cm_t1 - cm_t0);
+                }
+    #endif
+            }
+            __syncwarp();                            /* the list is rewritten for the next unit */
+    #ifdef RS_TIMELINE
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
+            tl_units++;
+    #endif
+            unsigned int u1 = 0;
+            if (lane == 0) {
+                u1 = atomicAdd(tile_counter, 1u);
+                if (order_w) {                       /* file the patch under its cost class for the next frame */
+                    const unsigned int k = ((unsigned int)clock() - unit_t0) >> 10;
+                    const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
+                    const unsigned int at = atomicAdd(order_w + cls, 1u);
+                    order_w[RS_ORDER_HEAD + (size_t)cls * n_fetch + at] = q;
+                }
+            }
+            u0 = __shfl_sync(0xffffffffu, u1, 0);
         }
-        else {
-            const unsigned int slot = n_tiles - 1u - u0 / RT_SMALL_PATCHES;
-            q = RT_SMALL_PATCHES * (listed ? __ldg(work_list + slot) : slot) + (RT_SMALL_PATCHES - 1u - u0 % RT_SMALL_PATCHES);
-        }
-        const unsigned int tile = q / RT_SMALL_PATCHES;
-        const int p = (int)(q % RT_SMALL_PATCHES);
-        const unsigned int unit_t0 = (unsigned int)clock();
-        const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
-        const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
-        const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
-        const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
-        s_list[warp][lane] = entry;
-        if (mirror_lists) s_list[warp][RT_SMALL_LIST + lane] = __ldg(mirror_lists + (size_t)bin * RT_SMALL_LIST + lane);
-        __syncwarp();
-        {
-            const int x = x0 + (p % (RT_SMALL_TILE_W / 8)) * 8 + (lane & 7);
-            const int y = y0 + (p / (RT_SMALL_TILE_W / 8)) * 4 + (lane >> 3);
-#ifdef RS_COSTMAP
+    } else {
+        /* Every turn of the loop runs ONE batch of up to 32 rays on this warp: the primary rays of the next 8x4 patch, or
+         * -- first, whenever a full warp's worth is waiting (and at the end whatever is left) -- 32 parked rays of the
+         * CTA's queue.  Either way a lane follows its ray's chain until the pixel is finished or its next ray is one to
+         * park; rays the queue has no room for are simply finished by the lane that holds them. */
+        for (;;) {
+            bool from_queue = false;
+            {
+                unsigned int waiting = 0;
+                if (lane == 0) waiting = ((volatile unsigned int*)s_qctl)[1];
+                waiting = __shfl_sync(0xffffffffu, waiting, 0);
+                from_queue = waiting >= 32u || (u0 >= n_fetch && waiting > 0u);
+            }
+            if (!from_queue && u0 >= n_fetch) break;
+
+            RtRay ray;
+            int pixel = 0;
+            bool live = false;                        /* this lane holds a ray */
+            unsigned int q = 0;                       /* patch id = 4 * tile + patch */
+            unsigned int unit_t0 = 0;
+            if (from_queue) {
+                live = rs_q_pop(s_queue, s_qctl, lane, ray, pixel, s_pending, tid);
+            } else {
+                if (by_cost) {
+                    const int j = __popc(__ballot_sync(0xffffffffu, lane < RS_CLASSES && u0 >= cls_end));
+                    const unsigned int start = __shfl_sync(0xffffffffu, cls_end, (j + 31) & 31);   /* end of the class before */
+                    const unsigned int idx = u0 - (j ? start : 0u);
+                    q = __ldcg(order_r + RS_ORDER_HEAD + (size_t)(RS_CLASSES - 1 - j) * n_fetch + idx);
+                }
+                else {
+                    const unsigned int slot = n_tiles - 1u - u0 / RT_SMALL_PATCHES;
+                    q = RT_SMALL_PATCHES * (listed ? __ldg(work_list + slot) : slot) + (RT_SMALL_PATCHES - 1u - u0 % RT_SMALL_PATCHES);
+                }
+                const unsigned int tile = q / RT_SMALL_PATCHES;
+                const int p = (int)(q % RT_SMALL_PATCHES);
+                unit_t0 = (unsigned int)clock();
+                const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
+                const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
+                const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
+                const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
+                __syncwarp();                        /* nobody still reads the previous patch's lists */
+                s_list[warp][lane] = entry;
+                if (mirror_lists) s_list[warp][RT_SMALL_LIST + lane] = __ldg(mirror_lists + (size_t)bin * RT_SMALL_LIST + lane);
+                __syncwarp();
+                const int x = x0 + (p % (RT_SMALL_TILE_W / 8)) * 8 + (lane & 7);
+                const int y = y0 + (p / (RT_SMALL_TILE_W / 8)) * 4 + (lane >> 3);
+                if (x < f.imgw && y < f.imgh && rt_shard_needs(f, x, y)) {
+                    live = true;
+                    pixel = y * f.imgw + x;
+                    ray.o = v3(f.pos[0], f.pos[1], f.pos[2]);
+                    ray.d = rt_primary_dir(f, x, y);
+                    ray.depth = 0;
+                    ray.off_plane0 = false;
+                    n_pixels++;
+                }
+            }
+    #ifdef RS_COSTMAP
             unsigned long long cm_t0;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cm_t0));
-#endif
-            if (x < f.imgw && y < f.imgh && rt_shard_needs(f, x, y)) {
-                image[y * f.imgw + x] = rt_trace_pixel<RtSmallScene<COUNT>, COUNT>(acc, f, x, y, s_pending,
-                                                                                  RT_SMALL_THREADS, tid, hit_ids, pc);
-                n_pixels++;
+            const int cm_pixel = pixel;
+    #endif
+            /* pass 0: chains run until they end or want to park (compact); what the queue cannot take is finished in
+             * pass 1 by the lane that holds it */
+    #pragma unroll 1
+            for (int pass = 0; pass < 2; pass++) {
+                sh.defer = pass == 0;
+                bool parked = false;
+                if (live) {
+                    const int py = pixel / f.imgw, px = pixel - py * f.imgw;
+                    unsigned int rgba;
+                    if (rt_trace_chain<RtSmallScene<COUNT>, COUNT, true>(acc, f, px, py, ray, s_pending, RT_SMALL_THREADS, tid,
+                                                                         hit_ids, pc, rgba)) {
+                        image[pixel] = rgba;
+                        live = false;
+                    } else {
+                        parked = true;
+                    }
+                }
+                __syncwarp();
+                if (!sh.defer) break;
+                if (rs_q_push(s_queue, s_qctl, lane, parked, ray, pixel, s_pending, tid)) live = false;
+                if (!__any_sync(0xffffffffu, live)) break;
             }
-#ifdef RS_COSTMAP
+    #ifdef RS_COSTMAP
             __syncwarp();   /* debug variant: ns spent on the patch, stored over the hit id of its first pixel */
-            if (lane == 0 && hit_ids && x < f.imgw && y < f.imgh) {
+            if (!from_queue && lane == 0 && hit_ids) {
                 unsigned long long cm_t1;
                 asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(cm_t1));
-                hit_ids[y * f.imgw + x] = (int)(cm_t1 - cm_t0);
+                hit_ids[cm_pixel] = (int)(cm_t1 - cm_t0);
             }
-#endif
-        }
-        __syncwarp();                            /* the list is rewritten for the next unit */
-#ifdef RS_TIMELINE
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
-        tl_units++;
-#endif
-        unsigned int u1 = 0;
-        if (lane == 0) {
-            u1 = atomicAdd(tile_counter, 1u);
-            if (order_w) {                       /* file the patch under its cost class for the next frame */
-                const unsigned int k = ((unsigned int)clock() - unit_t0) >> 10;
-                const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
-                const unsigned int at = atomicAdd(order_w + cls, 1u);
-                order_w[RS_ORDER_HEAD + (size_t)cls * n_fetch + at] = q;
+    #endif
+            if (from_queue) continue;
+    #ifdef RS_TIMELINE
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
+            tl_units++;
+    #endif
+            unsigned int u1 = 0;
+            if (lane == 0) {
+                u1 = atomicAdd(tile_counter, 1u);
+                if (order_w) {                       /* file the patch under its cost class for the next frame */
+                    const unsigned int k = ((unsigned int)clock() - unit_t0) >> 10;
+                    const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
+                    const unsigned int at = atomicAdd(order_w + cls, 1u);
+                    order_w[RS_ORDER_HEAD + (size_t)cls * n_fetch + at] = q;
+                }
             }
+            u0 = __shfl_sync(0xffffffffu, u1, 0);
         }
-        u0 = __shfl_sync(0xffffffffu, u1, 0);
     }
     rs_griddep_launch();                         /* FXAA may be launched; it waits for this grid to complete */
     if (COUNT) {
@@ -803,11 +1006,15 @@ extern "C" int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_pl
 
 /* per device, once (rt_create): opt in to the dynamic shared memory the largest accepted scene needs */
 extern "C" cudaError_t rt_trace_small_init(void) {
-    cudaError_t e = cudaFuncSetAttribute(rt_trace_small_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(rt_trace_small_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          RT_SMALL_DYN_SMEM_MAX);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(rt_trace_small_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                RT_SMALL_DYN_SMEM_MAX);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(rt_trace_small_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, RT_SMALL_DYN_SMEM_MAX);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(rt_trace_small_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RT_SMALL_DYN_SMEM_MAX);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(rt_trace_small_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RT_SMALL_DYN_SMEM_MAX);
+    return e;
 }
 
 /* bytes of tile-list storage a frame of this size needs */
@@ -832,7 +1039,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
                                              const unsigned int* order_r, unsigned int* order_w,
                                              int after_own_post, uint4* lgrid, int build_lgrid, int mirror_bins,
-                                             cudaStream_t stream) {
+                                             int compact, cudaStream_t stream) {
     /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel.
      * after_own_post: the previous operation on the stream is the FXAA / copy kernel of this context's previous
      * frame (nothing this frame reads is still being written): the pre-pass overlaps it, see rt_cull_tiles_kernel */
@@ -875,8 +1082,11 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const unsigned short* tl = tile_lists;
     const uint4* lg = lgrid;
     const unsigned short* ml = mirror_lists;
-    if (count) e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<true>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml);
-    else       e = cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<false>, *sc, *f, image, hit_ids, counters, tile_counter, tl, tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml);
+#define RS_LAUNCH(C, Q) cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<C, Q>, *sc, *f, image, hit_ids, counters, tile_counter, tl, \
+                                          tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml)
+    if (compact) e = count ? RS_LAUNCH(true, true) : RS_LAUNCH(false, true);
+    else         e = count ? RS_LAUNCH(true, false) : RS_LAUNCH(false, false);
+#undef RS_LAUNCH
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

@@ -355,6 +355,88 @@ def test_mirror_bins_change_tested_primitives_only():
     assert (img_a == img_b).all() and img_a.any()
 
 
+def test_ray_compaction_changes_scheduling_only():
+    """Rays of the second and later generations that have to traverse the hierarchy are parked in a per-CTA
+    shared-memory queue and traced 32 at a time by whichever warp finds a full batch (RT_OPT_COMPACTION 1).  Which
+    thread finishes a pixel must not matter: pixels, hit ids and the ray / test counters equal the lane-per-pixel
+    walk (RT_OPT_COMPACTION 0, the default) -- both views round the clock, the reflection-heavy sea levels of config 3, tiny and
+    odd frame sizes (partial batches only), shards, the deep-hierarchy fallback, mirror / light bins off (every bounce
+    and shadow ray traverses: the queue overflows and lanes finish rays themselves), random mirror clouds."""
+    r = gu.renderer()
+    s = rt.Scene()
+
+    def both(f, **kw):
+        r.set_option(_lib.RT_OPT_COMPACTION, 0)
+        a = gu.render(r, s, f, **kw)
+        r.set_option(_lib.RT_OPT_COMPACTION, 1)
+        b = gu.render(r, s, f, **kw)
+        r.set_option(_lib.RT_OPT_COMPACTION, 0)
+        assert (a[1] == b[1]).all(), int((a[1] != b[1]).sum())
+        assert (a[0] == b[0]).all(), int((a[0] != b[0]).sum())
+        return a
+
+    for view in (5, 6):
+        for hours in np.arange(0.0, 24.0, 3.0):
+            both(s.configure(view=view, hours=float(hours), imgw=960, imgh=540, alias=False))
+    for sea in (-4.5, 1.5, 7.5, 11.5):
+        both(s.configure(view=6, hours=14.0, imgw=1280, imgh=720, sea_level=sea, alias=True))
+    both(s.configure(view=5, hours=14.0, imgw=1920, imgh=1080, sea_level=-4.5, alias=True))
+    for (w, h) in ((33, 9), (2, 2), (641, 359), (8, 4), (64, 36)):
+        both(s.configure(view=5, hours=18.0, imgw=w, imgh=h, alias=False))
+    f = s.configure(view=5, hours=14.0, imgw=640, imgh=360, alias=True)
+    for n, sid in ((2, 1), (4, 3)):
+        sh = rt.make_shard(n, sid, 64, 32)
+        r.set_scene(s.objects, s.lights)
+        outs = []
+        for c in (0, 1):
+            r.set_option(_lib.RT_OPT_COMPACTION, c)
+            outs.append(r.render_to_host(f, shard=sh, out=np.zeros(640 * 360, dtype=np.uint32)).copy())
+        r.set_option(_lib.RT_OPT_COMPACTION, 0)
+        assert (outs[0] == outs[1]).all() and outs[0].any()
+    # every secondary ray traverses: bins off, then the deep-hierarchy fallback (linear loops) on top
+    f = s.configure(view=5, hours=9.0, imgw=800, imgh=450, alias=False)
+    r.set_option(_lib.RT_OPT_MIRROR_BINS, 1)
+    r.set_option(_lib.RT_OPT_SHADOW_BINS, 1)
+    both(f)
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 2)
+    both(f)
+    for k in (_lib.RT_OPT_TRACE_IMPL, _lib.RT_OPT_MIRROR_BINS, _lib.RT_OPT_SHADOW_BINS):
+        r.set_option(k, 0)
+    # counters: the same rays and the same tests, whoever runs them
+    f = s.configure(view=5, hours=14.0, imgw=960, imgh=540, alias=False)
+    cs = []
+    for c in (0, 1):
+        r.set_option(_lib.RT_OPT_COMPACTION, c)
+        r.set_option(_lib.RT_OPT_COUNTERS, 1)
+        gu.render(r, s, f)
+        cs.append(r.counters())
+        r.set_option(_lib.RT_OPT_COUNTERS, 0)
+    r.set_option(_lib.RT_OPT_COMPACTION, 0)
+    assert cs[0] == cs[1], (cs[0], cs[1])
+    # random clouds of mirrors: long chains everywhere
+    rng = np.random.default_rng(31)
+    base = s.objects.copy()
+    f = s.configure(view=5, hours=14.0, imgw=480, imgh=270, alias=False)
+    for k in range(6):
+        n = int(rng.integers(30, 200))
+        o = np.zeros(n + 1, dtype=base.dtype)
+        o[0] = base[0]
+        src_t = base[base["type"] == 2][0]
+        src_s = base[(base["type"] == 0) & (base["light"] == 0)][0]
+        for i in range(1, n + 1):
+            c = rng.uniform([-110, -6, 10], [0, 30, 130])
+            if rng.random() < 0.4:
+                o[i] = src_s
+                o[i]["pos"] = c
+                o[i]["size"] = [rng.uniform(0.5, 6.0)] * 3
+            else:
+                o[i] = src_t
+                a, b = rng.normal(size=3) * rng.uniform(2, 15), rng.normal(size=3) * rng.uniform(2, 15)
+                o[i]["pos"], o[i]["size"], o[i]["third"] = c, c + a, c + b
+            o[i]["mirror"] = float(rng.choice([0.0, 0.3, 0.8]))
+        both(f, objects=o)
+
+
 def test_order_history_changes_scheduling_only():
     """Whole frames of the shared-memory tracer are walked most-expensive-patch-first using the costs the
     previous frame of the same size measured (RT_OPT_ORDER 0).  The frames must not depend on it: same pixels
