@@ -69,7 +69,7 @@ enum {
     RT_OPT_FXAA_IMPL = 2,   /* 0 = TMA-staged (default when width%4==0), 1 = plain shared-memory */
     RT_OPT_TIMING    = 3,   /* 1 = record CUDA events around trace and fxaa */
     RT_OPT_SKY_ALL4  = 4,   /* 1 = fetch all four sky maps like the reference (default 0: only non-zero weights; bit-identical) */
-    RT_OPT_TRACE_IMPL = 5,  /* 0 = auto: shared-memory tracer when the scene fits (<= ~165 primitives), else the HBM-resident LBVH tracer; 1 = always the HBM tracer; 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests) */
+    RT_OPT_TRACE_IMPL = 5,  /* 0 = auto: shared-memory tracer when the scene fits (<= ~165 primitives), else the persistent packet tracer of big scenes (trace_big.cu); 1 = the plain one-thread-per-pixel tracer over the HBM-resident LBVH (no lists, no packets: the cross-check of the other two); 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests); 3 = the persistent packet tracer for any scene.  Identical pixels */
     RT_OPT_BUILDER = 6,     /* hierarchy over the Morton-sorted primitives: 0 = auto (PLOC up to 1024 primitives, Karras above), 1 = Karras, 2 = PLOC */
     RT_OPT_FORCE_RADIX = 7, /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
     RT_OPT_ORDER = 8,       /* work order of the shared-memory tracer on whole frames: 0 = most expensive patches of the previous frame of this size first (default; first frame bottom-up), 1 = always bottom-up.  Scheduling only: identical pixels */
@@ -77,7 +77,8 @@ enum {
     RT_OPT_MIRROR_BINS = 10, /* rays that primary rays send off plane 0 (the sea) in the shared-memory tracer: 0 = candidate lists of the bin's mirrored frustum (default), 1 = traverse the hierarchy.  Which primitives get tested only: identical pixels */
     RT_OPT_LIGHT_BINS_REUSE = 11, /* light bins of the shared-memory tracer: 0 = rebuilt only when the scene or the lights changed since they were built (default; they do not depend on the camera), 1 = rebuilt by every frame's pre-pass.  Identical pixels */
     RT_OPT_COMPACTION = 12, /* ray compaction in the shared-memory tracer: 0 = every lane follows its own pixel's chain to the end (default), 1 = rays of the second and later generations that have to traverse the hierarchy are parked in a per-CTA shared-memory queue (ballot + popc slot assignment) and traced 32 at a time by full warps.  Measured SLOWER on every BASELINE view (full warps, but rays of unrelated patches: the traversal loses the coherence an 8x4 patch has), hence opt-in.  Scheduling only: identical pixels */
-    RT_OPT_N = 13
+    RT_OPT_PACKET = 13, /* persistent tracer of big scenes: 0 = the 32 primary rays of an 8x4 patch walk the hierarchy as ONE packet (warp-uniform node, one stack per warp, broadcast node loads; default), 1 = every lane traverses for itself.  Identical pixels */
+    RT_OPT_N = 14
 };
 
 /* One frame's uniforms: what launchKernel receives by value / as small host arrays. */
@@ -217,6 +218,9 @@ int  rt_get_counters(rt_context* ctx, unsigned long long out[RT_CNT_COUNT]);
  * bins of 8 ushorts: [0] count or 0xFFFF = too many, [1..7] leaf offsets); returns the bytes copied, 0 if none,
  * -RT_ERR_* on an error */
 long long rt_debug_light_bins(rt_context* ctx, void* out, size_t bytes);
+/* Error word of the device code: bit 0 = a traversal stack ran out (hierarchy deeper than rt_set_scene's check lets
+ * through; the frame is not to be trusted).  Synchronises; reading clears the word. */
+int  rt_get_device_errors(rt_context* ctx, unsigned int* out);
 /* kernels this library has launched in this process so far (all contexts): callers difference it around a region */
 unsigned long long rt_launch_count(void);
 /* ms of the last frame's kernels (RT_OPT_TIMING=1): [0]=trace [1]=fxaa [2]=bvh build/refit */

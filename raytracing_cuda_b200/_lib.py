@@ -21,6 +21,7 @@ RT_OPT_SHADOW_BINS = 9
 RT_OPT_MIRROR_BINS = 10
 RT_OPT_LIGHT_BINS_REUSE = 11
 RT_OPT_COMPACTION = 12
+RT_OPT_PACKET = 13
 RT_PEER_HANDLE_BYTES = 64
 RT_MAX_SLOTS = 8
 RT_CNT_COUNT = 16
@@ -73,6 +74,7 @@ SIGNATURES = {
     "rt_synchronize": (C.c_int, [_P]),
     "rt_get_counters": (C.c_int, [_P, C.POINTER(C.c_ulonglong)]),
     "rt_debug_light_bins": (C.c_longlong, [_P, C.c_void_p, C.c_size_t]),
+    "rt_get_device_errors": (C.c_int, [_P, C.POINTER(C.c_uint)]),
     "rt_launch_count": (C.c_ulonglong, []),
     "rt_get_timings": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "rt_bvh_info": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -33,6 +33,9 @@ cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned
 int rt_radix_hist_entries(int n);
 cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                             RtCountersDev* counters, int brute, int count, cudaStream_t stream);
+cudaError_t rt_launch_trace_big(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
+                                RtCountersDev* counters, unsigned int* tile_counter, unsigned int* err, int count,
+                                int packet, int n_sm, cudaStream_t stream);
 cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
@@ -617,9 +620,13 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
     ctx->last_base = image;
     if (count) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(RtCountersDev), ctx->stream));
     if (timing) cudaEventRecord(ctx->ev[0], ctx->stream);
-    /* RT_OPT_TRACE_IMPL: 0 = auto (shared-memory tracer when the scene fits), 1 = HBM-resident LBVH tracer,
-     * 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests) */
-    const bool small = ctx->opt[RT_OPT_TRAVERSAL] != 1 && ctx->opt[RT_OPT_TRACE_IMPL] != 1 &&
+    /* RT_OPT_TRACE_IMPL: 0 = auto (shared-memory tracer when the scene fits, else the persistent packet tracer of big
+     * scenes), 1 = the plain one-thread-per-pixel tracer over the HBM-resident LBVH (tests: it has no lists, no packets),
+     * 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests), 3 = the persistent packet tracer for
+     * any scene */
+    const int impl = ctx->opt[RT_OPT_TRACE_IMPL];
+    const bool brute = ctx->opt[RT_OPT_TRAVERSAL] == 1;
+    const bool small = !brute && impl != 1 && impl != 3 &&
                        rt_trace_small_supported(ctx->scene.n_bvh_prims, ctx->scene.n_objects, ctx->scene.n_planes);
     if (small) {
         const size_t need = rt_trace_small_list_bytes(frame->imgw, frame->imgh) / sizeof(unsigned short);
@@ -687,8 +694,12 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
         RtSceneDev sc = ctx->scene;
         if (!grid)
             for (int i = 0; i < RT_LGB_LIGHTS; i++) sc.lg_offsets[i] = sc.lg_entries[i] = nullptr;
-        RT_CHECK(ctx, rt_launch_trace(&sc, &f, image, hit_ids_dev, ctx->d_counters,
-                                      ctx->opt[RT_OPT_TRAVERSAL] == 1, count, ctx->stream));
+        if (brute || impl == 1)
+            RT_CHECK(ctx, rt_launch_trace(&sc, &f, image, hit_ids_dev, ctx->d_counters, brute, count, ctx->stream));
+        else
+            RT_CHECK(ctx, rt_launch_trace_big(&sc, &f, image, hit_ids_dev, ctx->d_counters, ctx->d_tile_counter,
+                                              ctx->d_tile_counter + RT_DEVICE_ERROR_WORD, count,
+                                              ctx->opt[RT_OPT_PACKET] == 0, ctx->n_sm, ctx->stream));
     }
     if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }
     int rc = RT_OK;
@@ -1000,6 +1011,17 @@ long long rt_debug_light_bins(rt_context* ctx, void* out, size_t bytes) {
 }
 
 unsigned long long rt_launch_count(void) { return __atomic_load_n(&g_rt_launches, __ATOMIC_RELAXED); }
+
+/* Error word of the device code (bit 0: a traversal stack ran out -- the hierarchy is deeper than rt_set_scene's
+ * check allows, pixels of that frame are not to be trusted).  Synchronises; the word is cleared by the read. */
+int rt_get_device_errors(rt_context* ctx, unsigned int* out) {
+    if (!ctx || !out) return RT_ERR_ARG;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    RT_CHECK(ctx, cudaMemcpy(out, ctx->d_tile_counter + RT_DEVICE_ERROR_WORD, sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    if (*out) RT_CHECK(ctx, cudaMemset(ctx->d_tile_counter + RT_DEVICE_ERROR_WORD, 0, sizeof(unsigned int)));
+    return RT_OK;
+}
 
 int rt_get_timings(rt_context* ctx, float out_ms[3]) {
     if (!ctx || !out_ms) return RT_ERR_ARG;

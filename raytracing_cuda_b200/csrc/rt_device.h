@@ -61,6 +61,10 @@ struct RtPeerSync {
     int rank;
     unsigned int timeout_ms;
 };
+/* the context's 64-uint counter block (api.cu d_tile_counter): [0] next work unit, [1] finished warps, [32] listed
+ * tiles of a shard (trace_small.cu), [40] device error word (rt_get_device_errors), [48] CTA ticket of the peer
+ * hand-shake (fxaa.cu) */
+#define RT_DEVICE_ERROR_WORD 40
 #define RT_BYVALUE_MAX 304             /* objects passed in kernel parameters (68 B each) by the per-frame refit */
 /* light bins of the small-scene tracer (trace_small.cu): per light a cube map of RT_LGRID_G x RT_LGRID_G direction
  * bins per face, each bin one uint4 = 8 ushorts: [0] count (0xFFFF: too many, traverse), [1..7] leaf offsets */

@@ -1,0 +1,94 @@
+/*
+ * trace_global.cuh -- scene accessor over the HBM / L2-resident LBVH (any primitive count), shared by the plain
+ * one-thread-per-pixel tracer (trace.cu) and the persistent tracer of big scenes (trace_big.cu).
+ */
+#ifndef RTB_TRACE_GLOBAL_CUH
+#define RTB_TRACE_GLOBAL_CUH
+
+#include "trace_pixel.cuh"
+
+/* Shadow ray of light `li` against the light grid of a big scene (light_grid.cu): the ray's line passes through the
+ * light, its direction from there is -to_light (to_light = L - P, the vector the caller normalised into d); the bin
+ * of that direction lists every primitive such a line can hit.  Returns 1 = occluded, 0 = not occluded, -1 = this
+ * light has no grid (the caller traverses the hierarchy).  Planes stay outside the grid and are tested here. */
+template <bool COUNT>
+__device__ __forceinline__ int rt_light_grid_occluded(const RtSceneDev& sc, const vec3& o, const vec3& d, float tmax,
+                                                      const vec3& to_light, int li, RtLocalCounters& cnt) {
+    /* static indices: a dynamic one would copy the kernel parameter block to local memory */
+    static_assert(RT_LGB_LIGHTS == 2, "select below");
+    const unsigned int* __restrict__ lg_off = li == 0 ? sc.lg_offsets[0] : (li == 1 ? sc.lg_offsets[1] : nullptr);
+    if (!lg_off) return -1;
+    const float ax = fabsf(to_light.x), ay = fabsf(to_light.y), az = fabsf(to_light.z);
+    const bool X = ax >= ay && ax >= az, Y = !X && ay >= az;
+    const float m = X ? ax : (Y ? ay : az);
+    if (!(m > 0.0f)) return -1;
+    for (int p = 0; p < sc.n_planes; p++) {
+        const float4 q0 = __ldg(sc.planes + 2 * p), q1 = __ldg(sc.planes + 2 * p + 1);
+        float t;
+        if (COUNT) cnt.plane_tests++;
+        if (__float_as_uint(q0.w) & RT_TAG_EMISSIVE) continue;
+        if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t) && t < tmax) return 1;
+    }
+    const float qm = X ? to_light.x : (Y ? to_light.y : to_light.z);
+    const float qa = X ? to_light.y : (Y ? to_light.z : to_light.x);
+    const float qb = X ? to_light.z : (Y ? to_light.x : to_light.y);
+    const int face = (X ? 0 : (Y ? 2 : 4)) + (qm > 0.0f ? 1 : 0);      /* direction = -to_light */
+    const float scale = (float)RT_LGB_G / (2.0f + 2.0f * 0.00390625f);  /* RS_LG_SCALE_OF(RT_LGB_G) */
+    const float k = -scale * rt_rcp_approx(m);
+    const float gs = __fmaf_rn(qa, k, scale * (1.0f + 0.00390625f));
+    const float gt = __fmaf_rn(qb, k, scale * (1.0f + 0.00390625f));
+    const int ix = min(max((int)gs, 0), RT_LGB_G - 1), iy = min(max((int)gt, 0), RT_LGB_G - 1);
+    const unsigned int* __restrict__ off = lg_off + ((size_t)face * RT_LGB_G + iy) * RT_LGB_G + ix;
+    const unsigned int e0 = __ldg(off), e1 = __ldg(off + 1);
+    const unsigned int* __restrict__ ent = li == 0 ? sc.lg_entries[0] : sc.lg_entries[1];
+    for (unsigned int e = e0; e < e1; e++) {
+        float t;
+        unsigned int tag;
+        if (rt_test_record<COUNT>(sc.prims + 3 * (size_t)__ldg(ent + e), o, d, t, tag, cnt) &&
+            !(tag & RT_TAG_EMISSIVE) && t < tmax)
+            return 1;
+    }
+    return 0;
+}
+
+/* scene accessor over the HBM-resident LBVH (any primitive count) */
+template <bool BRUTE, bool COUNT>
+struct RtGlobalScene {
+    const RtSceneDev& sc;
+    __device__ __forceinline__ RtGlobalScene(const RtSceneDev& s) : sc(s) {}
+#ifdef RT_NODEMAP
+    unsigned int dbg[3] = {0, 0, 0};   /* debug variant: node tests of primary / bounce / shadow rays */
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, bool, RtLocalCounters& cnt) {
+        const unsigned int before = cnt.node_tests;
+        const RtHit h = rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
+        dbg[depth ? 1 : 0] += cnt.node_tests - before;
+        return h;
+    }
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3&, int, RtLocalCounters& cnt) {
+        const unsigned int before = cnt.node_tests;
+        const bool r = rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
+        dbg[2] += cnt.node_tests - before;
+        return r;
+    }
+#else
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int, bool, RtLocalCounters& cnt) {
+        return rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
+    }
+    /* to_light = L - P (the vector the caller normalised into d), li = index of the light */
+    __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3& to_light, int li,
+                                             RtLocalCounters& cnt) {
+        if (!BRUTE) {
+            const int g = rt_light_grid_occluded<COUNT>(sc, o, d, tmax, to_light, li, cnt);
+            if (g >= 0) return g != 0;
+        }
+        return rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
+    }
+#endif
+    __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) { return rt_hit_normal<BRUTE>(sc, h, P); }
+    __device__ __forceinline__ void material(unsigned int idx, float4& m0, float4& m1) {
+        m0 = __ldg(sc.mats + 2 * idx);
+        m1 = __ldg(sc.mats + 2 * idx + 1);
+    }
+};
+
+#endif

@@ -245,6 +245,12 @@ class Renderer:
         self._check(self._lib.rt_get_counters(self._h, buf), "rt_get_counters")
         return {name: int(buf[i]) for i, name in enumerate(_lib.COUNTER_NAMES)}
 
+    def device_errors(self):
+        """Error word of the device code (bit 0: a traversal stack ran out); synchronises, reading clears it."""
+        e = C.c_uint(0)
+        self._check(self._lib.rt_get_device_errors(self._h, C.byref(e)), "rt_get_device_errors")
+        return e.value
+
     def light_bins(self):
         """Diagnostics: the light bins of the last small-scene frame as uint16[4 lights, 6 faces, 64, 64, 8]
         ([..., 0] = count or 0xFFFF, [..., 1:] = leaf offsets), or None."""

@@ -334,3 +334,67 @@ def test_light_grid_of_big_scenes_changes_tested_primitives_only():
     frames = [r.render_to_host(f, want_ids=False).copy() for _ in range(3)]
     assert (frames[0] == frames[1]).all() and (frames[1] == frames[2]).all()
     r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
+
+
+def test_persistent_packet_tracer_equals_plain_tracer():
+    """The tracer of big scenes (trace_big.cu: persistent warps, the 32 primary rays of an 8x4 patch walking the LBVH as
+    one packet, per-lane stacks in shared memory; RT_OPT_TRACE_IMPL 0 for scenes that do not fit shared memory, 3 =
+    forced) against the plain one-thread-per-pixel tracer (RT_OPT_TRACE_IMPL 1): pixels and hit ids identical -- the
+    terrain from several poses (incl. grazing rays and a camera inside it), packets off (RT_OPT_PACKET 1), odd frame
+    sizes, screen-tile shards of several tile sizes, the built-in scene (spheres, huge triangles, mirror chains),
+    degenerate scenes.  The device error word (traversal stack ran out) stays clear."""
+    r = gu.renderer()
+    s = rt.Scene()
+    objs = rt.terrain_objects(160)
+
+    def frames(f, o, lights, shard=None):
+        outs = []
+        r.set_scene(o, lights)
+        for impl, packet in ((1, 0), (3, 0), (3, 1)):
+            r.set_option(_lib.RT_OPT_TRACE_IMPL, impl)
+            r.set_option(_lib.RT_OPT_PACKET, packet)
+            if shard is None:
+                outs.append(r.render_to_host(f, want_ids=True))
+            else:
+                img = r.render_to_host(f, shard=shard, out=np.zeros(f.imgw * f.imgh, dtype=np.uint32)).copy()
+                outs.append((img, img))
+        r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
+        r.set_option(_lib.RT_OPT_PACKET, 0)
+        for k in (1, 2):
+            assert (outs[0][1] == outs[k][1]).all(), (k, int((outs[0][1] != outs[k][1]).sum()))
+            assert (outs[0][0] == outs[k][0]).all(), (k, int((outs[0][0] != outs[k][0]).sum()))
+        return outs[0]
+
+    rng = np.random.default_rng(17)
+    poses = [((324.4, 330.0, -84.0), 141.2, 35.0), ((324.4, 330.0, -84.0), 141.2, 2.0), ((0.0, 20.0, 0.0), 10.0, 0.0),
+             ((-400.0, 500.0, 600.0), 300.0, 44.0), ((100.0, -5.0, 100.0), 45.0, -20.0)]
+    for k, (pos, hor, ver) in enumerate(poses):
+        s.set_pose(pos, hor, ver)
+        s.set_time(float(rng.uniform(0, 24)))
+        for (w, h, alias) in ((480, 270, False), (333, 187, True)):
+            s.set_antialiasing(alias)
+            img, ids = frames(s.frame(w, h), objs, s.lights)
+        assert k != 0 or (ids >= 1).mean() > 0.5
+    # the auto choice for a big scene IS the packet tracer
+    s.set_pose(*poses[0])
+    s.set_antialiasing(False)
+    f = s.frame(480, 270)
+    r.set_scene(objs, s.lights)
+    a = r.render_to_host(f).copy()
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 3)
+    assert (a == r.render_to_host(f)).all()
+    r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
+    # shards: tiles large enough for the four-corner shortcut, and tiles too small for it
+    s.set_antialiasing(True)
+    f = s.frame(640, 360)
+    for n, sid, tw, th in ((2, 1, 64, 32), (4, 3, 128, 64), (8, 5, 64, 32), (3, 2, 8, 4), (2, 0, 2, 2)):
+        frames(f, objs, s.lights, shard=rt.make_shard(n, sid, tw, th))
+    # the built-in scene through it, both views, and a few degenerate scenes
+    for view in (5, 6):
+        for hours in (14.0, 1.0, 9.0):
+            frames(s.configure(view=view, hours=hours, imgw=640, imgh=360, alias=False), s.objects, s.lights)
+    f = s.configure(view=5, hours=14.0, imgw=160, imgh=90, alias=False)
+    base = s.objects.copy()
+    for subset in ([0], [0, 129], [129], [5], [0, 131, 132], list(range(11, 33))):
+        frames(f, base[subset], s.lights)
+    assert r.device_errors() == 0
