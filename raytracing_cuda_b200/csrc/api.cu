@@ -40,7 +40,7 @@ cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, uns
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
                                   unsigned int* order_w, int after_own_post, uint4* lgrid, int build_lgrid,
-                                  int mirror_bins, int compact, cudaStream_t stream);
+                                  int mirror_bins, int compact, int fetch_max, cudaStream_t stream);
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
@@ -673,7 +673,8 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
                                             ctx->scene_settled ? 1 : 0, use_lgrid ? ctx->d_lgrid : (uint4*)nullptr,
                                             build_lgrid ? 1 : 0, ctx->opt[RT_OPT_MIRROR_BINS] == 0,
-                                            ctx->opt[RT_OPT_COMPACTION] != 0, ctx->stream));
+                                            ctx->opt[RT_OPT_COMPACTION] != 0, ctx->opt[RT_OPT_FETCH] == 0 ? 4 : 1,
+                                            ctx->stream));
         if (use_lgrid) ctx->lgrid_valid = true;
     }
     else {

@@ -5,9 +5,10 @@
  * all three kernels agree bit for bit; only WHICH primitives get tested, and in what order, differs.
  *
  * What changes against the plain one-thread-per-pixel kernel (trace.cu):
- *   - persistent CTAs (4 per SM), every WARP autonomous: it pulls single 8x4-pixel patches from an atomic counter,
- *     the frame walked from its last patch to its first, no CTA barrier in the loop (as in trace_small.cu); for a
- *     screen-tile shard a patch none of whose pixels the shard needs costs four owner look-ups, not a launch slot;
+ *   - persistent CTAs (4 per SM), every WARP autonomous: a CTA reserves chunks of 8x4 patches (64x16 pixels) from a
+ *     global counter, its warps pull single 8x4-pixel patches of the chunk from a counter in shared memory; the
+ *     frame is walked from its last chunk to its first, no CTA barrier in the loop; for a screen-tile shard a
+ *     patch none of whose pixels the shard needs costs four owner look-ups, not a launch slot;
  *   - PACKET traversal for the primary rays.  The 32 primary rays of a patch form a thin bundle and visit almost
  *     the same nodes, so the warp walks the hierarchy ONCE for all of them: one warp-uniform node index, one stack
  *     per warp in shared memory, every lane tests ITS ray against the node's two child boxes, a child is entered
@@ -210,23 +211,6 @@ struct RtBigScene {
     }
 };
 
-/* Which pixels of the patch [x0, x0+8) x [y0, y0+4) does this shard trace (own tiles + the 1-pixel FXAA apron)?
- * Whole frames: all of them.  Shards whose tiles are at least 10x6 pixels: the patch grown by one pixel spans at most
- * 2x2 tiles, so four owner look-ups (lanes 0..3, one corner each) settle the common cases -- no corner owned: nothing to
- * trace; all four owned: everything; only a patch on a tile border asks per pixel. */
-__device__ __forceinline__ bool rb_patch_pixel_needed(const RtFrameDev& f, int x0, int y0, int x, int y, int lane) {
-    const bool inside = x < f.imgw && y < f.imgh;
-    if (f.n_shards <= 1) return inside;
-    if (f.tile_w >= 10 && f.tile_h >= 6) {
-        const int cx = (lane & 1) ? min(x0 + 8, f.imgw - 1) : max(x0 - 1, 0);
-        const int cy = (lane & 2) ? min(y0 + 4, f.imgh - 1) : max(y0 - 1, 0);
-        const unsigned int own = __ballot_sync(0xffffffffu, lane < 4 && rt_shard_owns(f, cx, cy)) & 15u;
-        if (own == 0u) return false;
-        if (own == 15u) return inside;
-    }
-    return inside && rt_shard_needs(f, x, y);
-}
-
 template <bool COUNT>
 __global__ void __launch_bounds__(RB_THREADS, RB_CTAS_PER_SM)
 rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image, int* __restrict__ hit_ids,
@@ -236,22 +220,48 @@ rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __res
     __shared__ int s_stack[RB_WARPS][RB_STACK_SMEM][32];     /* per-lane stacks: entry e of lane l at [warp][e][l] */
     __shared__ int s_wstack[RB_WARPS][RB_PACKET_STACK];       /* per-warp stack of the packet traversal */
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int px_w = (f.imgw + 7) / 8, px_h = (f.imgh + 3) / 4;
-    const unsigned int n_patches = (unsigned int)(px_w * px_h);
-
-    unsigned int u = 0;
-    if (lane == 0) u = atomicAdd(tile_counter + RB_CNT_PATCH, 1u);
-    u = __shfl_sync(0xffffffffu, u, 0);
+    /* Work units.  The frame is cut into CHUNKS of 8x4 patches (64x16 pixels); a CTA reserves one chunk at a time from
+     * the global counter and its eight warps take the chunk's patches one by one from a counter in shared memory,
+     * each warp for itself.  The warps of an SM so work on neighbouring patches at about the same time and share
+     * the nodes and leaf records they pull through L1 -- handing single patches to whichever warp of the GPU asks
+     * next scatters neighbours over all SMs and was measured 38 % slower than the plain kernel.
+     * s_pool = (chunk << 6) | k: k < 32 = next patch of the chunk, k = 32 = used up (whoever draws it refills),
+     * k > 32 = a refill is under way (at most one draw per waiting warp: k <= 40). */
+    __shared__ unsigned int s_pool;
+    const int cw = (f.imgw + 63) / 64, ch = (f.imgh + 15) / 16;
+    const unsigned int n_chunks = (unsigned int)(cw * ch);
+    if (tid == 0) s_pool = 32u;
+    __syncthreads();
 
     RtBigScene<COUNT> acc(sc, &s_stack[warp][0][lane], err);
     RtPixelCounters pc = {{0, 0, 0, 0, 0, 0, 0, 0, 0}, 0, 0, 0, 0};
     unsigned int n_pixels = 0;
 
-    while (u < n_patches) {
-        const unsigned int p = n_patches - 1u - u;            /* bottom-up, like trace_small.cu */
-        const int py = (int)(p / (unsigned int)px_w), pxi = (int)p - py * px_w;
-        const int x = pxi * 8 + (lane & 7), y = py * 4 + (lane >> 3);
-        const bool mine = rb_patch_pixel_needed(f, pxi * 8, py * 4, x, y, lane);
+    for (;;) {
+        unsigned int unit = 0;
+        if (lane == 0) {
+            for (;;) {
+                const unsigned int old = atomicAdd(&s_pool, 1u);
+                const unsigned int k = old & 63u;
+                if (k < 32u) { unit = old; break; }
+                if (k == 32u) {                                   /* this warp refills the CTA's pool */
+                    const unsigned int g = atomicAdd(tile_counter + RB_CNT_PATCH, 1u);
+                    unit = g << 6;                                /* ... and takes the new chunk's first patch */
+                    atomicExch(&s_pool, (g << 6) | 1u);
+                    break;
+                }
+                while ((*(volatile unsigned int*)&s_pool & 63u) >= 32u) __nanosleep(64);
+            }
+        }
+        unit = __shfl_sync(0xffffffffu, unit, 0);
+        const unsigned int g = unit >> 6, k = unit & 63u;
+        if (g >= n_chunks) break;                                 /* every later chunk is past the end too */
+        const unsigned int c = n_chunks - 1u - g;                /* bottom-up, like trace_small.cu */
+        const int cy = (int)(c / (unsigned int)cw), cx = (int)c - cy * cw;
+        const int x0 = cx * 64 + (int)(k & 7u) * 8, y0 = cy * 16 + (int)(k >> 3) * 4;
+        if (x0 >= f.imgw || y0 >= f.imgh) continue;
+        const int x = x0 + (lane & 7), y = y0 + (lane >> 3);
+        const bool mine = rt_patch_pixel_needed(f, x0, y0, x, y, lane);
         if (__any_sync(0xffffffffu, mine)) {
             acc.have_primary = false;
             if (packet) {
@@ -273,9 +283,6 @@ rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __res
             }
             __syncwarp();
         }
-        unsigned int un = 0;
-        if (lane == 0) un = atomicAdd(tile_counter + RB_CNT_PATCH, 1u);
-        u = __shfl_sync(0xffffffffu, un, 0);
     }
     rb_griddep_launch();
     if (COUNT) rt_flush_counters(pc, n_pixels, counters);
@@ -292,9 +299,9 @@ rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __res
 extern "C" cudaError_t rt_launch_trace_big(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                            RtCountersDev* counters, unsigned int* tile_counter, unsigned int* err,
                                            int count, int packet, int n_sm, cudaStream_t stream) {
-    const int patches = ((f->imgw + 7) / 8) * ((f->imgh + 3) / 4);
+    const int chunks = ((f->imgw + 63) / 64) * ((f->imgh + 15) / 16);     /* a CTA works through whole chunks */
     int grid = n_sm * RB_CTAS_PER_SM;
-    if (grid > (patches + RB_WARPS - 1) / RB_WARPS) grid = (patches + RB_WARPS - 1) / RB_WARPS;
+    if (grid > chunks) grid = chunks;
     if (grid < 1) grid = 1;
     RT_LAUNCHED(1);
     if (count) rt_trace_big_kernel<true><<<grid, RB_THREADS, 0, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, err, packet);

@@ -282,4 +282,21 @@ __device__ __forceinline__ bool rt_shard_needs(const RtFrameDev& f, int x, int y
            rt_shard_owns(f, x1, y1) || rt_shard_owns(f, x, y);
 }
 
+/* All 32 lanes of a warp call (lane = its lane id, (x, y) = its pixel of the patch).  Which pixels of the patch [x0, x0+8) x [y0, y0+4) does this shard trace (own tiles + the 1-pixel FXAA apron)?
+ * Whole frames: all of them.  Shards whose tiles are at least 10x6 pixels: the patch grown by one pixel spans at most
+ * 2x2 tiles, so four owner look-ups (lanes 0..3, one corner each) settle the common cases -- no corner owned: nothing to
+ * trace; all four owned: everything; only a patch on a tile border asks per pixel. */
+__device__ __forceinline__ bool rt_patch_pixel_needed(const RtFrameDev& f, int x0, int y0, int x, int y, int lane) {
+    const bool inside = x < f.imgw && y < f.imgh;
+    if (f.n_shards <= 1) return inside;
+    if (f.tile_w >= 10 && f.tile_h >= 6) {
+        const int cx = (lane & 1) ? min(x0 + 8, f.imgw - 1) : max(x0 - 1, 0);
+        const int cy = (lane & 2) ? min(y0 + 4, f.imgh - 1) : max(y0 - 1, 0);
+        const unsigned int own = __ballot_sync(0xffffffffu, lane < 4 && rt_shard_owns(f, cx, cy)) & 15u;
+        if (own == 0u) return false;
+        if (own == 15u) return inside;
+    }
+    return inside && rt_shard_needs(f, x, y);
+}
+
 #endif
