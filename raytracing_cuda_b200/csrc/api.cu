@@ -32,10 +32,11 @@ cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned
                                 unsigned int* hist, int n, int force_radix, cudaStream_t stream);
 int rt_radix_hist_entries(int n);
 cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
-                            RtCountersDev* counters, int brute, int count, cudaStream_t stream);
+                            RtCountersDev* counters, unsigned int* err, int brute, int count, int packet,
+                            cudaStream_t stream);
 cudaError_t rt_launch_trace_big(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                 RtCountersDev* counters, unsigned int* tile_counter, unsigned int* err, int count,
-                                int packet, int n_sm, cudaStream_t stream);
+                                int packet, int smem_stack, int n_sm, cudaStream_t stream);
 cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
@@ -620,13 +621,14 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
     ctx->last_base = image;
     if (count) RT_CHECK(ctx, cudaMemsetAsync(ctx->d_counters, 0, sizeof(RtCountersDev), ctx->stream));
     if (timing) cudaEventRecord(ctx->ev[0], ctx->stream);
-    /* RT_OPT_TRACE_IMPL: 0 = auto (shared-memory tracer when the scene fits, else the persistent packet tracer of big
-     * scenes), 1 = the plain one-thread-per-pixel tracer over the HBM-resident LBVH (tests: it has no lists, no packets),
-     * 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests), 3 = the persistent packet tracer for
-     * any scene */
+    /* RT_OPT_TRACE_IMPL: 0 = auto (shared-memory tracer when the scene fits, else the plain one-thread-per-pixel tracer
+     * over the HBM-resident LBVH), 1 = the plain tracer for any scene (tests: it has no lists, no packets), 2 =
+     * shared-memory tracer with its deep-hierarchy fallback forced (tests), 3 = the persistent tracer of trace_big.cu
+     * (packets per RT_OPT_PACKET; measured slower than the plain kernel on the terrain, hence not the default), 4 = the
+     * plain tracer with packet traversal of the primary rays */
     const int impl = ctx->opt[RT_OPT_TRACE_IMPL];
     const bool brute = ctx->opt[RT_OPT_TRAVERSAL] == 1;
-    const bool small = !brute && impl != 1 && impl != 3 &&
+    const bool small = !brute && impl != 1 && impl != 3 && impl != 4 &&
                        rt_trace_small_supported(ctx->scene.n_bvh_prims, ctx->scene.n_objects, ctx->scene.n_planes);
     if (small) {
         const size_t need = rt_trace_small_list_bytes(frame->imgw, frame->imgh) / sizeof(unsigned short);
@@ -695,12 +697,14 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
         RtSceneDev sc = ctx->scene;
         if (!grid)
             for (int i = 0; i < RT_LGB_LIGHTS; i++) sc.lg_offsets[i] = sc.lg_entries[i] = nullptr;
-        if (brute || impl == 1)
-            RT_CHECK(ctx, rt_launch_trace(&sc, &f, image, hit_ids_dev, ctx->d_counters, brute, count, ctx->stream));
+        unsigned int* const errw = ctx->d_tile_counter + RT_DEVICE_ERROR_WORD;
+        if (brute || impl != 3)
+            RT_CHECK(ctx, rt_launch_trace(&sc, &f, image, hit_ids_dev, ctx->d_counters, errw, brute, count,
+                                          impl == 4 && !brute && ctx->opt[RT_OPT_PACKET] == 0, ctx->stream));
         else
-            RT_CHECK(ctx, rt_launch_trace_big(&sc, &f, image, hit_ids_dev, ctx->d_counters, ctx->d_tile_counter,
-                                              ctx->d_tile_counter + RT_DEVICE_ERROR_WORD, count,
-                                              ctx->opt[RT_OPT_PACKET] == 0, ctx->n_sm, ctx->stream));
+            RT_CHECK(ctx, rt_launch_trace_big(&sc, &f, image, hit_ids_dev, ctx->d_counters, ctx->d_tile_counter, errw, count,
+                                              ctx->opt[RT_OPT_PACKET] == 0, ctx->opt[RT_OPT_BIG_STACK] != 0, ctx->n_sm,
+                                              ctx->stream));
     }
     if (timing) { cudaEventRecord(ctx->ev[1], ctx->stream); cudaEventRecord(ctx->ev[2], ctx->stream); }
     int rc = RT_OK;

@@ -23,24 +23,46 @@
 template <bool BRUTE, bool COUNT>
 __global__ void __launch_bounds__(RT_TRACE_THREADS)
 rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
-                int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters) {
+                int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters, unsigned int* __restrict__ err, int packet) {
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_TRACE_THREADS];   /* (phong.rgb, kR) per depth */
+    __shared__ int s_wstack[RT_TRACE_THREADS / 32][RT_PACKET_STACK];  /* per-warp stack of the packet traversal */
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     /* block = 32x8 pixels, warp = 8x4 patch */
     const int x = blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
     const int y = blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
-    if (x >= f.imgw || y >= f.imgh) return;
-    if (!rt_shard_needs(f, x, y)) return;
+    const bool mine = x < f.imgw && y < f.imgh && rt_shard_needs(f, x, y);
+    if (!packet && !mine) return;
 
     RtPixelCounters pc = {{0, 0, 0, 0, 0, 0, 0, 0, 0}, 0, 0, 0, 0};
-    RtGlobalScene<BRUTE, COUNT> acc(sc);
+    RtGlobalPacketScene<BRUTE, COUNT> acc(sc);
+    if (!BRUTE && packet) {
+        /* the patch's 32 primary rays walk the hierarchy as one packet (rt_packet_closest, trace_global.cuh) */
+        if (!__any_sync(0xffffffffu, mine)) return;
+        const vec3 o = v3(f.pos[0], f.pos[1], f.pos[2]);
+        const vec3 d = mine ? rt_primary_dir(f, x, y) : v3(0.0f, 0.0f, 1.0f);
+        RtHit best;
+        best.t = __int_as_float(0x7f800000);
+        best.tag = RT_MISS;
+        best.slot = 0;
+        if (mine)
+            for (int p = 0; p < sc.n_planes; p++) {
+                const float4 q0 = __ldg(sc.planes + 2 * p), q1 = __ldg(sc.planes + 2 * p + 1);
+                float t;
+                if (COUNT) pc.t.plane_tests++;
+                if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t)) rt_consider(best, t, __float_as_uint(q0.w), ~p);
+            }
+        rt_packet_closest<COUNT>(sc, mine, o, d, best, pc.t, s_wstack[warp], lane, err);
+        acc.primary = best;
+        acc.have_primary = true;
+        if (!mine) return;
+    }
 #ifdef RT_TIMEMAP
     unsigned long long tm_t0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_t0));
 #endif
-    image[y * f.imgw + x] = rt_trace_pixel<RtGlobalScene<BRUTE, COUNT>, COUNT>(acc, f, x, y, s_pending, RT_TRACE_THREADS,
-                                                                              threadIdx.x, hit_ids, pc);
+    image[y * f.imgw + x] = rt_trace_pixel<RtGlobalPacketScene<BRUTE, COUNT>, COUNT>(acc, f, x, y, s_pending, RT_TRACE_THREADS,
+                                                                                    threadIdx.x, hit_ids, pc);
 #ifdef RT_TIMEMAP
     if (hit_ids) {   /* debug variant: ns this pixel's thread took */
         unsigned long long tm_t1;
@@ -55,17 +77,17 @@ rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restric
 }
 
 extern "C" cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image,
-                                       int* hit_ids, RtCountersDev* counters, int brute, int count,
-                                       cudaStream_t stream) {
+                                       int* hit_ids, RtCountersDev* counters, unsigned int* err, int brute, int count,
+                                       int packet, cudaStream_t stream) {
     dim3 block(RT_TRACE_THREADS, 1, 1);
     dim3 grid((f->imgw + 31) / 32, (f->imgh + 7) / 8, 1);
     RT_LAUNCHED(1);
     if (brute) {
-        if (count) rt_trace_kernel<true, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters);
-        else       rt_trace_kernel<true, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters);
+        if (count) rt_trace_kernel<true, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        else       rt_trace_kernel<true, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
     } else {
-        if (count) rt_trace_kernel<false, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters);
-        else       rt_trace_kernel<false, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters);
+        if (count) rt_trace_kernel<false, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        else       rt_trace_kernel<false, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
     }
     return cudaGetLastError();
 }

@@ -17,10 +17,12 @@
  *     is no divergence and no per-lane stack traffic.  A lane may so see primitives its own traversal would have
  *     skipped; the exact leaf tests decide, and the (t, index) minimum over a superset of the primitives a ray can
  *     hit is the reference's minimum over all objects (kernel.cu:144-151);
- *   - the per-lane traversal (bounces; shadow rays of a light without a grid) keeps its stack in SHARED memory:
- *     RB_STACK_SMEM 32-bit entries per thread, deeper pushes continue in a local-memory array, and a push beyond
- *     both (a hierarchy deeper than the host-side check lets through, api.cu) raises the context's device error word
- *     (rt_get_device_errors) instead of dropping the subtree silently.
+ *   - the per-lane traversal (bounces; shadow rays of a light without a grid) can keep the first RB_STACK_SMEM
+ *     entries of its stack in SHARED memory (template SS; deeper pushes continue in a local-memory array).  Measured:
+ *     the 16 KB per CTA this takes out of the unified L1 cost more than the conflict-free stack accesses gain -- the
+ *     kernel lives on its 97 % L1 hit rate -- so the default keeps the whole stack in local memory (RT_OPT_BIG_STACK).
+ *     Either way a push beyond the stack (a hierarchy deeper than the host-side check lets through, api.cu) raises
+ *     the context's device error word (rt_get_device_errors) instead of dropping the subtree silently.
  */
 #include "trace_global.cuh"
 
@@ -29,17 +31,16 @@
 #ifndef RB_CTAS_PER_SM
 #define RB_CTAS_PER_SM 4
 #endif
-#define RB_STACK_SMEM 16                      /* per-thread stack entries in shared memory */
-#define RB_PACKET_STACK (RT_STACK_SIZE + 2)   /* per-warp stack of the packet traversal: one push per level at most */
+#define RB_STACK_SMEM 16                      /* per-thread stack entries in shared memory (SS = 0: none) */
 #define RB_CNT_PATCH 0                        /* tile_counter[]: next patch, finished warps (api.cu: d_tile_counter) */
 #define RB_CNT_DONE 1
 
 __device__ __forceinline__ void rb_griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 /* LBVH traversal of ONE ray with the short stack in shared memory.  `stk` = this thread's column (entry e at
- * stk[32 e]), entries beyond RB_STACK_SMEM go to `deep`.  ANY: first non-emissive hit with t < tmax
+ * stk[32 e]), entries beyond SS go to `deep`.  ANY: first non-emissive hit with t < tmax
  * (kernel.cu:188-193); else closest hit into `best`. */
-template <bool ANY, bool COUNT, bool ROBUST>
+template <bool ANY, bool COUNT, bool ROBUST, int SS>
 __device__ __forceinline__ bool rb_traverse_loop(const RtSceneDev& sc, const RtRayBox& rb, const vec3& o, const vec3& d,
                                                  RtHit& best, float tmax, RtLocalCounters& cnt, int* __restrict__ stk,
                                                  unsigned int* __restrict__ err) {
@@ -63,11 +64,11 @@ __device__ __forceinline__ bool rb_traverse_loop(const RtSceneDev& sc, const RtR
             int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
             if (h0 && h1) {
                 if (t1 < t0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                if (sp < RB_STACK_SMEM) {
+                if (sp < SS) {
                     stk[32 * sp] = c1;
                     sp++;
-                } else if (sp < RB_STACK_SMEM + RT_STACK_SIZE) {
-                    deep[sp - RB_STACK_SMEM] = c1;
+                } else if (sp < SS + RT_STACK_SIZE) {
+                    deep[sp - SS] = c1;
                     sp++;
                 } else {
                     atomicOr(err, 1u);           /* deeper than any hierarchy the host lets through: say so */
@@ -91,77 +92,23 @@ __device__ __forceinline__ bool rb_traverse_loop(const RtSceneDev& sc, const RtR
         }
         if (sp == 0) break;
         sp--;
-        node = sp < RB_STACK_SMEM ? stk[32 * sp] : deep[sp - RB_STACK_SMEM];
+        node = sp < SS ? stk[32 * sp] : deep[sp - SS];
     }
     return false;
 }
 
-template <bool ANY, bool COUNT>
+template <bool ANY, bool COUNT, int SS>
 __device__ __forceinline__ bool rb_traverse(const RtSceneDev& sc, const vec3& o, const vec3& d, RtHit& best, float tmax,
                                             RtLocalCounters& cnt, int* __restrict__ stk, unsigned int* __restrict__ err) {
     if (sc.root == RT_NODE_SENTINEL) return false;
     const RtRayBox rb = rt_ray_box(o, d);
-    if (rb.slack > RT_ROBUST_SLACK) return rb_traverse_loop<ANY, COUNT, true>(sc, rb, o, d, best, tmax, cnt, stk, err);
-    return rb_traverse_loop<ANY, COUNT, false>(sc, rb, o, d, best, tmax, cnt, stk, err);
-}
-
-/* Packet traversal: closest hits of the warp's 32 primary rays in one walk.  All 32 lanes call; `live` = this lane
- * has a ray.  `wstk` = the warp's stack in shared memory.  Every slab test is the per-axis-slack one
- * (rt_slab_robust): it is at least as tight as the common-slack test for every ray and needs no per-ray choice. */
-template <bool COUNT>
-__device__ __forceinline__ void rb_packet_closest(const RtSceneDev& sc, bool live, const vec3& o, const vec3& d, RtHit& best,
-                                                  RtLocalCounters& cnt, int* __restrict__ wstk, int lane,
-                                                  unsigned int* __restrict__ err) {
-    if (sc.root == RT_NODE_SENTINEL) return;
-    const RtRayBox rb = rt_ray_box(o, d);
-    const float4* __restrict__ nodes = sc.nodes;
-    int node = sc.root;                           /* warp-uniform from here on */
-    int sp = 0;
-    for (;;) {
-        if (node >= 0) {
-            const float4 n0 = __ldg(nodes + 4 * node);
-            const float4 n1 = __ldg(nodes + 4 * node + 1);
-            const float4 n2 = __ldg(nodes + 4 * node + 2);
-            const float4 n3 = __ldg(nodes + 4 * node + 3);
-            const float lim = fmaxf(best.t, 0.0f);
-            float t0, t1;
-            const bool h0 = live && rt_slab_robust(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0);
-            const bool h1 = live && rt_slab_robust(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1);
-            if (COUNT && live) cnt.node_tests += 2;
-            const unsigned int b0 = __ballot_sync(0xffffffffu, h0), b1 = __ballot_sync(0xffffffffu, h1);
-            const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-            if (b0 && b1) {
-                /* the child most rays reach first goes first (rays that meet only one child vote for it) */
-                const unsigned int first1 = __ballot_sync(0xffffffffu, h1 && (!h0 || t1 < t0));
-                const bool one_first = 2 * __popc(first1) > __popc(b0 | b1);
-                if (sp < RB_PACKET_STACK) {
-                    if (lane == 0) wstk[sp] = one_first ? c0 : c1;
-                    sp++;
-                } else if (lane == 0) {
-                    atomicOr(err, 1u);
-                }
-                node = one_first ? c1 : c0;
-                continue;
-            }
-            if (b0) { node = c0; continue; }
-            if (b1) { node = c1; continue; }
-        } else {
-            const int slot = ~node;
-            float t;
-            unsigned int tag;
-            if (live && rt_test_record<COUNT>(sc.prims + 3 * (size_t)slot, o, d, t, tag, cnt)) rt_consider(best, t, tag, slot);
-        }
-        if (sp == 0) break;
-        __syncwarp();                             /* lane 0's pushes are visible to everybody */
-        sp--;
-        node = wstk[sp];
-        __syncwarp();                             /* ... and read before the slot is pushed over */
-    }
+    if (rb.slack > RT_ROBUST_SLACK) return rb_traverse_loop<ANY, COUNT, true, SS>(sc, rb, o, d, best, tmax, cnt, stk, err);
+    return rb_traverse_loop<ANY, COUNT, false, SS>(sc, rb, o, d, best, tmax, cnt, stk, err);
 }
 
 /* scene accessor of the persistent tracer: RtGlobalScene's materials / normals / light-grid look-up; the closest hit
  * of the PRIMARY ray is handed in (packet traversal), everything else traverses with the shared-memory stack */
-template <bool COUNT>
+template <bool COUNT, int SS>
 struct RtBigScene {
     const RtSceneDev& sc;
     int* stk;                         /* this thread's stack column */
@@ -186,7 +133,7 @@ struct RtBigScene {
         best.tag = RT_MISS;
         best.slot = 0;
         planes_closest(o, d, best, cnt);
-        rb_traverse<false, COUNT>(sc, o, d, best, 0.0f, cnt, stk, err);
+        rb_traverse<false, COUNT, SS>(sc, o, d, best, 0.0f, cnt, stk, err);
         return best;
     }
     /* to_light = L - P (the vector the caller normalised into d), li = index of the light */
@@ -202,7 +149,7 @@ struct RtBigScene {
             if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t) && t < tmax) return true;
         }
         RtHit dummy;
-        return rb_traverse<true, COUNT>(sc, o, d, dummy, tmax, cnt, stk, err);
+        return rb_traverse<true, COUNT, SS>(sc, o, d, dummy, tmax, cnt, stk, err);
     }
     __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) { return rt_hit_normal<false>(sc, h, P); }
     __device__ __forceinline__ void material(unsigned int idx, float4& m0, float4& m1) {
@@ -211,14 +158,14 @@ struct RtBigScene {
     }
 };
 
-template <bool COUNT>
+template <bool COUNT, int SS>
 __global__ void __launch_bounds__(RB_THREADS, RB_CTAS_PER_SM)
 rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image, int* __restrict__ hit_ids,
                     RtCountersDev* __restrict__ counters, unsigned int* __restrict__ tile_counter,
                     unsigned int* __restrict__ err, int packet) {
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RB_THREADS];
-    __shared__ int s_stack[RB_WARPS][RB_STACK_SMEM][32];     /* per-lane stacks: entry e of lane l at [warp][e][l] */
-    __shared__ int s_wstack[RB_WARPS][RB_PACKET_STACK];       /* per-warp stack of the packet traversal */
+    __shared__ int s_stack[RB_WARPS][SS > 0 ? SS : 1][SS > 0 ? 32 : 1];   /* per-lane stacks: entry e of lane l at [warp][e][l] */
+    __shared__ int s_wstack[RB_WARPS][RT_PACKET_STACK];       /* per-warp stack of the packet traversal */
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     /* Work units.  The frame is cut into CHUNKS of 8x4 patches (64x16 pixels); a CTA reserves one chunk at a time from
      * the global counter and its eight warps take the chunk's patches one by one from a counter in shared memory,
@@ -233,7 +180,7 @@ rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __res
     if (tid == 0) s_pool = 32u;
     __syncthreads();
 
-    RtBigScene<COUNT> acc(sc, &s_stack[warp][0][lane], err);
+    RtBigScene<COUNT, SS> acc(sc, &s_stack[warp][0][SS > 0 ? lane : 0], err);
     RtPixelCounters pc = {{0, 0, 0, 0, 0, 0, 0, 0, 0}, 0, 0, 0, 0};
     unsigned int n_pixels = 0;
 
@@ -272,12 +219,12 @@ rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __res
                 best.tag = RT_MISS;
                 best.slot = 0;
                 if (mine) acc.planes_closest(o, d, best, pc.t);
-                rb_packet_closest<COUNT>(sc, mine, o, d, best, pc.t, s_wstack[warp], lane, err);
+                rt_packet_closest<COUNT>(sc, mine, o, d, best, pc.t, s_wstack[warp], lane, err);
                 acc.primary = best;
                 acc.have_primary = true;
             }
             if (mine) {
-                image[y * f.imgw + x] = rt_trace_pixel<RtBigScene<COUNT>, COUNT>(acc, f, x, y, s_pending, RB_THREADS, tid,
+                image[y * f.imgw + x] = rt_trace_pixel<RtBigScene<COUNT, SS>, COUNT>(acc, f, x, y, s_pending, RB_THREADS, tid,
                                                                                hit_ids, pc);
                 n_pixels++;
             }
@@ -298,13 +245,15 @@ rt_trace_big_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __res
 
 extern "C" cudaError_t rt_launch_trace_big(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                                            RtCountersDev* counters, unsigned int* tile_counter, unsigned int* err,
-                                           int count, int packet, int n_sm, cudaStream_t stream) {
+                                           int count, int packet, int smem_stack, int n_sm, cudaStream_t stream) {
     const int chunks = ((f->imgw + 63) / 64) * ((f->imgh + 15) / 16);     /* a CTA works through whole chunks */
     int grid = n_sm * RB_CTAS_PER_SM;
     if (grid > chunks) grid = chunks;
     if (grid < 1) grid = 1;
     RT_LAUNCHED(1);
-    if (count) rt_trace_big_kernel<true><<<grid, RB_THREADS, 0, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, err, packet);
-    else       rt_trace_big_kernel<false><<<grid, RB_THREADS, 0, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, err, packet);
+#define RB_LAUNCH(C, S) rt_trace_big_kernel<C, S><<<grid, RB_THREADS, 0, stream>>>(*sc, *f, image, hit_ids, counters, tile_counter, err, packet)
+    if (smem_stack) { if (count) RB_LAUNCH(true, RB_STACK_SMEM); else RB_LAUNCH(false, RB_STACK_SMEM); }
+    else            { if (count) RB_LAUNCH(true, 0); else RB_LAUNCH(false, 0); }
+#undef RB_LAUNCH
     return cudaGetLastError();
 }

@@ -91,4 +91,72 @@ struct RtGlobalScene {
     }
 };
 
+#define RT_PACKET_STACK (RT_STACK_SIZE + 2)   /* per-warp stack of the packet traversal: one push per level at most */
+
+/* Packet traversal: closest hits of the warp's 32 primary rays in one walk.  All 32 lanes call; `live` = this lane
+ * has a ray.  `wstk` = the warp's stack in shared memory.  Every slab test is the per-axis-slack one
+ * (rt_slab_robust): it is at least as tight as the common-slack test for every ray and needs no per-ray choice. */
+template <bool COUNT>
+__device__ __forceinline__ void rt_packet_closest(const RtSceneDev& sc, bool live, const vec3& o, const vec3& d, RtHit& best,
+                                                  RtLocalCounters& cnt, int* __restrict__ wstk, int lane,
+                                                  unsigned int* __restrict__ err) {
+    if (sc.root == RT_NODE_SENTINEL) return;
+    const RtRayBox rb = rt_ray_box(o, d);
+    const float4* __restrict__ nodes = sc.nodes;
+    int node = sc.root;                           /* warp-uniform from here on */
+    int sp = 0;
+    for (;;) {
+        if (node >= 0) {
+            const float4 n0 = __ldg(nodes + 4 * node);
+            const float4 n1 = __ldg(nodes + 4 * node + 1);
+            const float4 n2 = __ldg(nodes + 4 * node + 2);
+            const float4 n3 = __ldg(nodes + 4 * node + 3);
+            const float lim = fmaxf(best.t, 0.0f);
+            float t0, t1;
+            const bool h0 = live && rt_slab_robust(rb, n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, lim, t0);
+            const bool h1 = live && rt_slab_robust(rb, n1.z, n1.w, n2.x, n2.y, n2.z, n2.w, lim, t1);
+            if (COUNT && live) cnt.node_tests += 2;
+            const unsigned int b0 = __ballot_sync(0xffffffffu, h0), b1 = __ballot_sync(0xffffffffu, h1);
+            const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+            if (b0 && b1) {
+                /* the child most rays reach first goes first (rays that meet only one child vote for it) */
+                const unsigned int first1 = __ballot_sync(0xffffffffu, h1 && (!h0 || t1 < t0));
+                const bool one_first = 2 * __popc(first1) > __popc(b0 | b1);
+                if (sp < RT_PACKET_STACK) {
+                    if (lane == 0) wstk[sp] = one_first ? c0 : c1;
+                    sp++;
+                } else if (lane == 0) {
+                    atomicOr(err, 1u);
+                }
+                node = one_first ? c1 : c0;
+                continue;
+            }
+            if (b0) { node = c0; continue; }
+            if (b1) { node = c1; continue; }
+        } else {
+            const int slot = ~node;
+            float t;
+            unsigned int tag;
+            if (live && rt_test_record<COUNT>(sc.prims + 3 * (size_t)slot, o, d, t, tag, cnt)) rt_consider(best, t, tag, slot);
+        }
+        if (sp == 0) break;
+        __syncwarp();                             /* lane 0's pushes are visible to everybody */
+        sp--;
+        node = wstk[sp];
+        __syncwarp();                             /* ... and read before the slot is pushed over */
+    }
+}
+
+/* RtGlobalScene whose primary-ray hit is handed in (packet traversal) */
+template <bool BRUTE, bool COUNT>
+struct RtGlobalPacketScene : RtGlobalScene<BRUTE, COUNT> {
+    RtHit primary;
+    bool have_primary;
+    __device__ __forceinline__ RtGlobalPacketScene(const RtSceneDev& s) : RtGlobalScene<BRUTE, COUNT>(s), have_primary(false) {}
+    __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, bool off, RtLocalCounters& cnt) {
+        if (depth == 0 && have_primary) return primary;
+        return RtGlobalScene<BRUTE, COUNT>::closest(o, d, depth, off, cnt);
+    }
+};
+
 #endif

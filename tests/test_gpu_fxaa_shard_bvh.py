@@ -337,10 +337,10 @@ def test_light_grid_of_big_scenes_changes_tested_primitives_only():
 
 
 def test_persistent_packet_tracer_equals_plain_tracer():
-    """The tracer of big scenes (trace_big.cu: persistent warps, the 32 primary rays of an 8x4 patch walking the LBVH as
-    one packet, per-lane stacks in shared memory; RT_OPT_TRACE_IMPL 0 for scenes that do not fit shared memory, 3 =
-    forced) against the plain one-thread-per-pixel tracer (RT_OPT_TRACE_IMPL 1): pixels and hit ids identical -- the
-    terrain from several poses (incl. grazing rays and a camera inside it), packets off (RT_OPT_PACKET 1), odd frame
+    """The persistent tracer of big scenes (trace_big.cu: warps pulling 8x4 patches, the 32 primary rays of a patch
+    walking the LBVH as one packet, per-lane stacks optionally in shared memory; RT_OPT_TRACE_IMPL 3) against the plain one-thread-per-pixel tracer (RT_OPT_TRACE_IMPL 1): pixels and hit ids identical -- the
+    terrain from several poses (incl. grazing rays and a camera inside it), packets off (RT_OPT_PACKET 1), the first
+    stack entries in shared memory (RT_OPT_BIG_STACK 1), packets inside the plain kernel (RT_OPT_TRACE_IMPL 4), odd frame
     sizes, screen-tile shards of several tile sizes, the built-in scene (spheres, huge triangles, mirror chains),
     degenerate scenes.  The device error word (traversal stack ran out) stays clear."""
     r = gu.renderer()
@@ -350,9 +350,10 @@ def test_persistent_packet_tracer_equals_plain_tracer():
     def frames(f, o, lights, shard=None):
         outs = []
         r.set_scene(o, lights)
-        for impl, packet in ((1, 0), (3, 0), (3, 1)):
+        for impl, packet, sstack in ((1, 0, 0), (3, 0, 0), (3, 1, 0), (3, 0, 1), (3, 1, 1), (4, 0, 0)):
             r.set_option(_lib.RT_OPT_TRACE_IMPL, impl)
             r.set_option(_lib.RT_OPT_PACKET, packet)
+            r.set_option(_lib.RT_OPT_BIG_STACK, sstack)
             if shard is None:
                 outs.append(r.render_to_host(f, want_ids=True))
             else:
@@ -360,7 +361,8 @@ def test_persistent_packet_tracer_equals_plain_tracer():
                 outs.append((img, img))
         r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
         r.set_option(_lib.RT_OPT_PACKET, 0)
-        for k in (1, 2):
+        r.set_option(_lib.RT_OPT_BIG_STACK, 0)
+        for k in range(1, len(outs)):
             assert (outs[0][1] == outs[k][1]).all(), (k, int((outs[0][1] != outs[k][1]).sum()))
             assert (outs[0][0] == outs[k][0]).all(), (k, int((outs[0][0] != outs[k][0]).sum()))
         return outs[0]
@@ -375,7 +377,7 @@ def test_persistent_packet_tracer_equals_plain_tracer():
             s.set_antialiasing(alias)
             img, ids = frames(s.frame(w, h), objs, s.lights)
         assert k != 0 or (ids >= 1).mean() > 0.5
-    # the auto choice for a big scene IS the packet tracer
+    # the auto choice for a big scene (the plain kernel) and the persistent tracer agree
     s.set_pose(*poses[0])
     s.set_antialiasing(False)
     f = s.frame(480, 270)
