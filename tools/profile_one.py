@@ -8,7 +8,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 import raytracing_cuda_b200 as rt  # noqa: E402
-from raytracing_cuda_b200 import _lib  # noqa: E402
+from raytracing_cuda_b200 import _lib, configs  # noqa: E402
 
 a = sys.argv[1:]
 view = int(a[0]) if len(a) > 0 else 5
@@ -18,7 +18,7 @@ h = int(a[3]) if len(a) > 3 else 1080
 frames = int(a[4]) if len(a) > 4 else 6
 impl = int(a[5]) if len(a) > 5 else 0
 r = rt.Renderer(0)
-r.set_sky(rt.synthetic_sky(8192, 4096))
+r.set_sky(configs.sky_maps(os.path.join(ROOT, "oracle", "_ref", "backgrounds"))[0])     # the bench's sky maps
 s = rt.Scene()
 f = s.configure(view=view, hours=hours, imgw=w, imgh=h, alias=True)
 r.set_scene(s.objects, s.lights)
