@@ -26,6 +26,7 @@ RT_OPT_FETCH = 14
 RT_OPT_BIG_STACK = 15
 RT_PEER_HANDLE_BYTES = 64
 RT_MAX_SLOTS = 8
+RT_SORT_STATIC_MAX = 1 << 20
 RT_CNT_COUNT = 16
 COUNTER_NAMES = ("rays_primary", "rays_shadow", "rays_mirror", "node_tests", "tri_tests", "sphere_tests",
                  "plane_tests", "sky_lookups", "shadow_skipped", "tri_exit_u", "tri_exit_v", "tri_full", "tri_accept",
@@ -82,6 +83,7 @@ SIGNATURES = {
     "rt_bvh_info": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "rt_bvh_download": (C.c_int, [_P, _P, _P, _P]),
     "rt_sort_pairs": (C.c_int, [_P, _P, _P, C.c_int]),
+    "rt_sort_pairs_static": (C.c_int, [_P, _P, _P, C.c_int]),
     "rtb_scene_create": (_P, []),
     "rtb_scene_destroy": (None, [_P]),
     "rtb_scene_objects": (C.POINTER(Object), [_P, C.POINTER(C.c_int)]),

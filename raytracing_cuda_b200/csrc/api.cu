@@ -31,6 +31,8 @@ int rt_build_by_value(const RtBuildBuffers* b, int mode);
 cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* vals, unsigned int* tmp_keys, unsigned int* tmp_vals,
                                 unsigned int* hist, int n, int force_radix, cudaStream_t stream);
 int rt_radix_hist_entries(int n);
+cudaError_t rt_radix_sort_pairs_static(unsigned int* keys, unsigned int* vals, int n, int device, cudaStream_t stream,
+                                       const char** why);
 cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f, unsigned int* image, int* hit_ids,
                             RtCountersDev* counters, unsigned int* err, int brute, int count, int packet,
                             cudaStream_t stream);
@@ -1080,6 +1082,27 @@ int rt_sort_pairs(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_de
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(tk); cudaFree(tv); cudaFree(hist);
     RT_CHECK(ctx, e);
+    return RT_OK;
+}
+
+/* rt_sort_pairs without any allocation: scratch in a file-scope device array (bvh_build.cu).  No cudaMalloc, no
+ * cudaFree, no synchronisation: asynchronous on the context's stream. */
+int rt_sort_pairs_static(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_dev, int n) {
+    if (!ctx || n < 0 || (n > 0 && (!keys_dev || !vals_dev))) return RT_ERR_ARG;
+    if (n > RT_SORT_STATIC_MAX) {
+        char msg[160];
+        snprintf(msg, sizeof(msg), "rt_sort_pairs_static: n = %d exceeds the static scratch capacity of %d keys "
+                 "(use rt_sort_pairs)", n, RT_SORT_STATIC_MAX);
+        return fail(ctx, RT_ERR_ARG, msg);
+    }
+    if (n <= 1) return RT_OK;
+    RT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const char* why = "";
+    const cudaError_t e = rt_radix_sort_pairs_static(keys_dev, vals_dev, n, ctx->device, ctx->stream, &why);
+    if (e != cudaSuccess) {
+        ctx->err = std::string("rt_sort_pairs_static: ") + why + ": " + cudaGetErrorString(e);
+        return RT_ERR_CUDA;
+    }
     return RT_OK;
 }
 

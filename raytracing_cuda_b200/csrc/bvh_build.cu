@@ -383,6 +383,49 @@ extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* val
 
 extern "C" int rt_radix_hist_entries(int n) { return 256 * ((n + RS_TILE - 1) / RS_TILE) + 256; }   /* rows + bin totals */
 
+/* ---- the same sort with its scratch in a file-scope device array: allocates nothing (rt_sort_pairs_static, api.cu).
+ * Layout in uints: [tmp keys, RT_SORT_STATIC_MAX][tmp values, RT_SORT_STATIC_MAX][histogram rows + bin totals].
+ * 8.25 MiB that every GPU which loads the library holds until the process exits.  Nothing in it has to start at
+ * zero: each of the four passes writes every histogram row, every bin total and all n temporary keys / values before
+ * it reads them, so the previous call's contents are never seen and no clear is needed.  All calls share the array:
+ * two sorts that overlap on one GPU (different streams, different contexts, different threads) race on it. */
+#define RS_STATIC_HIST (256 * ((RT_SORT_STATIC_MAX + RS_TILE - 1) / RS_TILE) + 256)
+static __device__ __align__(256) unsigned int g_sort_scratch[2 * RT_SORT_STATIC_MAX + RS_STATIC_HIST];
+
+/* `g_sort_scratch` in HOST code is a host-side stand-in for the symbol, not a device address: the address a kernel
+ * can use comes from cudaGetSymbolAddress, looked up once per device with that device current. */
+#define RS_STATIC_MAX_DEVICES 64
+static unsigned int* g_sort_scratch_dev[RS_STATIC_MAX_DEVICES];
+
+/* device = the CURRENT device (the caller has made it so).  *why gets a static message on failure. */
+extern "C" cudaError_t rt_radix_sort_pairs_static(unsigned int* keys, unsigned int* vals, int n, int device,
+                                                  cudaStream_t stream, const char** why) {
+    *why = "";
+    if (n <= 1) return cudaSuccess;
+    if (n > RT_SORT_STATIC_MAX) {
+        *why = "n exceeds RT_SORT_STATIC_MAX, the capacity of the static scratch array";
+        return cudaErrorInvalidValue;
+    }
+    if (device < 0 || device >= RS_STATIC_MAX_DEVICES) {
+        *why = "device index beyond the per-device address table";
+        return cudaErrorInvalidDevice;
+    }
+    if (!g_sort_scratch_dev[device]) {
+        unsigned int* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_sort_scratch);
+        if (e != cudaSuccess || !p) {
+            *why = "cudaGetSymbolAddress(g_sort_scratch) failed";
+            return e != cudaSuccess ? e : cudaErrorInvalidSymbol;
+        }
+        g_sort_scratch_dev[device] = p;
+    }
+    unsigned int* const base = g_sort_scratch_dev[device];
+    const cudaError_t e = rt_radix_sort_pairs(keys, vals, base, base + RT_SORT_STATIC_MAX, base + 2 * RT_SORT_STATIC_MAX, n,
+                                              1 /* always the multi-pass radix sort: the variant that uses scratch */, stream);
+    if (e != cudaSuccess) *why = "sort kernel launch failed";
+    return e;
+}
+
 /* ------------------------------------------------------------------ hierarchy */
 
 /* common-prefix length of sorted keys i and j; index breaks ties between equal codes */
