@@ -78,9 +78,8 @@ enum {
     RT_OPT_LIGHT_BINS_REUSE = 11, /* light bins of the shared-memory tracer: 0 = rebuilt only when the scene or the lights changed since they were built (default; they do not depend on the camera), 1 = rebuilt by every frame's pre-pass.  Identical pixels */
     RT_OPT_COMPACTION = 12, /* ray compaction in the shared-memory tracer: 0 = every lane follows its own pixel's chain to the end (default), 1 = rays of the second and later generations that have to traverse the hierarchy are parked in a per-CTA shared-memory queue (ballot + popc slot assignment) and traced 32 at a time by full warps.  Measured SLOWER on every BASELINE view (full warps, but rays of unrelated patches: the traversal loses the coherence an 8x4 patch has), hence opt-in.  Scheduling only: identical pixels */
     RT_OPT_PACKET = 13, /* persistent tracer of big scenes: 0 = the 32 primary rays of an 8x4 patch walk the hierarchy as ONE packet (warp-uniform node, one stack per warp, broadcast node loads; default), 1 = every lane traverses for itself.  Identical pixels */
-    RT_OPT_FETCH = 14, /* work fetch of the shared-memory tracer: 0 = a warp that has just finished a cheap patch reserves up to 4 units with one atomic (default), 1 = one unit per atomic.  Scheduling only: identical pixels */
-    RT_OPT_BIG_STACK = 15, /* persistent tracer of big scenes, per-lane traversal stack: 0 = local memory (default), 1 = first 16 entries in shared memory.  Identical pixels */
-    RT_OPT_N = 16
+    RT_OPT_BIG_STACK = 14, /* persistent tracer of big scenes, per-lane traversal stack: 0 = local memory (default), 1 = first 16 entries in shared memory.  Identical pixels */
+    RT_OPT_N = 15
 };
 
 /* One frame's uniforms: what launchKernel receives by value / as small host arrays. */

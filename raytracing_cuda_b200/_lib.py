@@ -22,8 +22,7 @@ RT_OPT_MIRROR_BINS = 10
 RT_OPT_LIGHT_BINS_REUSE = 11
 RT_OPT_COMPACTION = 12
 RT_OPT_PACKET = 13
-RT_OPT_FETCH = 14
-RT_OPT_BIG_STACK = 15
+RT_OPT_BIG_STACK = 14
 RT_PEER_HANDLE_BYTES = 64
 RT_MAX_SLOTS = 8
 RT_SORT_STATIC_MAX = 1 << 20

@@ -43,10 +43,12 @@ cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrameDev* f, uns
                                   RtCountersDev* counters, unsigned int* tile_counter, unsigned short* tile_lists,
                                   int count, int force_linear, int n_sm, const unsigned int* order_r,
                                   unsigned int* order_w, int after_own_post, uint4* lgrid, int build_lgrid,
-                                  int mirror_bins, int compact, int fetch_max, cudaStream_t stream);
+                                  int mirror_bins, int compact, cudaStream_t stream);
 size_t rt_trace_small_order_bytes(int imgw, int imgh);
 size_t rt_trace_small_patches(int imgw, int imgh);
 size_t rt_trace_small_list_bytes(int imgw, int imgh);
+cudaError_t rt_lgb_finish(const unsigned int* total, const unsigned int* fail, unsigned int cap, unsigned int* state,
+                          cudaStream_t stream);
 size_t rt_lgb_bins(void);
 size_t rt_lgb_sums(void);
 cudaError_t rt_lgb_count(const RtSceneDev* sc, const float* light_pos, unsigned int* counts, unsigned int* offsets,
@@ -144,6 +146,10 @@ struct rt_context {
     unsigned int* d_lgb_offsets[RT_LGB_LIGHTS] = {nullptr, nullptr};
     unsigned int* d_lgb_entries[RT_LGB_LIGHTS] = {nullptr, nullptr};
     size_t cap_lgb_entries[RT_LGB_LIGHTS] = {0, 0};
+    unsigned int* d_lgb_state = nullptr;     /* 4 uints per light: the build's own verdict (rt_lgb_finish_kernel) */
+    unsigned int* h_lgb_state = nullptr;     /* page-locked copy of it, read back asynchronously */
+    cudaEvent_t lgb_read[RT_LGB_LIGHTS] = {nullptr, nullptr};
+    bool lgb_read_pending[RT_LGB_LIGHTS] = {false, false};
     bool lgb_stale = true;
     bool lgb_waited = false;                 /* a frame has been rendered since the grid went stale */
     size_t cap_tile_lists = 0;
@@ -298,8 +304,10 @@ int rt_destroy(rt_context* ctx) {
     void* ptrs[] = {ctx->d_objs, ctx->d_plane_idx, b.mats, b.recs, b.planes, b.bvh_src, b.prim_lo, b.prim_hi, b.bounds,
                     b.keys, b.vals, b.tmp_keys, b.tmp_vals, b.hist, b.children, b.node_parent, b.leaf_parent, b.node_other, b.flags, b.node_aux,
                     b.nodes, b.prims, b.depth, ctx->d_base, ctx->d_stage_out, ctx->d_stage_ids, ctx->d_counters, ctx->d_tile_counter, ctx->d_tile_lists, ctx->d_order, ctx->d_lgrid, ctx->d_lgb_counts, ctx->d_lgb_sums, ctx->d_lgb_fail, ctx->d_lgb_offsets[0],
-                    ctx->d_lgb_offsets[1], ctx->d_lgb_entries[0], ctx->d_lgb_entries[1]};
+                    ctx->d_lgb_offsets[1], ctx->d_lgb_entries[0], ctx->d_lgb_entries[1], ctx->d_lgb_state};
     for (void* p : ptrs) if (p) cudaFree(p);
+    if (ctx->h_lgb_state) cudaFreeHost(ctx->h_lgb_state);
+    for (int i = 0; i < RT_LGB_LIGHTS; i++) if (ctx->lgb_read[i]) cudaEventDestroy(ctx->lgb_read[i]);
     for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     for (RtSlot& sl : ctx->slots) {
         if (sl.dev) cudaFree(sl.dev);
@@ -560,9 +568,12 @@ static int fill_frame(rt_context* ctx, const rt_frame* fr, const rt_shard* sh, R
     return RT_OK;
 }
 
-/* Light grid of a big scene (light_grid.cu): per light count pass + scan, 8-byte read-back of (total, fail) -- the
- * grid is rebuilt only when the scene or the lights changed, next to an LBVH build that already synchronises --
- * then the fill pass.  A light whose lists would not fit the budget keeps traversing the hierarchy. */
+/* Light grid of a big scene (light_grid.cu): per light count pass + scan + fill pass.  No host synchronisation once a
+ * light's entry buffer exists: the fill runs with the buffer's capacity, a one-thread kernel leaves the verdict
+ * (complete / overflowed) on the device where the tracer reads it, and the host learns of it through an asynchronous
+ * copy it looks at when the next frame is rendered (lgb_poll) -- an overflowed light traverses meanwhile and gets a
+ * bigger buffer then.  Only the first build of a light reads the entry count back: it has to size an allocation, and
+ * cudaMalloc synchronises anyway. */
 static int build_light_grid(rt_context* ctx) {
     for (int i = 0; i < RT_LGB_LIGHTS; i++) ctx->scene.lg_offsets[i] = ctx->scene.lg_entries[i] = nullptr;
     ctx->lgb_stale = false;
@@ -573,7 +584,12 @@ static int build_light_grid(rt_context* ctx) {
         RT_CHECK(ctx, regrow(&ctx->d_lgb_counts, bins));
         RT_CHECK(ctx, regrow(&ctx->d_lgb_sums, rt_lgb_sums()));
         RT_CHECK(ctx, regrow(&ctx->d_lgb_fail, (size_t)1));
+        RT_CHECK(ctx, regrow(&ctx->d_lgb_state, (size_t)4 * RT_LGB_LIGHTS));
+        RT_CHECK(ctx, cudaMemsetAsync(ctx->d_lgb_state, 0, sizeof(unsigned int) * 4 * RT_LGB_LIGHTS, ctx->stream));
+        RT_CHECK(ctx, cudaHostAlloc((void**)&ctx->h_lgb_state, sizeof(unsigned int) * 4 * RT_LGB_LIGHTS, cudaHostAllocDefault));
+        for (int i = 0; i < RT_LGB_LIGHTS; i++) RT_CHECK(ctx, cudaEventCreateWithFlags(&ctx->lgb_read[i], cudaEventDisableTiming));
     }
+    ctx->scene.lg_state = ctx->d_lgb_state;
     const size_t budget = (size_t)64 << 20;          /* entries per light: 256 MB */
     const int lit = ctx->n_lights < RT_LGB_LIGHTS ? ctx->n_lights : RT_LGB_LIGHTS;
     for (int li = 0; li < lit; li++) {
@@ -581,20 +597,45 @@ static int build_light_grid(rt_context* ctx) {
         const float lp[3] = {ctx->lights[li].pos.x, ctx->lights[li].pos.y, ctx->lights[li].pos.z};
         RT_CHECK(ctx, rt_lgb_count(&ctx->scene, lp, ctx->d_lgb_counts, ctx->d_lgb_offsets[li], ctx->d_lgb_sums,
                                    ctx->d_lgb_fail, ctx->stream));
-        unsigned int total = 0, failed = 0;
-        RT_CHECK(ctx, cudaMemcpyAsync(&total, ctx->d_lgb_offsets[li] + bins, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
-        RT_CHECK(ctx, cudaMemcpyAsync(&failed, ctx->d_lgb_fail, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
-        RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-        if (failed || (size_t)total > budget) continue;
-        if ((size_t)total > ctx->cap_lgb_entries[li] || !ctx->d_lgb_entries[li]) {
-            const size_t c = (size_t)total + (size_t)total / 8 + 1024;
+        if (!ctx->d_lgb_entries[li]) {
+            unsigned int total = 0, failed = 0;
+            RT_CHECK(ctx, cudaMemcpyAsync(&total, ctx->d_lgb_offsets[li] + bins, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+            RT_CHECK(ctx, cudaMemcpyAsync(&failed, ctx->d_lgb_fail, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+            RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+            if (failed || (size_t)total > budget) continue;          /* this light keeps traversing */
+            size_t c = (size_t)total + (size_t)total / 4 + 1024;     /* head-room for lights that move */
+            if (c > budget) c = budget;
             RT_CHECK(ctx, regrow(&ctx->d_lgb_entries[li], c));
             ctx->cap_lgb_entries[li] = c;
         }
         RT_CHECK(ctx, rt_lgb_fill(&ctx->scene, lp, ctx->d_lgb_counts, ctx->d_lgb_offsets[li], ctx->d_lgb_entries[li],
                                   (unsigned int)ctx->cap_lgb_entries[li], ctx->d_lgb_fail, ctx->stream));
+        RT_CHECK(ctx, rt_lgb_finish(ctx->d_lgb_offsets[li] + bins, ctx->d_lgb_fail, (unsigned int)ctx->cap_lgb_entries[li],
+                                    ctx->d_lgb_state + 4 * li, ctx->stream));
+        RT_CHECK(ctx, cudaMemcpyAsync(ctx->h_lgb_state + 4 * li, ctx->d_lgb_state + 4 * li, sizeof(unsigned int) * 4,
+                                      cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CHECK(ctx, cudaEventRecord(ctx->lgb_read[li], ctx->stream));
+        ctx->lgb_read_pending[li] = true;
         ctx->scene.lg_offsets[li] = ctx->d_lgb_offsets[li];
         ctx->scene.lg_entries[li] = ctx->d_lgb_entries[li];
+    }
+    return RT_OK;
+}
+
+/* Has a build's verdict arrived, and did a light's lists outgrow its buffer?  Then drop the buffer (after the frames
+ * that may still read it) and have the next frame build the grid again, sized afresh.  Never waits for a verdict. */
+static int lgb_poll(rt_context* ctx) {
+    for (int li = 0; li < RT_LGB_LIGHTS; li++) {
+        if (!ctx->lgb_read_pending[li] || cudaEventQuery(ctx->lgb_read[li]) != cudaSuccess) continue;
+        ctx->lgb_read_pending[li] = false;
+        const unsigned int* st = ctx->h_lgb_state + 4 * li;
+        if (st[0] == 0u && st[2] == 0u && (size_t)st[1] > ctx->cap_lgb_entries[li]) {
+            RT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+            RT_CHECK(ctx, regrow(&ctx->d_lgb_entries[li], (size_t)0));
+            ctx->cap_lgb_entries[li] = 0;
+            ctx->lgb_stale = true;
+            ctx->lgb_waited = true;
+        }
     }
     return RT_OK;
 }
@@ -677,8 +718,7 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
                                             ctx->opt[RT_OPT_TRACE_IMPL] == 2, ctx->n_sm, ord_r, ord_w,
                                             ctx->scene_settled ? 1 : 0, use_lgrid ? ctx->d_lgrid : (uint4*)nullptr,
                                             build_lgrid ? 1 : 0, ctx->opt[RT_OPT_MIRROR_BINS] == 0,
-                                            ctx->opt[RT_OPT_COMPACTION] != 0, ctx->opt[RT_OPT_FETCH] == 0 ? 4 : 1,
-                                            ctx->stream));
+                                            ctx->opt[RT_OPT_COMPACTION] != 0, ctx->stream));
         if (use_lgrid) ctx->lgrid_valid = true;
     }
     else {
@@ -687,6 +727,10 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
          * frame never pay for it and keep traversing. */
         const int sb = ctx->opt[RT_OPT_SHADOW_BINS];
         bool grid = sb != 1 && ctx->opt[RT_OPT_TRAVERSAL] != 1;
+        if (grid) {
+            const int prc = lgb_poll(ctx);
+            if (prc != RT_OK) return prc;
+        }
         if (grid && ctx->lgb_stale) {
             if (sb == 2 || ctx->lgb_waited) {
                 const int rc = build_light_grid(ctx);

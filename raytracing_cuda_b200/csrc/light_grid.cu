@@ -178,3 +178,21 @@ extern "C" cudaError_t rt_lgb_fill(const RtSceneDev* sc, const float* light_pos,
                                                             offsets, entries, cap, fail);
     return cudaGetLastError();
 }
+
+/* Verdict of one light's build, left ON THE DEVICE so that the host need not wait for it: state[0] = 1 when no
+ * primitive overflowed its bin budget and all `total` entries fitted the `cap` the fill pass ran with (only then may
+ * the tracer use this light's lists, rt_light_grid_occluded), state[1] = total, state[2] = fail. */
+__global__ void rt_lgb_finish_kernel(const unsigned int* __restrict__ total, const unsigned int* __restrict__ fail,
+                                     unsigned int cap, unsigned int* __restrict__ state) {
+    const unsigned int t = *total, f = *fail;
+    state[1] = t;
+    state[2] = f;
+    state[0] = (f == 0u && t <= cap) ? 1u : 0u;
+}
+
+extern "C" cudaError_t rt_lgb_finish(const unsigned int* total, const unsigned int* fail, unsigned int cap,
+                                     unsigned int* state, cudaStream_t stream) {
+    RT_LAUNCHED(1);
+    rt_lgb_finish_kernel<<<1, 1, 0, stream>>>(total, fail, cap, state);
+    return cudaGetLastError();
+}

@@ -101,6 +101,9 @@ struct RtSceneDev {
      * of the possible occluders per direction bin); NULL: that light's shadow rays traverse the hierarchy */
     const unsigned int* lg_offsets[RT_LGB_LIGHTS];
     const unsigned int* lg_entries[RT_LGB_LIGHTS];
+    /* 4 uints per light, written by the build itself (rt_lgb_finish_kernel): [0] = 1 when the light's lists are
+     * complete and may be used, else its shadow rays traverse; [1] entries, [2] overflow flag */
+    const unsigned int* lg_state;
 };
 
 struct RtLightDev {

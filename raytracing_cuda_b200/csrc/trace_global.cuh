@@ -17,7 +17,7 @@ __device__ __forceinline__ int rt_light_grid_occluded(const RtSceneDev& sc, cons
     /* static indices: a dynamic one would copy the kernel parameter block to local memory */
     static_assert(RT_LGB_LIGHTS == 2, "select below");
     const unsigned int* __restrict__ lg_off = li == 0 ? sc.lg_offsets[0] : (li == 1 ? sc.lg_offsets[1] : nullptr);
-    if (!lg_off) return -1;
+    if (!lg_off || __ldg(sc.lg_state + 4 * li) == 0u) return -1;     /* no grid, or its build overflowed */
     const float ax = fabsf(to_light.x), ay = fabsf(to_light.y), az = fabsf(to_light.z);
     const bool X = ax >= ay && ax >= az, Y = !X && ay >= az;
     const float m = X ? ax : (Y ? ay : az);

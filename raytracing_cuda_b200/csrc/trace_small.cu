@@ -614,7 +614,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
                       int tiles_x, unsigned int n_tiles_all, int bins_x,
                       const unsigned int* __restrict__ work_list, int force_linear,
                       const unsigned int* order_r, unsigned int* order_w, const uint4* __restrict__ lgrid,
-                      const unsigned short* __restrict__ mirror_lists, int fetch_max) {
+                      const unsigned short* __restrict__ mirror_lists) {
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
@@ -713,7 +713,6 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
 #endif
     if constexpr (!COMPACT) {
         /* every lane follows its own pixel's chain of rays to the end (the default: see RT_OPT_COMPACTION) */
-        unsigned int u_end = u0 + 1u;                 /* this warp has reserved the units [u0, u_end) */
         while (u0 < n_fetch) {
             unsigned int q = 0;                       /* patch id = 4 * tile + patch */
             if (by_cost) {
@@ -762,29 +761,20 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl_t1));
             tl_units++;
     #endif
-            /* Next unit.  One same-address global atomic per patch was 10 % of the kernel's stall samples (64,800 per
-             * 1080p frame, each followed by a dependent shuffle); a warp that has just finished a CHEAP patch (sky:
-             * ~1 us) therefore reserves several units with one atomic -- 4 after a patch under 4096 cycles, 2 under
-             * 8192 -- and walks them.  Cheap patches come in runs (the order history sorts by cost, the bottom-up
-             * walk ends in the sky), so the reservation of a warp stays a few microseconds of work and no warp sits
-             * on units behind a long patch (which reserving ahead unconditionally did: +7 %). */
-            const unsigned int cyc = (unsigned int)clock() - unit_t0;
-            if (lane == 0 && order_w) {              /* file the patch under its cost class for the next frame */
-                const unsigned int k = cyc >> 10;
-                const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
-                const unsigned int at = atomicAdd(order_w + cls, 1u);
-                order_w[RS_ORDER_HEAD + (size_t)cls * n_fetch + at] = q;
-            }
-            u0++;
-            if (u0 >= u_end) {
-                unsigned int u1 = 0, k1 = 1u;
-                if (lane == 0) {
-                    if (fetch_max > 1) k1 = cyc < 4096u ? 4u : (cyc < 8192u ? 2u : 1u);
-                    u1 = atomicAdd(tile_counter, k1);
+            /* One unit per atomic.  (Round 2 measured a warp reserving 4 units after a cheap patch: the bookkeeping
+             * cost two more spilled registers across the pixel trace and the bench 3.5 %, 49.3 vs 51.0 Grays/s, and
+             * won nothing even at 4K -- the same-address atomic runs at half of what the L2 serves) */
+            unsigned int u1 = 0;
+            if (lane == 0) {
+                u1 = atomicAdd(tile_counter, 1u);
+                if (order_w) {                       /* file the patch under its cost class for the next frame */
+                    const unsigned int k = ((unsigned int)clock() - unit_t0) >> 10;
+                    const int cls = min(RS_CLASSES - 1, 31 - __clz((int)(k | 1u)));
+                    const unsigned int at = atomicAdd(order_w + cls, 1u);
+                    order_w[RS_ORDER_HEAD + (size_t)cls * n_fetch + at] = q;
                 }
-                u0 = __shfl_sync(0xffffffffu, u1, 0);
-                u_end = u0 + __shfl_sync(0xffffffffu, k1, 0);
             }
+            u0 = __shfl_sync(0xffffffffu, u1, 0);
         }
     } else {
         /* Every turn of the loop runs ONE batch of up to 32 rays on this warp: the primary rays of the next 8x4 patch, or
@@ -970,7 +960,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
                                              unsigned short* tile_lists, int count, int force_linear, int n_sm,
                                              const unsigned int* order_r, unsigned int* order_w,
                                              int after_own_post, uint4* lgrid, int build_lgrid, int mirror_bins,
-                                             int compact, int fetch_max, cudaStream_t stream) {
+                                             int compact, cudaStream_t stream) {
     /* order_r / order_w: order history read / written by this frame (NULL: none), see the kernel.
      * after_own_post: the previous operation on the stream is the FXAA / copy kernel of this context's previous
      * frame (nothing this frame reads is still being written): the pre-pass overlaps it, see rt_cull_tiles_kernel */
@@ -1014,7 +1004,7 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const uint4* lg = lgrid;
     const unsigned short* ml = mirror_lists;
 #define RS_LAUNCH(C, Q) cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<C, Q>, *sc, *f, image, hit_ids, counters, tile_counter, tl, \
-                                          tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml, fetch_max)
+                                          tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml)
     if (compact) e = count ? RS_LAUNCH(true, true) : RS_LAUNCH(false, true);
     else         e = count ? RS_LAUNCH(true, false) : RS_LAUNCH(false, false);
 #undef RS_LAUNCH

@@ -474,37 +474,6 @@ def test_order_history_changes_scheduling_only():
         assert (ids == ids_ref).all() and (img == img_ref).all(), k
 
 
-def test_multi_unit_work_fetch_changes_scheduling_only():
-    """A warp that has just finished a cheap patch reserves up to four work units with one atomic (RT_OPT_FETCH 0)
-    instead of one (RT_OPT_FETCH 1): every patch must still be traced exactly once -- whole frames with and without
-    the order history, repeated frames (the self re-arming counter), sizes whose patch count is no multiple of the
-    reservation, shards (listed work tiles)."""
-    r = gu.renderer()
-    s = rt.Scene()
-    for (view, hours, w, h) in ((5, 14.0, 1920, 1080), (6, 1.0, 1280, 720), (5, 18.0, 641, 359), (6, 9.0, 33, 9),
-                                (5, 6.0, 8, 4), (6, 14.0, 3840, 2160)):
-        f = s.configure(view=view, hours=hours, imgw=w, imgh=h, alias=False)
-        r.set_option(_lib.RT_OPT_FETCH, 1)
-        img_ref, ids_ref = gu.render(r, s, f)
-        r.set_option(_lib.RT_OPT_FETCH, 0)
-        for k in range(3):
-            if k == 2:
-                r.set_option(_lib.RT_OPT_ORDER, 1)
-            img, ids = gu.render(r, s, f)
-            assert (ids == ids_ref).all() and (img == img_ref).all(), (w, h, k)
-        r.set_option(_lib.RT_OPT_ORDER, 0)
-    f = s.configure(view=5, hours=14.0, imgw=640, imgh=360, alias=True)
-    r.set_scene(s.objects, s.lights)
-    for n, sid in ((2, 0), (4, 3)):
-        sh = rt.make_shard(n, sid, 64, 32)
-        outs = []
-        for v in (1, 0, 0):
-            r.set_option(_lib.RT_OPT_FETCH, v)
-            outs.append(r.render_to_host(f, shard=sh, out=np.zeros(640 * 360, dtype=np.uint32)).copy())
-        r.set_option(_lib.RT_OPT_FETCH, 0)
-        assert (outs[0] == outs[1]).all() and (outs[0] == outs[2]).all() and outs[0].any()
-
-
 @pytest.mark.parametrize("alias", [True, False])
 def test_back_to_back_frames_overlap_safely(alias):
     """Consecutive frames of one context with an unchanged scene: the next frame's binning pre-pass is launched

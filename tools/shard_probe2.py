@@ -19,8 +19,7 @@ TW, TH = (int(v) for v in os.environ.get("RTB_TILE", "256x128").split("x"))
 r = rt.Renderer(0)
 r.set_sky(configs.sky_maps(os.path.join(ROOT, "oracle", "_ref", "backgrounds"))[0])
 out = torch.zeros(w * h, dtype=torch.int32, device="cuda")
-VARIANTS = {"default": {}, "compaction": {_lib.RT_OPT_COMPACTION: 1}, "bottom-up order": {_lib.RT_OPT_ORDER: 1},
-            "single fetch": {_lib.RT_OPT_FETCH: 1}}
+VARIANTS = {"default": {}, "compaction": {_lib.RT_OPT_COMPACTION: 1}, "bottom-up order": {_lib.RT_OPT_ORDER: 1}}
 for name in (sys.argv[1:] or ["config3"]):
     if name == "config3":
         _, objs, lights, f = configs.config3(sea_levels=(3.5,))[0]
