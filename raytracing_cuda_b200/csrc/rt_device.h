@@ -38,8 +38,8 @@
 #define RT_MAX_LIGHTS 8
 #define RT_NODE_SENTINEL 0x7FFFFFFF   /* empty-stack marker / empty tree */
 #define RT_STACK_SIZE 64
-/* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 48*n must fit 16 bits */
-#define RT_SMALL_MAX_PRIMS 288
+/* shared-memory tracer (trace_small.cu): link offsets 64*(n-1) + 64*n must fit a signed 16-bit stack entry */
+#define RT_SMALL_MAX_PRIMS 256
 /* peer frame (peer.cu): flag block behind the frames, uints with 32-byte spacing */
 #define RT_PEER_FLAG_UINTS 256
 #define RT_PEER_FLAG_DONE(k) (8 * (k))     /* frame number rank k (< 16) has finished */

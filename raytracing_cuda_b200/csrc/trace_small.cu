@@ -52,7 +52,12 @@
 
 /* Shared-memory addressing: the hot loops use 32-bit shared-window addresses and explicit ld/st.shared, so a
  * node or leaf fetch is one add + LDS.128s with immediate offsets.  Node and leaf links are byte offsets from
- * the start of the staged scene (`base`): node i -> 64 i, leaf slot j -> ~(64 n_nodes + 48 j). */
+ * the start of the staged scene (`base`): node i -> 64 i, leaf slot j -> ~(64 n_nodes + RS_LEAF j).
+ * A staged leaf is RS_LEAF = 64 bytes: the three float4 of the record in HBM (rt_device.h) and, as the fourth, the unit
+ * normal of a triangle -- normalize(cross(e1, e2)) (kernel.cu:123) depends on the triangle only, so every CTA computes
+ * it once while it stages the scene, with the same inline functions the hit code used, and a shaded hit fetches it with
+ * one LDS.128 at rec + 48 instead of ~35 instructions (cross, norm3df, correctly rounded reciprocal, three products). */
+#define RS_LEAF 64
 struct RtSmallShared {
     bool defer;              /* rays that would traverse the hierarchy are handed to a compacted batch (rt_trace_chain) */
     unsigned int base;       /* shared address of the staged nodes (leaf records follow them) */
@@ -160,7 +165,7 @@ struct RtSmallScene {
     }
     __device__ __forceinline__ void linear_closest(const vec3& o, const vec3& d, RtHit& best, RtLocalCounters& cnt) {
         for (int j = 0; j < s.n_prims; j++) {
-            const int off = s.prims_off + 48 * j;
+            const int off = s.prims_off + RS_LEAF * j;
             float t;
             unsigned int tag;
             if (rs_test_record(s.base + off, o, d, t, tag, cnt, COUNT)) rt_consider(best, t, tag, off);
@@ -236,7 +241,7 @@ struct RtSmallScene {
             for (int j = 0; j < s.n_prims; j++) {
                 float t;
                 unsigned int tag;
-                if (rs_test_record(s.base + s.prims_off + 48 * j, o, d, t, tag, cnt, COUNT) &&
+                if (rs_test_record(s.base + s.prims_off + RS_LEAF * j, o, d, t, tag, cnt, COUNT) &&
                     !(tag & RT_TAG_EMISSIVE) && t < tmax)
                     return true;
             }
@@ -251,10 +256,10 @@ struct RtSmallScene {
         if (h.slot < 0) return f4xyz(rs_lds128(s.base - RS_PLANES_BYTES + 32 * (~h.slot) + 16));
         const unsigned int rec = s.base + (unsigned int)h.slot;
         if (h.tag & RT_TAG_SPHERE) return rt_normalize(rt_sub(P, f4xyz(rs_lds128(rec))));
-        return rt_normalize(rt_cross(f4xyz(rs_lds128(rec + 16)), f4xyz(rs_lds128(rec + 32))));
+        return f4xyz(rs_lds128(rec + 48));            /* staged with the leaf: see RS_LEAF */
     }
     __device__ __forceinline__ void material(unsigned int idx, float4& m0, float4& m1) {
-        const unsigned int a = s.base + (unsigned int)(s.prims_off + 48 * s.n_prims) + 32u * idx;
+        const unsigned int a = s.base + (unsigned int)(s.prims_off + RS_LEAF * s.n_prims) + 32u * idx;
         m0 = rs_lds128(a);
         m1 = rs_lds128(a + 16);
     }
@@ -380,7 +385,7 @@ __device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFram
             if (!((s_mask[warp][k0] >> lane) & 1u)) continue;
             count++;
             if (count < 8) {
-                const unsigned int off = (unsigned int)(prims_off + 48 * (int)s_slot[s_warp[warp][k0]]);
+                const unsigned int off = (unsigned int)(prims_off + RS_LEAF * (int)s_slot[s_warp[warp][k0]]);
 #pragma unroll
                 for (int k = 1; k < 8; k++)                  /* static register indices */
                     if (k == count) w[k >> 1] |= off << (16 * (k & 1));
@@ -447,7 +452,7 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
         const bool keep = j < n && (!fr.ok || rs_tile_may_hit(fr, eye, sc.prims + 3 * j, pad));
         const unsigned int m = __ballot_sync(0xffffffffu, keep);
         const int at = count + __popc(m & ((1u << lane) - 1u));
-        if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + 48 * j);
+        if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
         count += __popc(m);
     }
     if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
@@ -504,7 +509,7 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
         }
         const unsigned int m = __ballot_sync(0xffffffffu, keep);
         const int at = mcount + __popc(m & ((1u << lane) - 1u));
-        if (keep && at < RT_SMALL_LIST - 1) mout[1 + at] = (unsigned short)(prims_off + 48 * j);
+        if (keep && at < RT_SMALL_LIST - 1) mout[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
         mcount += __popc(m);
     }
     if (lane == 0) mout[0] = mcount < RT_SMALL_LIST ? (unsigned short)mcount : (unsigned short)0xFFFFu;
@@ -614,7 +619,9 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
                       int tiles_x, unsigned int n_tiles_all, int bins_x,
                       const unsigned int* __restrict__ work_list, int force_linear,
                       const unsigned int* order_r, unsigned int* order_w, const uint4* __restrict__ lgrid,
-                      const unsigned short* __restrict__ mirror_lists) {
+                      const unsigned short* __restrict__ mirror_lists, unsigned int tiles_x_magic) {
+    /* tiles_x_magic = floor(2^32 / tiles_x) + 1: __umulhi(t, magic) == t / tiles_x for every t with t * tiles_x < 2^32
+     * (Granlund-Montgomery; the launcher checks the bound), one IMAD.HI instead of a ~20-instruction division per patch */
     /* fixed-size state first (compile-time shared addresses), the staged scene in dynamic shared memory */
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_SMALL_THREADS];
     __shared__ short s_stack[(RT_SMALL_STACK + 2) * RT_SMALL_THREADS];   /* sentinel + entries + 1 scratch */
@@ -632,7 +639,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     float4* s_planes = (float4*)smem;
     float4* s_nodes = (float4*)(smem + RS_PLANES_BYTES);
     float4* s_prims = s_nodes + 4 * n_nodes;
-    float4* s_mats = s_prims + 3 * n;
+    float4* s_mats = s_prims + (RS_LEAF / 16) * n;
 
     unsigned int u0 = 0;
     if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
@@ -643,12 +650,16 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         float4 v = __ldg(sc.nodes + i);
         if ((i & 3) == 3) {
             const int c0 = __float_as_int(v.x), c1 = __float_as_int(v.y);
-            v.x = __int_as_float(c0 >= 0 ? c0 * 64 : ~(prims_off + (~c0) * 48));
-            v.y = __int_as_float(c1 >= 0 ? c1 * 64 : ~(prims_off + (~c1) * 48));
+            v.x = __int_as_float(c0 >= 0 ? c0 * 64 : ~(prims_off + (~c0) * RS_LEAF));
+            v.y = __int_as_float(c1 >= 0 ? c1 * 64 : ~(prims_off + (~c1) * RS_LEAF));
         }
         s_nodes[i] = v;
     }
-    for (int i = tid; i < 3 * n; i += RT_SMALL_THREADS) s_prims[i] = __ldg(sc.prims + i);
+    for (int i = tid; i < 3 * n; i += RT_SMALL_THREADS) s_prims[4 * (i / 3) + i % 3] = __ldg(sc.prims + i);
+    for (int i = tid; i < n; i += RT_SMALL_THREADS) {
+        const vec3 nrm = rt_normalize(rt_cross(f4xyz(__ldg(sc.prims + 3 * i + 1)), f4xyz(__ldg(sc.prims + 3 * i + 2))));
+        s_prims[4 * i + 3] = make_float4(nrm.x, nrm.y, nrm.z, 0.0f);      /* (meaningless for a sphere; never read there) */
+    }
     for (int i = tid; i < 2 * sc.n_objects; i += RT_SMALL_THREADS) s_mats[i] = __ldg(sc.mats + i);
     for (int i = tid; i < 2 * sc.n_planes; i += RT_SMALL_THREADS) s_planes[i] = __ldg(sc.planes + i);
     __syncthreads();                             /* the only CTA barrier */
@@ -728,7 +739,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
             const unsigned int tile = q / RT_SMALL_PATCHES;
             const int p = (int)(q % RT_SMALL_PATCHES);
             const unsigned int unit_t0 = (unsigned int)clock();
-            const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
+            const int by = tiles_x > 1 ? (int)__umulhi(tile, tiles_x_magic) : (int)tile, bx = (int)tile - by * tiles_x;   /* tile / tiles_x, exactly */
             const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
             const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
             const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
@@ -812,7 +823,7 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
                 const unsigned int tile = q / RT_SMALL_PATCHES;
                 const int p = (int)(q % RT_SMALL_PATCHES);
                 unit_t0 = (unsigned int)clock();
-                const int by = (int)tile / tiles_x, bx = (int)tile - by * tiles_x;
+                const int by = tiles_x > 1 ? (int)__umulhi(tile, tiles_x_magic) : (int)tile, bx = (int)tile - by * tiles_x;   /* tile / tiles_x, exactly */
                 const int x0 = bx * RT_SMALL_TILE_W, y0 = by * RT_SMALL_TILE_H;
                 const int bin = (y0 / RT_SMALL_BIN_H) * bins_x + x0 / RT_SMALL_BIN_W;
                 const unsigned short entry = __ldg(tile_lists + (size_t)bin * RT_SMALL_LIST + lane);
@@ -916,10 +927,10 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
 extern "C" size_t rt_trace_small_smem_bytes(int n_bvh_prims, int n_objects, int n_planes) {
     const size_t n_nodes = n_bvh_prims > 1 ? (size_t)n_bvh_prims - 1 : 0;
     (void)n_planes;   /* the plane block has a fixed size (<= 16 planes) */
-    return RS_PLANES_BYTES + 16 * (4 * n_nodes + 3 * (size_t)n_bvh_prims + 2 * (size_t)n_objects);
+    return RS_PLANES_BYTES + 16 * (4 * n_nodes + (RS_LEAF / 16) * (size_t)n_bvh_prims + 2 * (size_t)n_objects);
 }
 
-/* scenes this kernel accepts: link offsets (64 n_nodes + 48 n) must fit the 16-bit stack entries */
+/* scenes this kernel accepts: link offsets (64 n_nodes + RS_LEAF n) must fit the 16-bit stack entries */
 extern "C" int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_planes) {
     return n_bvh_prims <= RT_SMALL_MAX_PRIMS && n_planes <= 16 &&
            rt_trace_small_smem_bytes(n_bvh_prims, n_objects, n_planes) <= RT_SMALL_DYN_SMEM_MAX;
@@ -1004,7 +1015,9 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     const uint4* lg = lgrid;
     const unsigned short* ml = mirror_lists;
 #define RS_LAUNCH(C, Q) cudaLaunchKernelEx(&cfg, rt_trace_small_kernel<C, Q>, *sc, *f, image, hit_ids, counters, tile_counter, tl, \
-                                          tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml)
+                                          tiles_x, (unsigned int)tiles, bins_x, wl, force_linear, order_r, order_w, lg, ml, tiles_x_magic)
+    if ((unsigned long long)tiles * (unsigned long long)tiles_x >= (1ull << 32)) return cudaErrorInvalidValue;   /* > 1e9 pixels */
+    const unsigned int tiles_x_magic = tiles_x > 1 ? (unsigned int)((1ull << 32) / (unsigned long long)tiles_x) + 1u : 0u;   /* one column: no division */
     if (compact) e = count ? RS_LAUNCH(true, true) : RS_LAUNCH(false, true);
     else         e = count ? RS_LAUNCH(true, false) : RS_LAUNCH(false, false);
 #undef RS_LAUNCH
