@@ -57,6 +57,7 @@ cudaError_t rt_lgb_fill(const RtSceneDev* sc, const float* light_pos, unsigned i
                         unsigned int* entries, unsigned int cap, unsigned int* fail, cudaStream_t stream);
 int rt_trace_small_supported(int n_bvh_prims, int n_objects, int n_planes);
 cudaError_t rt_trace_small_init(void);
+cudaError_t rt_fxaa_init(void);
 cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h, const rt_shard* sh,
                                 const RtPeerSync* peer, cudaStream_t stream);
 cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned int* in, unsigned int* out, int w, int h,
@@ -285,7 +286,7 @@ int rt_create(int device, rt_context** out) {
               cudaMemset(ctx->d_counters, 0, sizeof(RtCountersDev)) == cudaSuccess &&
               cudaMalloc((void**)&ctx->d_tile_counter, 64 * sizeof(unsigned int)) == cudaSuccess &&
               cudaMemset(ctx->d_tile_counter, 0, 64 * sizeof(unsigned int)) == cudaSuccess &&
-              rt_trace_small_init() == cudaSuccess;
+              rt_trace_small_init() == cudaSuccess && rt_fxaa_init() == cudaSuccess;
     for (int i = 0; i < 6 && ok; i++) ok = cudaEventCreate(&ctx->ev[i]) == cudaSuccess;
     if (!ok) {
         rt_destroy(ctx);       /* frees whatever has been allocated so far */

@@ -100,6 +100,19 @@ rt_fxaa_smem_kernel(const unsigned int* __restrict__ in, unsigned int* __restric
 #define FX_STAGE_BYTES (FX_BOXW * FX_BOXH * 4)
 #define FX_STAGE_WORDS 2464   /* 9792 B rounded up to a multiple of 128 B: every TMA destination is 128-byte aligned */
 #define FX_THREADS 256
+/* Two shapes of the same kernel.  FX_CTAS_WAVE CTAs per SM (32 registers, one stage): frames whose tiles all fit in
+ * ONE wave (1920x1080 = 1,020 tiles on 1,184 slots) -- one tile per CTA, no loop; every CTA is resident with its
+ * barrier initialised while the tracer's tail still runs (programmatic dependent launch).  FX_CTAS_LOOP CTAs per SM
+ * (64 registers, two stages): larger frames, each CTA loops over its tiles with the next load in flight (faster at
+ * 3840x2160: 25.0 vs 27.0 us).  profiles/r02_ab_fxaa_residency.txt has the measurements, and how they led to the
+ * shared-memory carve-out (rt_fxaa_init), which is where the time was. */
+#ifndef FX_CTAS_WAVE
+#define FX_CTAS_WAVE 8
+#endif
+#ifndef FX_WAVE_STAGES
+#define FX_WAVE_STAGES 1
+#endif
+#define FX_CTAS_LOOP 4
 
 __device__ __forceinline__ uint32_t fx_smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -192,11 +205,14 @@ __device__ __forceinline__ void fx_filter_tile(const unsigned int* __restrict__ 
     }
 }
 
-__global__ void __launch_bounds__(FX_THREADS)
+/* SHARD = false: the whole frame on one GPU (no shard arithmetic, no peer handshake: fewer live registers) */
+template <bool SHARD, int CTAS>
+__global__ void __launch_bounds__(FX_THREADS, CTAS)
 rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned int* __restrict__ in,
                    unsigned int* __restrict__ out, int w, int h, int n_shards, int shard_id, int stride, int kx,
                    int ky, const RtPeerSync peer) {
-    __shared__ __align__(128) unsigned int s_px[2][FX_STAGE_WORDS];
+    constexpr bool LOOP = CTAS != FX_CTAS_WAVE;     /* one wave: grid == tiles, one tile per CTA, one stage */
+    __shared__ __align__(128) unsigned int s_px[LOOP ? 2 : FX_WAVE_STAGES][FX_STAGE_WORDS];
     __shared__ float s_lum[FX_BOXH][FX_BOXW];
     __shared__ __align__(8) uint64_t s_bar[2];
 
@@ -215,14 +231,14 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
 
     int k = blockIdx.x;
     int tx, ty;
-    bool have = fx_tile_origin(k, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, tx, ty);
+    bool have = fx_tile_origin(k, tiles_x, tiles_y, SHARD ? n_shards : 1, shard_id, stride, kx, ky, tx, ty);
     if (tid == 0 && have && tx < tiles_x) {
         fx_mbar_expect_tx(&s_bar[0], FX_STAGE_BYTES);
         fx_tma_load_2d(&s_px[0][0], &in_map, tx * FX_TW - FX_HALO_X, ty * FX_TH - 1, &s_bar[0]);
     }
     /* peer frame: the owner must have released the buffer before the first store; the first tile is already on its
      * way into shared memory meanwhile.  A wait that gave up leaves the buffer alone (error word set). */
-    const bool may_store = peer.flags ? fx_peer_acquire(peer, tid == 0) : true;
+    const bool may_store = (SHARD && peer.flags) ? fx_peer_acquire(peer, tid == 0) : true;
     uint32_t phases = 0;   /* bit s = parity to wait for on stage s */
     int stage = 0;
     /* whole frames: the next tile by addition (k advances by gridDim.x), no division in the loop */
@@ -231,7 +247,10 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         const int kn = k + gridDim.x;
         int ntx, nty;
         bool have_next;
-        if (n_shards <= 1) {
+        if (!LOOP) {
+            ntx = nty = 0;
+            have_next = false;
+        } else if (!SHARD) {
             ntx = tx + step_x;
             nty = ty + step_y;
             if (ntx >= tiles_x) { ntx -= tiles_x; nty++; }
@@ -239,10 +258,10 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         } else {
             have_next = fx_tile_origin(kn, tiles_x, tiles_y, n_shards, shard_id, stride, kx, ky, ntx, nty);
         }
-        if (tid == 0 && have_next && ntx < tiles_x) {
+        if (LOOP && tid == 0 && have_next && ntx < tiles_x) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             fx_mbar_expect_tx(&s_bar[stage ^ 1], FX_STAGE_BYTES);
-            fx_tma_load_2d(&s_px[stage ^ 1][0], &in_map, ntx * FX_TW - FX_HALO_X, nty * FX_TH - 1, &s_bar[stage ^ 1]);
+            fx_tma_load_2d(&s_px[LOOP ? stage ^ 1 : 0][0], &in_map, ntx * FX_TW - FX_HALO_X, nty * FX_TH - 1, &s_bar[stage ^ 1]);
         }
         if (tx < tiles_x) {
             fx_mbar_wait(&s_bar[stage], (phases >> stage) & 1u);
@@ -256,6 +275,7 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
             else if (inner) fx_filter_tile<true>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
             else            fx_filter_tile<false>(s_px[stage], s_lum, out, tx, ty, w, h, tid);
         }
+        if (!LOOP) break;
         __syncthreads();   /* everyone is done with s_px[stage] and s_lum before they are refilled */
         k = kn;
         tx = ntx;
@@ -263,7 +283,7 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         have = have_next;
         stage ^= 1;
     }
-    if (peer.flags) rt_peer_publish(peer, gridDim.x, tid == 0);
+    if (SHARD && peer.flags) rt_peer_publish(peer, gridDim.x, tid == 0);
 }
 
 /* pass-through when AA is off (reference kernel.cu:275-278), shard-aware */
@@ -339,6 +359,21 @@ static RtPeerSync fx_peer_arg(const RtPeerSync* peer) {
     return p;
 }
 
+/* per device, once (rt_create).  The FXAA / copy kernel sits between two tracers in the stream, chained by
+ * programmatic dependent launch in both directions; it asks for the tracer's shared-memory carve-out so that its CTAs
+ * can become resident while the tracer's last CTAs still run, and the next frame's CTAs while its own do
+ * (measured through the CTA's shared-memory size: profiles/r02_ab_fxaa_residency.txt, runs 4 and 5). */
+extern "C" cudaError_t rt_fxaa_init(void) {
+    const int most = cudaSharedmemCarveoutMaxShared;
+    cudaError_t e = cudaFuncSetAttribute(rt_fxaa_tma_kernel<false, FX_CTAS_WAVE>, cudaFuncAttributePreferredSharedMemoryCarveout, most);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_fxaa_tma_kernel<false, FX_CTAS_LOOP>, cudaFuncAttributePreferredSharedMemoryCarveout, most);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_fxaa_tma_kernel<true, FX_CTAS_WAVE>, cudaFuncAttributePreferredSharedMemoryCarveout, most);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_fxaa_tma_kernel<true, FX_CTAS_LOOP>, cudaFuncAttributePreferredSharedMemoryCarveout, most);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_fxaa_smem_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, most);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_copy_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, most);
+    return e;
+}
+
 extern "C" cudaError_t rt_launch_fxaa_smem(const unsigned int* in, unsigned int* out, int w, int h,
                                            const rt_shard* sh, const RtPeerSync* peer, cudaStream_t stream) {
     dim3 block(FX_BW, FX_BH, 1), grid((w + FX_BW - 1) / FX_BW, (h + FX_BH - 1) / FX_BH, 1);
@@ -363,7 +398,8 @@ extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned
         const int stiles_x = (tiles_x + kx - 1) / kx, stiles_y = (tiles_y + ky - 1) / ky;
         slots = ((stiles_x + n - 1) / n) * stiles_y * kx * ky;
     }
-    int grid = n_sm * 4;
+    const bool one_wave = slots <= n_sm * FX_CTAS_WAVE;
+    int grid = n_sm * (one_wave ? FX_CTAS_WAVE : FX_CTAS_LOOP);
     if (grid > slots) grid = slots;
     if (grid < 1) grid = 1;
     cudaLaunchAttribute pdl[1];
@@ -376,7 +412,10 @@ extern "C" cudaError_t rt_launch_fxaa_tma(const CUtensorMap* map, const unsigned
     cfg.attrs = pdl;
     cfg.numAttrs = 1;
     RT_LAUNCHED(1);
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, rt_fxaa_tma_kernel, *map, in, out, w, h, n, id, st, kx, ky, fx_peer_arg(peer));
+    const bool shard = n > 1 || (peer && peer->flags);
+    auto kernel = shard ? (one_wave ? rt_fxaa_tma_kernel<true, FX_CTAS_WAVE> : rt_fxaa_tma_kernel<true, FX_CTAS_LOOP>)
+                        : (one_wave ? rt_fxaa_tma_kernel<false, FX_CTAS_WAVE> : rt_fxaa_tma_kernel<false, FX_CTAS_LOOP>);
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, *map, in, out, w, h, n, id, st, kx, ky, fx_peer_arg(peer));
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

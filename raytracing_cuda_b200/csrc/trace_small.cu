@@ -946,6 +946,14 @@ extern "C" cudaError_t rt_trace_small_init(void) {
         e = cudaFuncSetAttribute(rt_trace_small_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RT_SMALL_DYN_SMEM_MAX);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(rt_trace_small_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, RT_SMALL_DYN_SMEM_MAX);
+    /* Every kernel of the frame chain asks for the SAME shared-memory carve-out (the largest, what the tracer needs).
+     * Two kernels with different carve-outs cannot share an SM, so a dependent launch could not become resident
+     * under its predecessor's tail: see rt_fxaa_init. */
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     return e;
 }
 

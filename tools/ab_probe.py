@@ -1,7 +1,8 @@
 #!/usr/bin/env python3
 """A/B probe of one rt_set_option key on the bench workload and on single frames, same process, same sky.
 
-usage: ab_probe.py KEY V0,V1[,V2..] [reps]      e.g.  ab_probe.py 12 0,1     (RT_OPT_COMPACTION on / off)
+usage: ab_probe.py KEY V0,V1[,V2..] [reps] [config3]      e.g.  ab_probe.py 12 0,1     (RT_OPT_COMPACTION on / off)
+       (a fourth argument "config3" runs the bench loop on the Mountains 4K sea-level frames instead of config 2)
 
   bench   bench.py's device loop: four contexts (Island 1080p, the four times of day), L2 flushed between steps, CUDA
           events per step -> Grays/s
@@ -22,7 +23,7 @@ key = int(sys.argv[1])
 values = [int(v) for v in sys.argv[2].split(",")]
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 40
 sky, label = configs.sky_maps(os.path.join(ROOT, "oracle", "_ref", "backgrounds"))
-states = configs.config2()
+states = list(configs.config3()) if len(sys.argv) > 4 and sys.argv[4] == "config3" else configs.config2()
 ctxs = []
 for i, (_, objs, lights, fr) in enumerate(states):
     r = rt.Renderer(0)
