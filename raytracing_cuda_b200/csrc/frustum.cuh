@@ -70,10 +70,8 @@ __device__ __forceinline__ void rs_tile_corners(const RtFrameDev& f, int x0, int
 }
 
 /* can any ray of the tile (origin `eye`, inside `fr`) hit leaf record `rec`? */
-__device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3& eye, const float4* __restrict__ rec,
-                                                float pad) {
-    const float4 q0 = __ldg(rec);
-    const float4 q1 = __ldg(rec + 1);
+__device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3& eye, const float4 q0, const float4 q1,
+                                                const float4 q2, float pad) {
     const unsigned int tag = __float_as_uint(q0.w);
     const vec3 a = vsub(f4xyz(q0), eye);
     if (tag & RT_TAG_SPHERE) {
@@ -84,7 +82,6 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
             if (vdot(fr.n[k], a) < -r) return false;
         return true;
     }
-    const float4 q2 = __ldg(rec + 2);
     const vec3 e1 = f4xyz(q1), e2 = f4xyz(q2);
     /* det = -d.Ng for every ray: the eye on the back side means `det < 0.001` rejects them all */
     const vec3 ng = vcross(e1, e2);
@@ -95,6 +92,10 @@ __device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3&
     for (int k = 0; k < 4; k++)
         if (vdot(fr.n[k], a) < -pad && vdot(fr.n[k], b) < -pad && vdot(fr.n[k], c) < -pad) return false;
     return true;
+}
+__device__ __forceinline__ bool rs_tile_may_hit(const RsFrustum& fr, const vec3& eye, const float4* __restrict__ rec,
+                                                float pad) {
+    return rs_tile_may_hit(fr, eye, __ldg(rec), __ldg(rec + 1), __ldg(rec + 2), pad);
 }
 
 

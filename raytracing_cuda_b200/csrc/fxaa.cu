@@ -205,6 +205,30 @@ __device__ __forceinline__ void fx_filter_tile(const unsigned int* __restrict__ 
     }
 }
 
+#ifdef RS_TIMELINE
+/* debug variant: [slot][0] first CTA entry  [1] first CTA past griddepcontrol.wait  [2] last CTA exit (see trace_small.cu) */
+__device__ unsigned long long g_tl_fx[8][4];
+__device__ unsigned int g_tl_fx_no, g_tl_fx_ticket;
+__device__ __forceinline__ unsigned long long fx_tl_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+extern "C" cudaError_t rt_debug_timeline_fxaa(unsigned long long* out, int reset) {
+    cudaError_t e = cudaMemcpyFromSymbol(out, g_tl_fx, sizeof(g_tl_fx));
+    if (e == cudaSuccess && reset) {
+        unsigned long long init[8][4];
+        for (int s = 0; s < 8; s++)
+            for (int k = 0; k < 4; k++) init[s][k] = k < 2 ? ~0ull : 0ull;
+        const unsigned int zero = 0;
+        e = cudaMemcpyToSymbol(g_tl_fx, init, sizeof(init));
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_tl_fx_no, &zero, sizeof(zero));
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_tl_fx_ticket, &zero, sizeof(zero));
+    }
+    return e;
+}
+#endif
+
 /* SHARD = false: the whole frame on one GPU (no shard arithmetic, no peer handshake: fewer live registers) */
 template <bool SHARD, int CTAS>
 __global__ void __launch_bounds__(FX_THREADS, CTAS)
@@ -218,6 +242,10 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
 
     const int tiles_x = (w + FX_TW - 1) / FX_TW, tiles_y = (h + FX_TH - 1) / FX_TH;
     const int tid = threadIdx.x;
+#ifdef RS_TIMELINE
+    unsigned long long* const tl = g_tl_fx[*(volatile unsigned int*)&g_tl_fx_no & 7u];
+    if (tid == 0) atomicMin(tl + 0, fx_tl_now());
+#endif
     if (tid == 0) {
         fx_mbar_init(&s_bar[0], 1);
         fx_mbar_init(&s_bar[1], 1);
@@ -228,6 +256,9 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
     /* programmatic dependent launch: the tracer has completed from here on; the next frame's pre-pass may start */
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#ifdef RS_TIMELINE
+    if (tid == 0) atomicMin(tl + 1, fx_tl_now());
+#endif
 
     int k = blockIdx.x;
     int tx, ty;
@@ -284,6 +315,14 @@ rt_fxaa_tma_kernel(const __grid_constant__ CUtensorMap in_map, const unsigned in
         stage ^= 1;
     }
     if (SHARD && peer.flags) rt_peer_publish(peer, gridDim.x, tid == 0);
+#ifdef RS_TIMELINE
+    __syncthreads();
+    if (tid == 0) {
+        atomicMax(tl + 2, fx_tl_now());
+        __threadfence();
+        if (atomicAdd(&g_tl_fx_ticket, 1u) == gridDim.x - 1) { g_tl_fx_ticket = 0; g_tl_fx_no++; }
+    }
+#endif
 }
 
 /* pass-through when AA is off (reference kernel.cu:275-278), shard-aware */

@@ -402,6 +402,7 @@ __device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFram
 #endif
 }
 
+template <int RS_CULL_CHUNKS>
 __device__ __forceinline__ void
 rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restrict__ tile_lists, int tiles_x,
             int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
@@ -446,31 +447,20 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
     rs_tile_corners(f, x0, y0, x1, y1, corner);
     const RsFrustum fr = rs_frustum_from_corners(corner);
     unsigned short* __restrict__ out = tile_lists + (size_t)tile * RT_SMALL_LIST;
-    int count = 0;
-    for (int j0 = 0; j0 < n; j0 += 32) {
-        const int j = j0 + lane;
-        const bool keep = j < n && (!fr.ok || rs_tile_may_hit(fr, eye, sc.prims + 3 * j, pad));
-        const unsigned int m = __ballot_sync(0xffffffffu, keep);
-        const int at = count + __popc(m & ((1u << lane) - 1u));
-        if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
-        count += __popc(m);
-    }
-    if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
 
     /* ---- mirror bins.  A primary ray that hits plane 0 (the reference's sea, scene.cpp:183-190) at P continues as
      * P + 0.001 r, r = normalize(d - 2 (N.d) N) (kernel.cu:212-213).  With a unit normal that is the mirror image
      * of the primary ray: its line passes through the eye's image E' behind the plane with the primary direction's
      * image, so the rays a tile sends off the plane lie in the tile's frustum mirrored, apex E' -- the same cull as
-     * above with the mirrored corners, plus: nothing wholly on E's far side of the plane can be met (the ray starts on
-     * the plane and leaves it towards the eye's side).  Rounding: P sits within |t| 2^-22 (< 1e-3 world units) of
-     * the exact point and r within 2^-23 of the exact direction, both far inside the pad (2^-13 of the largest
-     * coordinate) every plane test here carries.  The exact leaf tests decide; bit-identical to the traversal. */
-    if (!mirror_lists) return;
-    unsigned short* __restrict__ mout = mirror_lists + (size_t)tile * RT_SMALL_LIST;
+     * the primary one with the mirrored corners, plus: nothing wholly on E's far side of the plane can be met (the ray
+     * starts on the plane and leaves it towards the eye's side).  Rounding: P sits within |t| 2^-22 (< 1e-3 world
+     * units) of the exact point and r within 2^-23 of the exact direction, both far inside the pad (2^-13 of the
+     * largest coordinate) every plane test here carries.  The exact leaf tests decide; bit-identical to the traversal. */
+    unsigned short* __restrict__ mout = mirror_lists ? mirror_lists + (size_t)tile * RT_SMALL_LIST : (unsigned short*)nullptr;
     bool on = false;
     vec3 pn = v3(0, 0, 0), p0 = v3(0, 0, 0);
     float hgt = 0.0f;
-    if (sc.n_planes > 0 && fr.ok) {
+    if (mout && sc.n_planes > 0 && fr.ok) {
         const float4 q0 = __ldg(sc.planes), q1 = __ldg(sc.planes + 1);
         const unsigned int tag = __float_as_uint(q0.w);
         pn = f4xyz(q1);
@@ -478,10 +468,6 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
         const float mirror = __ldg(sc.mats + 2 * (tag & RT_TAG_INDEX)).w;
         hgt = vdot(vsub(eye, p0), pn);
         on = mirror > 0.0f && !(tag & RT_TAG_EMISSIVE) && fabsf(vdot(pn, pn) - 1.0f) <= 1e-6f;
-    }
-    if (!on) {
-        if (lane == 0) mout[0] = (unsigned short)0xFFFFu;       /* traverse */
-        return;
     }
     const vec3 eye_m = vsub(eye, vscale(pn, 2.0f * hgt));
     vec3 corner_m[4];
@@ -491,45 +477,126 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
     const float apex_m[3] = {eye_m.x, eye_m.y, eye_m.z};
     const float pad_m = fmaxf(pad, rs_cull_pad(sc, apex_m));
     const float side = hgt > pad_m ? 1.0f : (hgt < -pad_m ? -1.0f : 0.0f);   /* eye (nearly) in the plane: no side cull */
-    int mcount = 0;
-    for (int j0 = 0; j0 < n; j0 += 32) {
-        const int j = j0 + lane;
-        bool keep = j < n;
-        if (keep && frm.ok) keep = rs_tile_may_hit(frm, eye_m, sc.prims + 3 * j, pad_m);
-        if (keep && side != 0.0f) {
-            const float4 r0 = __ldg(sc.prims + 3 * j), r1 = __ldg(sc.prims + 3 * j + 1);
-            const float ha = side * vdot(vsub(f4xyz(r0), p0), pn);
-            if (__float_as_uint(r0.w) & RT_TAG_SPHERE) {
-                keep = !(ha < -(fabsf(r1.x) + pad_m));
-            } else {
-                const float4 r2 = __ldg(sc.prims + 3 * j + 2);
-                const float hb = ha + side * vdot(f4xyz(r1), pn), hc = ha + side * vdot(f4xyz(r2), pn);
-                keep = !(ha < -pad_m && hb < -pad_m && hc < -pad_m);
+
+    /* Every lane first loads the records of RS_CULL_CHUNKS of its primitives (lane, lane + 32, ...), then tests them
+     * against both frusta: with 4, one L2 round trip per 128 primitives instead of one per 32 and list (the pre-pass
+     * is a chain of latencies, and the tracer behind it waits for its last CTA). */
+    /* One chunk at a time (large frames: register budget of 4 CTAs per SM) walks the primitives twice, once per list,
+     * as round 1 did: fusing the two tests there cost 0.3 % of the 4K frame. */
+    constexpr bool FUSED = RS_CULL_CHUNKS > 1;
+    int count = 0, mcount = 0;
+#pragma unroll
+    for (int pass = 0; pass < (FUSED ? 1 : 2); pass++) {
+        const bool primary = FUSED || pass == 0, mirrored = on && (FUSED || pass == 1);
+        if (!primary && !mirrored) break;
+        for (int c0 = 0; c0 < n; c0 += 32 * RS_CULL_CHUNKS) {
+            float4 r0[RS_CULL_CHUNKS], r1[RS_CULL_CHUNKS], r2[RS_CULL_CHUNKS];
+#pragma unroll
+            for (int c = 0; c < RS_CULL_CHUNKS; c++) {
+                if (c0 + c * 32 < n) {
+                    const float4* __restrict__ rec = sc.prims + 3 * min(c0 + c * 32 + lane, n - 1);
+                    r0[c] = __ldg(rec);
+                    r1[c] = __ldg(rec + 1);
+                    r2[c] = __ldg(rec + 2);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < RS_CULL_CHUNKS; c++) {
+                if (c0 + c * 32 >= n) continue;
+                const int j = c0 + c * 32 + lane;
+                if (primary) {
+                    const bool keep = j < n && (!fr.ok || rs_tile_may_hit(fr, eye, r0[c], r1[c], r2[c], pad));
+                    const unsigned int m = __ballot_sync(0xffffffffu, keep);
+                    const int at = count + __popc(m & ((1u << lane) - 1u));
+                    if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
+                    count += __popc(m);
+                }
+                if (mirrored) {
+                    bool mkeep = j < n;
+                    if (mkeep && frm.ok) mkeep = rs_tile_may_hit(frm, eye_m, r0[c], r1[c], r2[c], pad_m);
+                    if (mkeep && side != 0.0f) {
+                        const float ha = side * vdot(vsub(f4xyz(r0[c]), p0), pn);
+                        if (__float_as_uint(r0[c].w) & RT_TAG_SPHERE) {
+                            mkeep = !(ha < -(fabsf(r1[c].x) + pad_m));
+                        } else {
+                            const float hb = ha + side * vdot(f4xyz(r1[c]), pn), hc = ha + side * vdot(f4xyz(r2[c]), pn);
+                            mkeep = !(ha < -pad_m && hb < -pad_m && hc < -pad_m);
+                        }
+                    }
+                    const unsigned int mm = __ballot_sync(0xffffffffu, mkeep);
+                    const int mat = mcount + __popc(mm & ((1u << lane) - 1u));
+                    if (mkeep && mat < RT_SMALL_LIST - 1) mout[1 + mat] = (unsigned short)(prims_off + RS_LEAF * j);
+                    mcount += __popc(mm);
+                }
             }
         }
-        const unsigned int m = __ballot_sync(0xffffffffu, keep);
-        const int at = mcount + __popc(m & ((1u << lane) - 1u));
-        if (keep && at < RT_SMALL_LIST - 1) mout[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
-        mcount += __popc(m);
     }
-    if (lane == 0) mout[0] = mcount < RT_SMALL_LIST ? (unsigned short)mcount : (unsigned short)0xFFFFu;
+    if (lane == 0) {
+        out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
+        if (mout) mout[0] = on && mcount < RT_SMALL_LIST ? (unsigned short)mcount : (unsigned short)0xFFFFu;   /* 0xFFFF: traverse */
+    }
 }
+
+#ifdef RS_TIMELINE
+/* debug variant (tools/build_variant.sh tl -DRS_TIMELINE): %globaltimer stamps of the last 8 frames' kernels.
+ * [slot][0] pre-pass first entry  [1] pre-pass last CTA done (before its final wait)  [2] tracer first CTA entry
+ * [3] tracer first / [4] last CTA past griddepcontrol.wait  [5] last unit done  [6] last warp exit */
+__device__ unsigned long long g_tl_frame[8][8];
+__device__ unsigned int g_tl_frame_no;
+__device__ __forceinline__ unsigned long long tl_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long* tl_slot() { return g_tl_frame[*(volatile unsigned int*)&g_tl_frame_no & 7u]; }
+extern "C" cudaError_t rt_debug_timeline_small(unsigned long long* out, int reset) {
+    cudaError_t e = cudaMemcpyFromSymbol(out, g_tl_frame, sizeof(g_tl_frame));
+    if (e == cudaSuccess && reset) {
+        unsigned long long init[8][8];
+        for (int s = 0; s < 8; s++)
+            for (int k = 0; k < 8; k++) init[s][k] = (k == 0 || k == 2 || k == 3) ? ~0ull : 0ull;
+        const unsigned int zero = 0;
+        e = cudaMemcpyToSymbol(g_tl_frame, init, sizeof(init));
+        if (e == cudaSuccess) e = cudaMemcpyToSymbol(g_tl_frame_no, &zero, sizeof(zero));
+    }
+    return e;
+}
+#endif
 
 /* The pre-pass reads the scene and writes lists nobody else is using, so -- when the host knows that the
  * scene was complete before the previous kernel on the stream (wait_first = 0: that kernel is the FXAA / copy
  * of this context's previous frame) -- it runs WHILE that kernel finishes.  Its last act is to wait for it:
  * the tracer, which waits for this kernel, then never overwrites the base image under a running FXAA. */
-__global__ void __launch_bounds__(256)
+/* (Round 2 measured a second instantiation without the light cells -- no shared memory, 128-thread CTAs of 7 K
+ * registers that become resident beside the previous frame's FXAA CTAs instead of queueing behind them: the pre-pass
+ * alone got 2 us faster and the bench step 0.5 % SLOWER, 53.97 vs 54.25 Grays/s; profiles/r02_frame_timeline.txt.) */
+/* CHUNKS = 4 (119 registers, 2 CTAs per SM): frames whose bins fit one wave of those (1920x1080: 255 CTAs).
+ * CHUNKS = 1 (4 CTAs per SM): larger frames, where the number of waves decides (3840x2160: 1,020 CTAs; the 4-chunk
+ * kernel took 31 instead of 26 us there). */
+template <int CHUNKS>
+__global__ void __launch_bounds__(256, CHUNKS > 1 ? 2 : 4)
 rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
                      int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
                      int work_tiles_x, int work_tiles_y, int wait_first, uint4* __restrict__ lgrid,
                      int n_cull_blocks, unsigned short* __restrict__ mirror_lists) {
+#ifdef RS_TIMELINE
+    if (threadIdx.x == 0) atomicMin(tl_slot() + 0, tl_now());
+#endif
     if (wait_first) rs_griddep_wait();
+#ifndef RS_LATE_TRIGGER
     rs_griddep_launch();                         /* the tracer may start staging the scene */
+#endif
     /* the CTAs behind the screen bins fill the light bins (lgrid != NULL), one coarse cell each */
     if ((int)blockIdx.x >= n_cull_blocks) rs_light_cell(sc, f, lgrid, (int)blockIdx.x - n_cull_blocks);
-    else rs_cull_bin(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y, mirror_lists);
+    else rs_cull_bin<CHUNKS>(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y, mirror_lists);
+#ifdef RS_TIMELINE
+    __syncthreads();
+    if (threadIdx.x == 0) atomicMax(tl_slot() + 1, tl_now());
+#endif
     rs_griddep_wait();
+#ifdef RS_LATE_TRIGGER
+    rs_griddep_launch();
+#endif
 }
 
 /* ---------------------------------------------------------------- ray queue (compaction)
@@ -611,6 +678,24 @@ __device__ __forceinline__ bool rs_q_pop(const float4* __restrict__ q, unsigned 
 
 /* ---------------------------------------------------------------- tracer */
 
+/* The last warp to finish re-arms the work counter for the next launch on this stream: every warp's fetches
+ * precede its arrival here (lane 0 of each warp calls this once).  (A few CTAs become resident only when the
+ * frame's units have all been handed out -- the previous frame's FXAA CTAs leave an SM's shared memory in pieces; an
+ * early exit for them before the staging cost two spilled registers and 0.9 % of the bench.) */
+__device__ __forceinline__ void rs_warp_finished(unsigned int* tile_counter, const unsigned int* order_r) {
+    __threadfence();
+    if (atomicAdd(tile_counter + 1, 1u) == gridDim.x * RT_SMALL_WARPS - 1) {
+        tile_counter[0] = 0;
+        tile_counter[1] = 0;
+        tile_counter[RS_CNT_TILES] = 0;
+#ifdef RS_TIMELINE
+        g_tl_frame_no++;
+#endif
+        if (order_r)                         /* this buffer is written by the next frame */
+            for (int c = 0; c < RS_CLASSES; c++) ((unsigned int*)order_r)[c] = 0;
+    }
+}
+
 template <bool COUNT, bool COMPACT>
 __global__ void __launch_bounds__(RT_SMALL_THREADS, RT_SMALL_CTAS_PER_SM)
 rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
@@ -644,6 +729,10 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     unsigned int u0 = 0;
     if (lane == 0) u0 = atomicAdd(tile_counter, 1u);
     if (COMPACT && tid < 2) s_qctl[tid] = 0u;
+#ifdef RS_TIMELINE
+    unsigned long long* const tl_frame = tl_slot();
+    if (tid == 0) atomicMin(tl_frame + 2, tl_now());
+#endif
 
     /* stage the scene: links become byte offsets from the start of the nodes */
     for (int i = tid; i < 4 * n_nodes; i += RT_SMALL_THREADS) {
@@ -662,8 +751,16 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
     }
     for (int i = tid; i < 2 * sc.n_objects; i += RT_SMALL_THREADS) s_mats[i] = __ldg(sc.mats + i);
     for (int i = tid; i < 2 * sc.n_planes; i += RT_SMALL_THREADS) s_planes[i] = __ldg(sc.planes + i);
-    __syncthreads();                             /* the only CTA barrier */
+    __syncthreads();                             /* the only CTA barrier of a working CTA */
     rs_griddep_wait();                           /* the pre-pass has finished: lists, work list, counts */
+#ifdef RS_TIMELINE
+    if (tid == 0) {
+        const unsigned long long t = tl_now();
+        const unsigned long long first = atomicMin(tl_frame + 3, t);
+        atomicMax(tl_frame + 4, t);
+        if (t > first && t - first > 20000ull) atomicAdd(tl_frame + 7, 1ull);   /* [7] CTAs that came 20 us late */
+    }
+#endif
 
     /* Work units: single 8x4 patches, fetched one at a time from an atomic counter, nothing reserved ahead.
      * Unit k is patch 3 - k % 4 of tile n_tiles - 1 - k / 4: the frame is walked from its LAST tile to its
@@ -908,19 +1005,12 @@ rt_trace_small_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __r
         unsigned long long* o = (unsigned long long*)hit_ids + 4 * (size_t)(blockIdx.x * RT_SMALL_WARPS + warp);
         o[0] = tl_t0; o[1] = tl_t1; o[2] = tl_t2; o[3] = tl_units;
     }
-#endif
-    /* The last warp to finish re-arms the work counter for the next launch on this stream: every warp's
-     * fetches precede its arrival here. */
     if (lane == 0) {
-        __threadfence();
-        if (atomicAdd(tile_counter + 1, 1u) == gridDim.x * RT_SMALL_WARPS - 1) {
-            tile_counter[0] = 0;
-            tile_counter[1] = 0;
-            tile_counter[RS_CNT_TILES] = 0;
-            if (order_r)                         /* this buffer is written by the next frame */
-                for (int c = 0; c < RS_CLASSES; c++) ((unsigned int*)order_r)[c] = 0;
-        }
+        if (tl_units) atomicMax(tl_frame + 5, tl_t1);
+        atomicMax(tl_frame + 6, tl_now());
     }
+#endif
+    if (lane == 0) rs_warp_finished(tile_counter, order_r);
 }
 
 /* dynamic shared memory: the staged scene */
@@ -949,7 +1039,8 @@ extern "C" cudaError_t rt_trace_small_init(void) {
     /* Every kernel of the frame chain asks for the SAME shared-memory carve-out (the largest, what the tracer needs).
      * Two kernels with different carve-outs cannot share an SM, so a dependent launch could not become resident
      * under its predecessor's tail: see rt_fxaa_init. */
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -1001,14 +1092,15 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.stream = stream;
     cfg.attrs = pdl;
     cfg.numAttrs = 1;
+    const bool with_lights = lgrid && build_lgrid;
     const int cull_blocks = (bins + 7) / 8;
     const int lit = f->n_lights < RT_LGRID_LIGHTS ? f->n_lights : RT_LGRID_LIGHTS;    /* lights with bins */
     /* build_lgrid = 0: the light bins in `lgrid` are still those of this scene and these lights (api.cu) */
-    cfg.gridDim = dim3(cull_blocks + (lgrid && build_lgrid ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
+    cfg.gridDim = dim3(cull_blocks + (with_lights ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
     cfg.blockDim = dim3(256, 1, 1);
     cfg.dynamicSmemBytes = 0;
     RT_LAUNCHED(2);                              /* pre-pass + tracer */
-    cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins,
+    cudaError_t e = cudaLaunchKernelEx(&cfg, (int)cfg.gridDim.x <= 2 * n_sm ? rt_cull_tiles_kernel<4> : rt_cull_tiles_kernel<1>, *sc, *f, tile_lists, bins_x, bins,
                                        sharded ? work_list : (unsigned int*)nullptr, tile_counter + RS_CNT_TILES, tiles_x,
                                        tiles_y, after_own_post ? 0 : 1, lgrid, cull_blocks, mirror_lists);
     if (e != cudaSuccess) return e;

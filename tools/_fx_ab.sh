@@ -1,4 +1,1 @@
-for v in "" co_s2 w8s2 ""; do
-  if [ -z "$v" ]; then unset RTB_LIB_PATH; else export RTB_LIB_PATH=build/variants/lib_$v.so; fi
-  echo "== ${v:-new}" ; python tools/ab_probe.py 0 0 60 2>&1 | tail -2 | cut -c1-330
-done
+for i in 1 2 3; do python -m pytest tests/test_gpu_fxaa_shard_bvh.py tests/test_gpu_parity.py -x -q 2>&1 | grep -E "^E |passed|failed|Error|^tests.*:[0-9]+:" | head -30; done

@@ -78,6 +78,17 @@ for rnd in range(2):                    # two rounds, interleaved: drift shows u
                 fx += t["fxaa_ms"]
             r0.set_option(_lib.RT_OPT_TIMING, 0)
             line[name] = {"trace_us": 1e3 * tr / reps, "fxaa_us": 1e3 * fx / reps}
+        # config 5: 32 frames of the day/night path in order (lights move: refit + light bins rebuilt per frame)
+        path = configs.config5(tuple(range(0, 256, 8)))
+        for rep in range(2):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _, objs, lights, f in path:
+                r0.set_scene(objs, lights)
+                r0.render(f, out)
+            e1.record(stream)
+            torch.cuda.synchronize()
+        line["config5 path us/frame (set_scene + render)"] = 1e3 * e0.elapsed_time(e1) / len(path)
         objs, lights, fr = states[0][1:]
         r0.set_scene(objs, lights)
         print(json.dumps(line), flush=True)
