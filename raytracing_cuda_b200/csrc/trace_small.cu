@@ -402,18 +402,117 @@ __device__ __forceinline__ void rs_light_cell(const RtSceneDev& sc, const RtFram
 #endif
 }
 
-template <int RS_CULL_CHUNKS>
+/* ---- mirror bins.  A primary ray that hits plane 0 (the reference's sea, scene.cpp:183-190) at P continues as
+ * P + 0.001 r, r = normalize(d - 2 (N.d) N) (kernel.cu:212-213).  With a unit normal that is the mirror image
+ * of the primary ray: its line passes through the eye's image E' behind the plane with the primary direction's
+ * image, so the rays a tile sends off the plane lie in the tile's frustum mirrored, apex E' -- the same cull as
+ * the primary one with the mirrored corners, plus: nothing wholly on E's far side of the plane can be met (the ray
+ * starts on the plane and leaves it towards the eye's side).  Rounding: P sits within |t| 2^-22 (< 1e-3 world
+ * units) of the exact point and r within 2^-23 of the exact direction, both far inside the pad (2^-13 of the
+ * largest coordinate) every plane test here carries.  The exact leaf tests decide; bit-identical to the traversal. */
+struct RsMirror {
+    bool on;            /* plane 0 is a unit-normal, non-emissive mirror */
+    vec3 pn, p0, eye_m; /* its normal, a point on it, the eye's image */
+    float pad_m, side;  /* side: +1 / -1 = the eye's side of the plane, 0 = eye (nearly) in the plane: no side cull */
+};
+
+__device__ __forceinline__ RsMirror rs_mirror_of(const RtSceneDev& sc, const vec3& eye, float pad, bool want) {
+    RsMirror m;
+    m.on = false;
+    m.pn = m.p0 = v3(0, 0, 0);
+    float hgt = 0.0f;
+    if (want && sc.n_planes > 0) {
+        const float4 q0 = __ldg(sc.planes), q1 = __ldg(sc.planes + 1);
+        const unsigned int tag = __float_as_uint(q0.w);
+        m.pn = f4xyz(q1);
+        m.p0 = f4xyz(q0);
+        const float mirror = __ldg(sc.mats + 2 * (tag & RT_TAG_INDEX)).w;
+        hgt = vdot(vsub(eye, m.p0), m.pn);
+        m.on = mirror > 0.0f && !(tag & RT_TAG_EMISSIVE) && fabsf(vdot(m.pn, m.pn) - 1.0f) <= 1e-6f;
+    }
+    m.eye_m = vsub(eye, vscale(m.pn, 2.0f * hgt));
+    const float apex_m[3] = {m.eye_m.x, m.eye_m.y, m.eye_m.z};
+    m.pad_m = fmaxf(pad, rs_cull_pad(sc, apex_m));
+    m.side = hgt > m.pad_m ? 1.0f : (hgt < -m.pad_m ? -1.0f : 0.0f);
+    return m;
+}
+
+__device__ __forceinline__ RsFrustum rs_mirror_frustum(const RsMirror& m, const vec3* corner) {
+    vec3 corner_m[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) corner_m[k] = vsub(corner[k], vscale(m.pn, 2.0f * vdot(corner[k], m.pn)));
+    return rs_frustum_from_corners(corner_m);
+}
+
+/* One CTA = a block of RS_CB_W x RS_CB_H bins (256 x 32 pixels), one warp per bin.  Two levels: the CTA tests every
+ * primitive (one per thread) against the frusta of the whole BLOCK and keeps the survivors, in index order, in shared
+ * memory; each warp then tests only those against its bin.  A warp walking all primitives for both of its lists ran
+ * ~1,900 instructions in series (3.9 M warp instructions per 1080p frame, ncu) -- the pre-pass is that chain, and the
+ * tracer behind it waits for its last CTA; most of a block's primitives fail the block test already. */
+#define RS_CB_W 4
+#define RS_CB_H 2
+
 __device__ __forceinline__ void
-rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restrict__ tile_lists, int tiles_x,
-            int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
-            int work_tiles_x, int work_tiles_y, unsigned short* __restrict__ mirror_lists) {
-    /* tiles_x, n_tiles count BINS here; work_list = NULL for whole frames; mirror_lists = NULL: no mirror bins */
-    const int lane = threadIdx.x & 31;
-    const int tile = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (tile >= n_tiles) return;
+rs_cull_block(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restrict__ tile_lists, int bins_x, int bins_y,
+              unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count, int work_tiles_x,
+              int work_tiles_y, unsigned short* __restrict__ mirror_lists, int block_id) {
+    /* work_list = NULL for whole frames; mirror_lists = NULL: no mirror bins */
+    __shared__ unsigned short s_surv[2][RT_SMALL_MAX_PRIMS];   /* [0] primary, [1] mirror survivors of the block */
+    __shared__ unsigned int s_ball[2][8];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
+    const int prims_off = 64 * n_nodes;
+    const int cbx = (bins_x + RS_CB_W - 1) / RS_CB_W;
+    const int cy = block_id / cbx, cx = block_id - cy * cbx;
+    const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
+    const float pad = rs_cull_pad(sc, f.pos);
+    const RsMirror mir = rs_mirror_of(sc, eye, pad, mirror_lists != nullptr);
+    {
+        const int x0 = cx * RS_CB_W * RT_SMALL_BIN_W, y0 = cy * RS_CB_H * RT_SMALL_BIN_H;
+        const int x1 = min(x0 + RS_CB_W * RT_SMALL_BIN_W - 1, f.imgw - 1), y1 = min(y0 + RS_CB_H * RT_SMALL_BIN_H - 1, f.imgh - 1);
+        vec3 corner[4];
+        rs_tile_corners(f, x0, y0, x1, y1, corner);
+        const RsFrustum fb = rs_frustum_from_corners(corner);
+        const RsFrustum fmb = rs_mirror_frustum(mir, corner);
+        const int j = threadIdx.x;                /* n <= RT_SMALL_MAX_PRIMS = the CTA's threads */
+        bool kp = false, km = false;
+        if (j < n) {
+            const float4 r0 = __ldg(sc.prims + 3 * j), r1 = __ldg(sc.prims + 3 * j + 1), r2 = __ldg(sc.prims + 3 * j + 2);
+            kp = !fb.ok || rs_tile_may_hit(fb, eye, r0, r1, r2, pad);
+            if (mir.on) {
+                km = !(fb.ok && fmb.ok) || rs_tile_may_hit(fmb, mir.eye_m, r0, r1, r2, mir.pad_m);
+                if (km && mir.side != 0.0f) {
+                    const float ha = mir.side * vdot(vsub(f4xyz(r0), mir.p0), mir.pn);
+                    if (__float_as_uint(r0.w) & RT_TAG_SPHERE) {
+                        km = !(ha < -(fabsf(r1.x) + mir.pad_m));
+                    } else {
+                        const float hb = ha + mir.side * vdot(f4xyz(r1), mir.pn), hc = ha + mir.side * vdot(f4xyz(r2), mir.pn);
+                        km = !(ha < -mir.pad_m && hb < -mir.pad_m && hc < -mir.pad_m);
+                    }
+                }
+            }
+        }
+        const unsigned int bp = __ballot_sync(0xffffffffu, kp), bm = __ballot_sync(0xffffffffu, km);
+        if (lane == 0) { s_ball[0][warp] = bp; s_ball[1][warp] = bm; }
+        __syncthreads();
+        int op = 0, om = 0;
+#pragma unroll
+        for (int w = 0; w < 8; w++)
+            if (w < warp) { op += __popc(s_ball[0][w]); om += __popc(s_ball[1][w]); }
+        const unsigned int below = (1u << lane) - 1u;
+        if (kp) s_surv[0][op + __popc(bp & below)] = (unsigned short)j;
+        if (km) s_surv[1][om + __popc(bm & below)] = (unsigned short)j;
+        __syncthreads();
+    }
+    int ns0 = 0, ns1 = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) { ns0 += __popc(s_ball[0][w]); ns1 += __popc(s_ball[1][w]); }
+
+    const int bbx = cx * RS_CB_W + warp % RS_CB_W, bby = cy * RS_CB_H + warp / RS_CB_W;
+    if (bbx >= bins_x || bby >= bins_y) return;
+    const int tile = bby * bins_x + bbx;
     /* The work tiles (16x8) of this bin that hold at least one pixel to trace: all of them, or with a
      * screen-tile shard those with own pixels or pixels of the 1-pixel FXAA apron. */
-    const int bby = tile / tiles_x, bbx = tile - bby * tiles_x;
     const int wx = bbx * (RT_SMALL_BIN_W / RT_SMALL_TILE_W) + lane % (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
     const int wy = bby * (RT_SMALL_BIN_H / RT_SMALL_TILE_H) + lane / (RT_SMALL_BIN_W / RT_SMALL_TILE_W);
     bool need = lane < (RT_SMALL_BIN_W / RT_SMALL_TILE_W) * (RT_SMALL_BIN_H / RT_SMALL_TILE_H) && wx < work_tiles_x &&
@@ -437,104 +536,41 @@ rs_cull_bin(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restric
         if (need) work_list[at] = (unsigned int)(wy * work_tiles_x + wx);
     }
     if (need_mask == 0u) return;                 /* nothing of this bin is traced here: no list needed either */
-    const int n = sc.n_bvh_prims, n_nodes = n > 1 ? n - 1 : 0;
-    const int prims_off = 64 * n_nodes;
-    const float pad = rs_cull_pad(sc, f.pos);
     const int x0 = bbx * RT_SMALL_BIN_W, y0 = bby * RT_SMALL_BIN_H;
     const int x1 = min(x0 + RT_SMALL_BIN_W - 1, f.imgw - 1), y1 = min(y0 + RT_SMALL_BIN_H - 1, f.imgh - 1);
-    const vec3 eye = v3(f.pos[0], f.pos[1], f.pos[2]);
     vec3 corner[4];
     rs_tile_corners(f, x0, y0, x1, y1, corner);
     const RsFrustum fr = rs_frustum_from_corners(corner);
     unsigned short* __restrict__ out = tile_lists + (size_t)tile * RT_SMALL_LIST;
-
-    /* ---- mirror bins.  A primary ray that hits plane 0 (the reference's sea, scene.cpp:183-190) at P continues as
-     * P + 0.001 r, r = normalize(d - 2 (N.d) N) (kernel.cu:212-213).  With a unit normal that is the mirror image
-     * of the primary ray: its line passes through the eye's image E' behind the plane with the primary direction's
-     * image, so the rays a tile sends off the plane lie in the tile's frustum mirrored, apex E' -- the same cull as
-     * the primary one with the mirrored corners, plus: nothing wholly on E's far side of the plane can be met (the ray
-     * starts on the plane and leaves it towards the eye's side).  Rounding: P sits within |t| 2^-22 (< 1e-3 world
-     * units) of the exact point and r within 2^-23 of the exact direction, both far inside the pad (2^-13 of the
-     * largest coordinate) every plane test here carries.  The exact leaf tests decide; bit-identical to the traversal. */
-    unsigned short* __restrict__ mout = mirror_lists ? mirror_lists + (size_t)tile * RT_SMALL_LIST : (unsigned short*)nullptr;
-    bool on = false;
-    vec3 pn = v3(0, 0, 0), p0 = v3(0, 0, 0);
-    float hgt = 0.0f;
-    if (mout && sc.n_planes > 0 && fr.ok) {
-        const float4 q0 = __ldg(sc.planes), q1 = __ldg(sc.planes + 1);
-        const unsigned int tag = __float_as_uint(q0.w);
-        pn = f4xyz(q1);
-        p0 = f4xyz(q0);
-        const float mirror = __ldg(sc.mats + 2 * (tag & RT_TAG_INDEX)).w;
-        hgt = vdot(vsub(eye, p0), pn);
-        on = mirror > 0.0f && !(tag & RT_TAG_EMISSIVE) && fabsf(vdot(pn, pn) - 1.0f) <= 1e-6f;
+    int count = 0;
+    for (int i0 = 0; i0 < ns0; i0 += 32) {
+        const int i = i0 + lane;
+        const int j = s_surv[0][min(i, ns0 - 1)];
+        const bool keep = i < ns0 && (!fr.ok || rs_tile_may_hit(fr, eye, sc.prims + 3 * j, pad));
+        const unsigned int m = __ballot_sync(0xffffffffu, keep);
+        const int at = count + __popc(m & ((1u << lane) - 1u));
+        if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
+        count += __popc(m);
     }
-    const vec3 eye_m = vsub(eye, vscale(pn, 2.0f * hgt));
-    vec3 corner_m[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) corner_m[k] = vsub(corner[k], vscale(pn, 2.0f * vdot(corner[k], pn)));
-    const RsFrustum frm = rs_frustum_from_corners(corner_m);
-    const float apex_m[3] = {eye_m.x, eye_m.y, eye_m.z};
-    const float pad_m = fmaxf(pad, rs_cull_pad(sc, apex_m));
-    const float side = hgt > pad_m ? 1.0f : (hgt < -pad_m ? -1.0f : 0.0f);   /* eye (nearly) in the plane: no side cull */
-
-    /* Every lane first loads the records of RS_CULL_CHUNKS of its primitives (lane, lane + 32, ...), then tests them
-     * against both frusta: with 4, one L2 round trip per 128 primitives instead of one per 32 and list (the pre-pass
-     * is a chain of latencies, and the tracer behind it waits for its last CTA). */
-    /* One chunk at a time (large frames: register budget of 4 CTAs per SM) walks the primitives twice, once per list,
-     * as round 1 did: fusing the two tests there cost 0.3 % of the 4K frame. */
-    constexpr bool FUSED = RS_CULL_CHUNKS > 1;
-    int count = 0, mcount = 0;
-#pragma unroll
-    for (int pass = 0; pass < (FUSED ? 1 : 2); pass++) {
-        const bool primary = FUSED || pass == 0, mirrored = on && (FUSED || pass == 1);
-        if (!primary && !mirrored) break;
-        for (int c0 = 0; c0 < n; c0 += 32 * RS_CULL_CHUNKS) {
-            float4 r0[RS_CULL_CHUNKS], r1[RS_CULL_CHUNKS], r2[RS_CULL_CHUNKS];
-#pragma unroll
-            for (int c = 0; c < RS_CULL_CHUNKS; c++) {
-                if (c0 + c * 32 < n) {
-                    const float4* __restrict__ rec = sc.prims + 3 * min(c0 + c * 32 + lane, n - 1);
-                    r0[c] = __ldg(rec);
-                    r1[c] = __ldg(rec + 1);
-                    r2[c] = __ldg(rec + 2);
-                }
-            }
-#pragma unroll
-            for (int c = 0; c < RS_CULL_CHUNKS; c++) {
-                if (c0 + c * 32 >= n) continue;
-                const int j = c0 + c * 32 + lane;
-                if (primary) {
-                    const bool keep = j < n && (!fr.ok || rs_tile_may_hit(fr, eye, r0[c], r1[c], r2[c], pad));
-                    const unsigned int m = __ballot_sync(0xffffffffu, keep);
-                    const int at = count + __popc(m & ((1u << lane) - 1u));
-                    if (keep && at < RT_SMALL_LIST - 1) out[1 + at] = (unsigned short)(prims_off + RS_LEAF * j);
-                    count += __popc(m);
-                }
-                if (mirrored) {
-                    bool mkeep = j < n;
-                    if (mkeep && frm.ok) mkeep = rs_tile_may_hit(frm, eye_m, r0[c], r1[c], r2[c], pad_m);
-                    if (mkeep && side != 0.0f) {
-                        const float ha = side * vdot(vsub(f4xyz(r0[c]), p0), pn);
-                        if (__float_as_uint(r0[c].w) & RT_TAG_SPHERE) {
-                            mkeep = !(ha < -(fabsf(r1[c].x) + pad_m));
-                        } else {
-                            const float hb = ha + side * vdot(f4xyz(r1[c]), pn), hc = ha + side * vdot(f4xyz(r2[c]), pn);
-                            mkeep = !(ha < -pad_m && hb < -pad_m && hc < -pad_m);
-                        }
-                    }
-                    const unsigned int mm = __ballot_sync(0xffffffffu, mkeep);
-                    const int mat = mcount + __popc(mm & ((1u << lane) - 1u));
-                    if (mkeep && mat < RT_SMALL_LIST - 1) mout[1 + mat] = (unsigned short)(prims_off + RS_LEAF * j);
-                    mcount += __popc(mm);
-                }
-            }
-        }
+    if (lane == 0) out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
+    if (!mirror_lists) return;
+    unsigned short* __restrict__ mout = mirror_lists + (size_t)tile * RT_SMALL_LIST;
+    if (!(mir.on && fr.ok)) {
+        if (lane == 0) mout[0] = (unsigned short)0xFFFFu;       /* traverse */
+        return;
     }
-    if (lane == 0) {
-        out[0] = count < RT_SMALL_LIST ? (unsigned short)count : (unsigned short)0xFFFFu;
-        if (mout) mout[0] = on && mcount < RT_SMALL_LIST ? (unsigned short)mcount : (unsigned short)0xFFFFu;   /* 0xFFFF: traverse */
+    const RsFrustum frm = rs_mirror_frustum(mir, corner);
+    int mcount = 0;
+    for (int i0 = 0; i0 < ns1; i0 += 32) {
+        const int i = i0 + lane;
+        const int j = s_surv[1][min(i, ns1 - 1)];
+        const bool mkeep = i < ns1 && (!frm.ok || rs_tile_may_hit(frm, mir.eye_m, sc.prims + 3 * j, mir.pad_m));
+        const unsigned int mm = __ballot_sync(0xffffffffu, mkeep);
+        const int mat = mcount + __popc(mm & ((1u << lane) - 1u));
+        if (mkeep && mat < RT_SMALL_LIST - 1) mout[1 + mat] = (unsigned short)(prims_off + RS_LEAF * j);
+        mcount += __popc(mm);
     }
+    if (lane == 0) mout[0] = mcount < RT_SMALL_LIST ? (unsigned short)mcount : (unsigned short)0xFFFFu;
 }
 
 #ifdef RS_TIMELINE
@@ -570,13 +606,9 @@ extern "C" cudaError_t rt_debug_timeline_small(unsigned long long* out, int rese
 /* (Round 2 measured a second instantiation without the light cells -- no shared memory, 128-thread CTAs of 7 K
  * registers that become resident beside the previous frame's FXAA CTAs instead of queueing behind them: the pre-pass
  * alone got 2 us faster and the bench step 0.5 % SLOWER, 53.97 vs 54.25 Grays/s; profiles/r02_frame_timeline.txt.) */
-/* CHUNKS = 4 (119 registers, 2 CTAs per SM): frames whose bins fit one wave of those (1920x1080: 255 CTAs).
- * CHUNKS = 1 (4 CTAs per SM): larger frames, where the number of waves decides (3840x2160: 1,020 CTAs; the 4-chunk
- * kernel took 31 instead of 26 us there). */
-template <int CHUNKS>
-__global__ void __launch_bounds__(256, CHUNKS > 1 ? 2 : 4)
-rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int tiles_x,
-                     int n_tiles, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
+__global__ void __launch_bounds__(256, 4)
+rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __restrict__ tile_lists, int bins_x,
+                     int bins_y, unsigned int* __restrict__ work_list, unsigned int* __restrict__ work_count,
                      int work_tiles_x, int work_tiles_y, int wait_first, uint4* __restrict__ lgrid,
                      int n_cull_blocks, unsigned short* __restrict__ mirror_lists) {
 #ifdef RS_TIMELINE
@@ -588,7 +620,8 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
 #endif
     /* the CTAs behind the screen bins fill the light bins (lgrid != NULL), one coarse cell each */
     if ((int)blockIdx.x >= n_cull_blocks) rs_light_cell(sc, f, lgrid, (int)blockIdx.x - n_cull_blocks);
-    else rs_cull_bin<CHUNKS>(sc, f, tile_lists, tiles_x, n_tiles, work_list, work_count, work_tiles_x, work_tiles_y, mirror_lists);
+    else rs_cull_block(sc, f, tile_lists, bins_x, bins_y, work_list, work_count, work_tiles_x, work_tiles_y, mirror_lists,
+                       (int)blockIdx.x);
 #ifdef RS_TIMELINE
     __syncthreads();
     if (threadIdx.x == 0) atomicMax(tl_slot() + 1, tl_now());
@@ -1039,8 +1072,7 @@ extern "C" cudaError_t rt_trace_small_init(void) {
     /* Every kernel of the frame chain asks for the SAME shared-memory carve-out (the largest, what the tracer needs).
      * Two kernels with different carve-outs cannot share an SM, so a dependent launch could not become resident
      * under its predecessor's tail: see rt_fxaa_init. */
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_cull_tiles_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(rt_trace_small_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
@@ -1093,14 +1125,15 @@ extern "C" cudaError_t rt_launch_trace_small(const RtSceneDev* sc, const RtFrame
     cfg.attrs = pdl;
     cfg.numAttrs = 1;
     const bool with_lights = lgrid && build_lgrid;
-    const int cull_blocks = (bins + 7) / 8;
+    const int bins_y = (f->imgh + RT_SMALL_BIN_H - 1) / RT_SMALL_BIN_H;
+    const int cull_blocks = ((bins_x + RS_CB_W - 1) / RS_CB_W) * ((bins_y + RS_CB_H - 1) / RS_CB_H);
     const int lit = f->n_lights < RT_LGRID_LIGHTS ? f->n_lights : RT_LGRID_LIGHTS;    /* lights with bins */
     /* build_lgrid = 0: the light bins in `lgrid` are still those of this scene and these lights (api.cu) */
     cfg.gridDim = dim3(cull_blocks + (with_lights ? lit * RS_LG_BLOCKS_PER_LIGHT : 0), 1, 1);
     cfg.blockDim = dim3(256, 1, 1);
     cfg.dynamicSmemBytes = 0;
     RT_LAUNCHED(2);                              /* pre-pass + tracer */
-    cudaError_t e = cudaLaunchKernelEx(&cfg, (int)cfg.gridDim.x <= 2 * n_sm ? rt_cull_tiles_kernel<4> : rt_cull_tiles_kernel<1>, *sc, *f, tile_lists, bins_x, bins,
+    cudaError_t e = cudaLaunchKernelEx(&cfg, rt_cull_tiles_kernel, *sc, *f, tile_lists, bins_x, bins_y,
                                        sharded ? work_list : (unsigned int*)nullptr, tile_counter + RS_CNT_TILES, tiles_x,
                                        tiles_y, after_own_post ? 0 : 1, lgrid, cull_blocks, mirror_lists);
     if (e != cudaSuccess) return e;
