@@ -615,9 +615,7 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
     if (threadIdx.x == 0) atomicMin(tl_slot() + 0, tl_now());
 #endif
     if (wait_first) rs_griddep_wait();
-#ifndef RS_LATE_TRIGGER
     rs_griddep_launch();                         /* the tracer may start staging the scene */
-#endif
     /* the CTAs behind the screen bins fill the light bins (lgrid != NULL), one coarse cell each */
     if ((int)blockIdx.x >= n_cull_blocks) rs_light_cell(sc, f, lgrid, (int)blockIdx.x - n_cull_blocks);
     else rs_cull_block(sc, f, tile_lists, bins_x, bins_y, work_list, work_count, work_tiles_x, work_tiles_y, mirror_lists,
@@ -626,10 +624,10 @@ rt_cull_tiles_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned short* __
     __syncthreads();
     if (threadIdx.x == 0) atomicMax(tl_slot() + 1, tl_now());
 #endif
+    /* Every CTA waits, not just one: with the others gone early the pre-pass ends 4 us sooner at 3840x2160, but the
+     * tracer's CTAs then find the SMs' shared memory in pieces more often (7..12 of 592 become resident only at
+     * the frame's end) and the frame gets 0.2 % slower (profiles/r02_frame_timeline.txt). */
     rs_griddep_wait();
-#ifdef RS_LATE_TRIGGER
-    rs_griddep_launch();
-#endif
 }
 
 /* ---------------------------------------------------------------- ray queue (compaction)
