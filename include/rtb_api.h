@@ -79,7 +79,8 @@ enum {
     RT_OPT_COMPACTION = 12, /* ray compaction in the shared-memory tracer: 0 = every lane follows its own pixel's chain to the end (default), 1 = rays of the second and later generations that have to traverse the hierarchy are parked in a per-CTA shared-memory queue (ballot + popc slot assignment) and traced 32 at a time by full warps.  Measured SLOWER on every BASELINE view (full warps, but rays of unrelated patches: the traversal loses the coherence an 8x4 patch has), hence opt-in.  Scheduling only: identical pixels */
     RT_OPT_PACKET = 13, /* persistent tracer of big scenes: 0 = the 32 primary rays of an 8x4 patch walk the hierarchy as ONE packet (warp-uniform node, one stack per warp, broadcast node loads; default), 1 = every lane traverses for itself.  Identical pixels */
     RT_OPT_BIG_STACK = 14, /* persistent tracer of big scenes, per-lane traversal stack: 0 = local memory (default), 1 = first 16 entries in shared memory.  Identical pixels */
-    RT_OPT_N = 15
+    RT_OPT_WIDE_BVH = 15,  /* plain tracer of big scenes: 0 = walks the binary LBVH (default), 1 = walks a 4-wide view of it (one 128-byte node per visit holding the boxes of the grandchildren; rebuilt after every rt_set_scene, 128 bytes per primitive) -- measured 37 % slower on the million-triangle terrain, hence opt-in.  Identical pixels */
+    RT_OPT_N = 16
 };
 
 /* One frame's uniforms: what launchKernel receives by value / as small host arrays. */

@@ -23,6 +23,7 @@ RT_OPT_LIGHT_BINS_REUSE = 11
 RT_OPT_COMPACTION = 12
 RT_OPT_PACKET = 13
 RT_OPT_BIG_STACK = 14
+RT_OPT_WIDE_BVH = 15
 RT_PEER_HANDLE_BYTES = 64
 RT_MAX_SLOTS = 8
 RT_SORT_STATIC_MAX = 1 << 20

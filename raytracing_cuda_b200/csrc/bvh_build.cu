@@ -932,3 +932,55 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
                                                       b->nodes, b->node_aux, b->prims, b->depth);
     return cudaGetLastError();
 }
+
+/* ------------------------------------------------------------------ 4-wide view of the hierarchy
+ * Wide node i = binary node i with each internal child replaced by that child's two children: 2..4 boxes and links
+ * in one 128-byte line (layout: rt_device.h, RT_WIDE_F4).  The boxes are copied bit for bit from the binary nodes, a
+ * link >= 0 names a binary node = its wide node.  Only the wide nodes of the root, its grandchildren, their
+ * grandchildren ... are ever visited; all n - 1 are written (one thread each, no dependency between them), which
+ * costs memory, not time.  Re-run after every build or refit. */
+__global__ void __launch_bounds__(256)
+rt_collapse_wide_kernel(const float* __restrict__ nodes, int n_internal, float4* __restrict__ wide) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_internal) return;
+    const float4* __restrict__ me = (const float4*)(nodes + 16 * (size_t)i);
+    float4 q[4] = {__ldg(me), __ldg(me + 1), __ldg(me + 2), __ldg(me + 3)};
+    const float* mine = (const float*)q;
+    float box[24];
+    int link[4] = {RT_NODE_SENTINEL, RT_NODE_SENTINEL, RT_NODE_SENTINEL, RT_NODE_SENTINEL};
+#pragma unroll
+    for (int k = 0; k < 24; k++) box[k] = 0.0f;
+    int at = 0;
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        const int l = __float_as_int(mine[12 + c]);
+        if (l >= 0) {
+            const float4* __restrict__ ch = (const float4*)(nodes + 16 * (size_t)l);
+            float4 r[4] = {__ldg(ch), __ldg(ch + 1), __ldg(ch + 2), __ldg(ch + 3)};
+            const float* g = (const float*)r;
+#pragma unroll
+            for (int k = 0; k < 12; k++) box[6 * at + k] = g[k];
+            link[at] = __float_as_int(g[12]);
+            link[at + 1] = __float_as_int(g[13]);
+            at += 2;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 6; k++) box[6 * at + k] = mine[6 * c + k];
+            link[at] = l;
+            at += 1;
+        }
+    }
+    float4* __restrict__ w = wide + (size_t)RT_WIDE_F4 * i;
+#pragma unroll
+    for (int k = 0; k < 6; k++) w[k] = make_float4(box[4 * k], box[4 * k + 1], box[4 * k + 2], box[4 * k + 3]);
+    w[6] = make_float4(__int_as_float(link[0]), __int_as_float(link[1]), __int_as_float(link[2]), __int_as_float(link[3]));
+    w[7] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
+extern "C" cudaError_t rt_collapse_wide(const float* nodes, int n_prims, float4* wide, cudaStream_t stream) {
+    if (n_prims < 2) return cudaSuccess;
+    const int n_internal = n_prims - 1;
+    RT_LAUNCHED(1);
+    rt_collapse_wide_kernel<<<(n_internal + 255) / 256, 256, 0, stream>>>(nodes, n_internal, wide);
+    return cudaGetLastError();
+}

@@ -104,7 +104,15 @@ struct RtSceneDev {
     /* 4 uints per light, written by the build itself (rt_lgb_finish_kernel): [0] = 1 when the light's lists are
      * complete and may be used, else its shadow rays traverse; [1] entries, [2] overflow flag */
     const unsigned int* lg_state;
+    /* 4-wide view of the hierarchy (rt_collapse_wide, bvh_build.cu), NULL: none.  Wide node i (RT_WIDE_F4 float4,
+     * 128 bytes) belongs to binary node i and holds the boxes and links of its grandchildren (a child that is a
+     * leaf stands for itself), so a ray makes one dependent fetch where the binary walk makes two. */
+    const float4* wide;
+    unsigned int* err;     /* device error word (RT_DEVICE_ERROR_WORD of the context's counter block) */
 };
+/* wide node: [0..5] four boxes, 6 floats each (centre xyz, half-extent xyz) packed back to back; [6] the four links as
+ * ints (>= 0 wide node, < 0 ~leaf slot, RT_NODE_SENTINEL: no child); [7] unused (one node = one 128-byte line) */
+#define RT_WIDE_F4 8
 
 struct RtLightDev {
     float px, py, pz, intensity;

@@ -20,8 +20,8 @@
 
 #define RT_TRACE_THREADS 256
 
-template <bool BRUTE, bool COUNT>
-__global__ void __launch_bounds__(RT_TRACE_THREADS)
+template <bool BRUTE, bool COUNT, bool WIDE>
+__global__ void __launch_bounds__(RT_TRACE_THREADS, COUNT ? 1 : 4)
 rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restrict__ image,
                 int* __restrict__ hit_ids, RtCountersDev* __restrict__ counters, unsigned int* __restrict__ err, int packet) {
     __shared__ float4 s_pending[RTB_MAX_DEPTH * RT_TRACE_THREADS];   /* (phong.rgb, kR) per depth */
@@ -35,7 +35,7 @@ rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restric
     if (!packet && !mine) return;
 
     RtPixelCounters pc = {{0, 0, 0, 0, 0, 0, 0, 0, 0}, 0, 0, 0, 0};
-    RtGlobalPacketScene<BRUTE, COUNT> acc(sc);
+    RtGlobalPacketScene<BRUTE, COUNT, WIDE> acc(sc);
     if (!BRUTE && packet) {
         /* the patch's 32 primary rays walk the hierarchy as one packet (rt_packet_closest, trace_global.cuh) */
         if (!__any_sync(0xffffffffu, mine)) return;
@@ -61,7 +61,7 @@ rt_trace_kernel(const RtSceneDev sc, const RtFrameDev f, unsigned int* __restric
     unsigned long long tm_t0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tm_t0));
 #endif
-    image[y * f.imgw + x] = rt_trace_pixel<RtGlobalPacketScene<BRUTE, COUNT>, COUNT>(acc, f, x, y, s_pending, RT_TRACE_THREADS,
+    image[y * f.imgw + x] = rt_trace_pixel<RtGlobalPacketScene<BRUTE, COUNT, WIDE>, COUNT>(acc, f, x, y, s_pending, RT_TRACE_THREADS,
                                                                                     threadIdx.x, hit_ids, pc);
 #ifdef RT_TIMEMAP
     if (hit_ids) {   /* debug variant: ns this pixel's thread took */
@@ -83,11 +83,14 @@ extern "C" cudaError_t rt_launch_trace(const RtSceneDev* sc, const RtFrameDev* f
     dim3 grid((f->imgw + 31) / 32, (f->imgh + 7) / 8, 1);
     RT_LAUNCHED(1);
     if (brute) {
-        if (count) rt_trace_kernel<true, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
-        else       rt_trace_kernel<true, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        if (count) rt_trace_kernel<true, true, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        else       rt_trace_kernel<true, false, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+    } else if (sc->wide) {           /* the 4-wide view of the hierarchy is there (RT_OPT_WIDE_BVH, api.cu): walk that */
+        if (count) rt_trace_kernel<false, true, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        else       rt_trace_kernel<false, false, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
     } else {
-        if (count) rt_trace_kernel<false, true><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
-        else       rt_trace_kernel<false, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        if (count) rt_trace_kernel<false, true, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
+        else       rt_trace_kernel<false, false, false><<<grid, block, 0, stream>>>(*sc, *f, image, hit_ids, counters, err, packet);
     }
     return cudaGetLastError();
 }

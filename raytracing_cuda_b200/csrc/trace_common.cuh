@@ -142,8 +142,106 @@ __device__ __forceinline__ bool rt_traverse(const RtSceneDev& sc, const vec3& o,
     return rt_traverse_loop<ANY, COUNT, false>(sc, rb, o, d, best, tmax, cnt);
 }
 
+/* The same walk over the 4-wide view (RtSceneDev.wide): one fetch of 7 float4 brings the boxes of up to four
+ * grandchildren; the ones the ray meets are visited nearest first (closest hit) or in any order (ANY).  The boxes are
+ * the binary hierarchy's own and the leaf tests decide, so the result is the binary walk's, bit for bit. */
+template <bool ANY, bool COUNT, bool ROBUST>
+__device__ __forceinline__ bool rt_traverse_wide_loop(const RtSceneDev& sc, const RtRayBox& rb, const vec3& o, const vec3& d,
+                                                      RtHit& best, float tmax, RtLocalCounters& cnt) {
+    int node = sc.root;
+    int stack[RT_STACK_SIZE];
+    int sp = 0;
+    const float4* __restrict__ wide = sc.wide;
+    while (true) {
+        if (node >= 0) {
+            const float4* __restrict__ w = wide + (size_t)RT_WIDE_F4 * node;
+            const float4 a0 = __ldg(w), a1 = __ldg(w + 1), a2 = __ldg(w + 2), a3 = __ldg(w + 3), a4 = __ldg(w + 4),
+                         a5 = __ldg(w + 5);
+            const int4 ln = __ldg((const int4*)(w + 6));
+            const float lim = ANY ? tmax : fmaxf(best.t, 0.0f);
+            float t0, t1, t2, t3;
+            bool h0 = ROBUST ? rt_slab_robust(rb, a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, lim, t0)
+                             : rt_slab(rb, a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, lim, t0);
+            bool h1 = ROBUST ? rt_slab_robust(rb, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w, lim, t1)
+                             : rt_slab(rb, a1.z, a1.w, a2.x, a2.y, a2.z, a2.w, lim, t1);
+            bool h2 = ROBUST ? rt_slab_robust(rb, a3.x, a3.y, a3.z, a3.w, a4.x, a4.y, lim, t2)
+                             : rt_slab(rb, a3.x, a3.y, a3.z, a3.w, a4.x, a4.y, lim, t2);
+            bool h3 = ROBUST ? rt_slab_robust(rb, a4.z, a4.w, a5.x, a5.y, a5.z, a5.w, lim, t3)
+                             : rt_slab(rb, a4.z, a4.w, a5.x, a5.y, a5.z, a5.w, lim, t3);
+            h2 = h2 && ln.z != RT_NODE_SENTINEL;          /* slots 0 and 1 always hold a child */
+            h3 = h3 && ln.w != RT_NODE_SENTINEL;
+            if (COUNT) cnt.node_tests += 2 + (ln.z != RT_NODE_SENTINEL) + (ln.w != RT_NODE_SENTINEL);
+            int c0 = ln.x, c1 = ln.y, c2 = ln.z, c3 = ln.w;
+            const float inf = __int_as_float(0x7f800000);
+            if (!h0) t0 = inf;
+            if (!h1) t1 = inf;
+            if (!h2) t2 = inf;
+            if (!h3) t3 = inf;
+#ifdef RT_WIDE_NEAREST_ONLY
+            if (!ANY) {
+                /* the nearest child to the front, the others in slot order */
+#define RT_CSWAP(ta, ca, tb, cb) do { if (tb < ta) { const float tt = ta; ta = tb; tb = tt; const int cc = ca; ca = cb; cb = cc; } } while (0)
+                RT_CSWAP(t0, c0, t1, c1);
+                RT_CSWAP(t0, c0, t2, c2);
+                RT_CSWAP(t0, c0, t3, c3);
+#undef RT_CSWAP
+            } else {
+#else
+            if (!ANY) {
+                /* sort the four (t, link) pairs by t, misses (t = inf) last: 5 compare-exchanges */
+#define RT_CSWAP(ta, ca, tb, cb) do { if (tb < ta) { const float tt = ta; ta = tb; tb = tt; const int cc = ca; ca = cb; cb = cc; } } while (0)
+                RT_CSWAP(t0, c0, t1, c1);
+                RT_CSWAP(t2, c2, t3, c3);
+                RT_CSWAP(t0, c0, t2, c2);
+                RT_CSWAP(t1, c1, t3, c3);
+                RT_CSWAP(t1, c1, t2, c2);
+#undef RT_CSWAP
+            } else {
+#endif
+                /* any order: hits to the front */
+                if (!(t0 < inf)) { if (t1 < inf) { t0 = t1; c0 = c1; t1 = inf; } else if (t2 < inf) { t0 = t2; c0 = c2; t2 = inf; } else if (t3 < inf) { t0 = t3; c0 = c3; t3 = inf; } }
+            }
+            if (t0 < inf) {
+                const int more = (t1 < inf) + (t2 < inf) + (t3 < inf);
+                if (sp + more <= RT_STACK_SIZE) {
+                    if (t3 < inf) stack[sp++] = c3;            /* farthest first: the nearest pops first */
+                    if (t2 < inf) stack[sp++] = c2;
+                    if (t1 < inf) stack[sp++] = c1;
+                } else if (sc.err) {
+                    atomicOr(sc.err, 1u);                       /* never silently: rt_get_device_errors */
+                }
+                node = c0;
+                continue;
+            }
+        } else {
+            const int slot = ~node;
+            float t;
+            unsigned int tag;
+            if (rt_test_record<COUNT>(sc.prims + 3 * (size_t)slot, o, d, t, tag, cnt)) {
+                if (ANY) {
+                    if (!(tag & RT_TAG_EMISSIVE) && t < tmax) return true;
+                } else {
+                    rt_consider(best, t, tag, slot);
+                }
+            }
+        }
+        if (sp == 0) break;
+        node = stack[--sp];
+    }
+    return false;
+}
+
+template <bool ANY, bool COUNT>
+__device__ __forceinline__ bool rt_traverse_wide(const RtSceneDev& sc, const vec3& o, const vec3& d, RtHit& best,
+                                                 float tmax, RtLocalCounters& cnt) {
+    if (sc.root == RT_NODE_SENTINEL) return false;
+    const RtRayBox rb = rt_ray_box(o, d);
+    if (rb.slack > RT_ROBUST_SLACK) return rt_traverse_wide_loop<ANY, COUNT, true>(sc, rb, o, d, best, tmax, cnt);
+    return rt_traverse_wide_loop<ANY, COUNT, false>(sc, rb, o, d, best, tmax, cnt);
+}
+
 /* closest hit over planes + BVH (BRUTE: over all records in original order) */
-template <bool BRUTE, bool COUNT>
+template <bool BRUTE, bool COUNT, bool WIDE = false>
 __device__ __forceinline__ RtHit rt_closest(const RtSceneDev& sc, const vec3& o, const vec3& d,
                                             RtLocalCounters& cnt) {
     RtHit best;
@@ -168,12 +266,13 @@ __device__ __forceinline__ RtHit rt_closest(const RtSceneDev& sc, const vec3& o,
         if (COUNT) cnt.plane_tests++;
         if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t)) rt_consider(best, t, __float_as_uint(q0.w), ~p);
     }
-    rt_traverse<false, COUNT>(sc, o, d, best, 0.0f, cnt);
+    if (WIDE) rt_traverse_wide<false, COUNT>(sc, o, d, best, 0.0f, cnt);
+    else rt_traverse<false, COUNT>(sc, o, d, best, 0.0f, cnt);
     return best;
 }
 
 /* reference kernel.cu:188-193 */
-template <bool BRUTE, bool COUNT>
+template <bool BRUTE, bool COUNT, bool WIDE = false>
 __device__ __forceinline__ bool rt_occluded(const RtSceneDev& sc, const vec3& o, const vec3& d, float tmax,
                                             RtLocalCounters& cnt) {
     if (BRUTE) {
@@ -193,6 +292,7 @@ __device__ __forceinline__ bool rt_occluded(const RtSceneDev& sc, const vec3& o,
         if (rt_hit_plane(o, d, f4xyz(q0), f4xyz(q1), t) && t < tmax) return true;
     }
     RtHit dummy;
+    if (WIDE) return rt_traverse_wide<true, COUNT>(sc, o, d, dummy, tmax, cnt);
     return rt_traverse<true, COUNT>(sc, o, d, dummy, tmax, cnt);
 }
 

@@ -51,8 +51,8 @@ __device__ __forceinline__ int rt_light_grid_occluded(const RtSceneDev& sc, cons
     return 0;
 }
 
-/* scene accessor over the HBM-resident LBVH (any primitive count) */
-template <bool BRUTE, bool COUNT>
+/* scene accessor over the HBM-resident LBVH (any primitive count); WIDE: over its 4-wide view */
+template <bool BRUTE, bool COUNT, bool WIDE = false>
 struct RtGlobalScene {
     const RtSceneDev& sc;
     __device__ __forceinline__ RtGlobalScene(const RtSceneDev& s) : sc(s) {}
@@ -60,19 +60,19 @@ struct RtGlobalScene {
     unsigned int dbg[3] = {0, 0, 0};   /* debug variant: node tests of primary / bounce / shadow rays */
     __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, bool, RtLocalCounters& cnt) {
         const unsigned int before = cnt.node_tests;
-        const RtHit h = rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
+        const RtHit h = rt_closest<BRUTE, COUNT, WIDE>(sc, o, d, cnt);
         dbg[depth ? 1 : 0] += cnt.node_tests - before;
         return h;
     }
     __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3&, int, RtLocalCounters& cnt) {
         const unsigned int before = cnt.node_tests;
-        const bool r = rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
+        const bool r = rt_occluded<BRUTE, COUNT, WIDE>(sc, o, d, tmax, cnt);
         dbg[2] += cnt.node_tests - before;
         return r;
     }
 #else
     __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int, bool, RtLocalCounters& cnt) {
-        return rt_closest<BRUTE, COUNT>(sc, o, d, cnt);
+        return rt_closest<BRUTE, COUNT, WIDE>(sc, o, d, cnt);
     }
     /* to_light = L - P (the vector the caller normalised into d), li = index of the light */
     __device__ __forceinline__ bool occluded(const vec3& o, const vec3& d, float tmax, const vec3& to_light, int li,
@@ -81,7 +81,7 @@ struct RtGlobalScene {
             const int g = rt_light_grid_occluded<COUNT>(sc, o, d, tmax, to_light, li, cnt);
             if (g >= 0) return g != 0;
         }
-        return rt_occluded<BRUTE, COUNT>(sc, o, d, tmax, cnt);
+        return rt_occluded<BRUTE, COUNT, WIDE>(sc, o, d, tmax, cnt);
     }
 #endif
     __device__ __forceinline__ vec3 normal(const RtHit& h, const vec3& P) { return rt_hit_normal<BRUTE>(sc, h, P); }
@@ -148,14 +148,14 @@ __device__ __forceinline__ void rt_packet_closest(const RtSceneDev& sc, bool liv
 }
 
 /* RtGlobalScene whose primary-ray hit is handed in (packet traversal) */
-template <bool BRUTE, bool COUNT>
-struct RtGlobalPacketScene : RtGlobalScene<BRUTE, COUNT> {
+template <bool BRUTE, bool COUNT, bool WIDE = false>
+struct RtGlobalPacketScene : RtGlobalScene<BRUTE, COUNT, WIDE> {
     RtHit primary;
     bool have_primary;
-    __device__ __forceinline__ RtGlobalPacketScene(const RtSceneDev& s) : RtGlobalScene<BRUTE, COUNT>(s), have_primary(false) {}
+    __device__ __forceinline__ RtGlobalPacketScene(const RtSceneDev& s) : RtGlobalScene<BRUTE, COUNT, WIDE>(s), have_primary(false) {}
     __device__ __forceinline__ RtHit closest(const vec3& o, const vec3& d, int depth, bool off, RtLocalCounters& cnt) {
         if (depth == 0 && have_primary) return primary;
-        return RtGlobalScene<BRUTE, COUNT>::closest(o, d, depth, off, cnt);
+        return RtGlobalScene<BRUTE, COUNT, WIDE>::closest(o, d, depth, off, cnt);
     }
 };
 

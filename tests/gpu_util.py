@@ -25,7 +25,7 @@ def renderer(sky=None):
     for k in (_lib.RT_OPT_TRAVERSAL, _lib.RT_OPT_COUNTERS, _lib.RT_OPT_FXAA_IMPL, _lib.RT_OPT_TIMING,
               _lib.RT_OPT_SKY_ALL4, _lib.RT_OPT_TRACE_IMPL, _lib.RT_OPT_BUILDER, _lib.RT_OPT_FORCE_RADIX,
               _lib.RT_OPT_ORDER, _lib.RT_OPT_SHADOW_BINS, _lib.RT_OPT_MIRROR_BINS, _lib.RT_OPT_LIGHT_BINS_REUSE,
-              _lib.RT_OPT_COMPACTION, _lib.RT_OPT_PACKET, _lib.RT_OPT_BIG_STACK):
+              _lib.RT_OPT_COMPACTION, _lib.RT_OPT_PACKET, _lib.RT_OPT_BIG_STACK, _lib.RT_OPT_WIDE_BVH):
         r.set_option(k, 0)
     return r
 

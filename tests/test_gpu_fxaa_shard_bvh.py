@@ -337,7 +337,7 @@ def test_light_grid_of_big_scenes_changes_tested_primitives_only():
 
 
 def test_persistent_packet_tracer_equals_plain_tracer():
-    """The persistent tracer of big scenes (trace_big.cu: warps pulling 8x4 patches, the 32 primary rays of a patch
+    """The plain tracer over the 4-wide view of the LBVH (RT_OPT_WIDE_BVH 1) and the persistent tracer of big scenes (trace_big.cu: warps pulling 8x4 patches, the 32 primary rays of a patch
     walking the LBVH as one packet, per-lane stacks optionally in shared memory; RT_OPT_TRACE_IMPL 3) against the plain one-thread-per-pixel tracer (RT_OPT_TRACE_IMPL 1): pixels and hit ids identical -- the
     terrain from several poses (incl. grazing rays and a camera inside it), packets off (RT_OPT_PACKET 1), the first
     stack entries in shared memory (RT_OPT_BIG_STACK 1), packets inside the plain kernel (RT_OPT_TRACE_IMPL 4), odd frame
@@ -350,10 +350,13 @@ def test_persistent_packet_tracer_equals_plain_tracer():
     def frames(f, o, lights, shard=None):
         outs = []
         r.set_scene(o, lights)
-        for impl, packet, sstack in ((1, 0, 0), (3, 0, 0), (3, 1, 0), (3, 0, 1), (3, 1, 1), (4, 0, 0)):
+        # the first entry is the plain tracer over the binary hierarchy; (1, 0, 0, 1) and (4, 0, 0, 1) walk its 4-wide view
+        for impl, packet, sstack, wide in ((1, 0, 0, 0), (1, 0, 0, 1), (3, 0, 0, 0), (3, 1, 0, 0), (3, 0, 1, 0), (3, 1, 1, 0),
+                                           (4, 0, 0, 0), (4, 0, 0, 1)):
             r.set_option(_lib.RT_OPT_TRACE_IMPL, impl)
             r.set_option(_lib.RT_OPT_PACKET, packet)
             r.set_option(_lib.RT_OPT_BIG_STACK, sstack)
+            r.set_option(_lib.RT_OPT_WIDE_BVH, wide)
             if shard is None:
                 outs.append(r.render_to_host(f, want_ids=True))
             else:
@@ -362,6 +365,7 @@ def test_persistent_packet_tracer_equals_plain_tracer():
         r.set_option(_lib.RT_OPT_TRACE_IMPL, 0)
         r.set_option(_lib.RT_OPT_PACKET, 0)
         r.set_option(_lib.RT_OPT_BIG_STACK, 0)
+        r.set_option(_lib.RT_OPT_WIDE_BVH, 0)
         for k in range(1, len(outs)):
             assert (outs[0][1] == outs[k][1]).all(), (k, int((outs[0][1] != outs[k][1]).sum()))
             assert (outs[0][0] == outs[k][0]).all(), (k, int((outs[0][0] != outs[k][0]).sum()))

@@ -20,9 +20,12 @@ r.set_scene(objs, lights)
 out = torch.empty(f.imgw * f.imgh, dtype=torch.int32, device="cuda")
 ref = None
 for rnd in range(2):
-    for name, impl, packet, sstack in (("plain", 1, 0, 0), ("plain+packet", 4, 0, 0), ("persistent+packet", 3, 0, 0),
-                                       ("persistent, per-lane", 3, 1, 0), ("persistent+packet, smem stack", 3, 0, 1),
-                                       ("persistent, per-lane, smem stack", 3, 1, 1)):
+    for name, impl, packet, sstack, wide in (("plain, binary LBVH", 1, 0, 0, 0), ("plain, 4-wide view", 1, 0, 0, 1),
+                                             ("plain+packet, binary", 4, 0, 0, 0), ("plain+packet, 4-wide", 4, 0, 0, 1),
+                                             ("persistent+packet", 3, 0, 0, 0),
+                                             ("persistent, per-lane", 3, 1, 0, 0), ("persistent+packet, smem stack", 3, 0, 1, 0),
+                                             ("persistent, per-lane, smem stack", 3, 1, 1, 0)):
+        r.set_option(_lib.RT_OPT_WIDE_BVH, wide)
         r.set_option(_lib.RT_OPT_TRACE_IMPL, impl)
         r.set_option(_lib.RT_OPT_PACKET, packet)
         r.set_option(_lib.RT_OPT_BIG_STACK, sstack)
