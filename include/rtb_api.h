@@ -69,7 +69,7 @@ enum {
     RT_OPT_FXAA_IMPL = 2,   /* 0 = TMA-staged (default when width%4==0), 1 = plain shared-memory */
     RT_OPT_TIMING    = 3,   /* 1 = record CUDA events around trace and fxaa */
     RT_OPT_SKY_ALL4  = 4,   /* 1 = fetch all four sky maps like the reference (default 0: only non-zero weights; bit-identical) */
-    RT_OPT_TRACE_IMPL = 5,  /* 0 = auto: shared-memory tracer when the scene fits (<= ~165 primitives), else the plain one-thread-per-pixel tracer over the HBM-resident LBVH; 1 = the plain tracer for any scene (no lists, no packets: the cross-check of the others); 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests); 3 = the persistent tracer of big scenes (trace_big.cu: warps pull 8x4 patches, primary rays as one packet per RT_OPT_PACKET, stack per RT_OPT_BIG_STACK) -- measured 28 % slower than the plain kernel on the million-triangle terrain, hence opt-in; 4 = the plain tracer with packet traversal of the primary rays (13 % slower).  Identical pixels */
+    RT_OPT_TRACE_IMPL = 5,  /* 0 = auto: shared-memory tracer when the scene fits (<= ~165 primitives), else the plain one-thread-per-pixel tracer over the HBM-resident LBVH; 1 = the plain tracer for any scene (no lists, no packets: the cross-check of the others); 2 = shared-memory tracer with its deep-hierarchy fallback forced (tests); 3 = the persistent tracer of big scenes (trace_big.cu: warps pull 8x4 patches, primary rays as one packet per RT_OPT_PACKET, stack per RT_OPT_BIG_STACK) -- measured 8..21 % slower than the plain kernel on the million-triangle terrain, hence opt-in; 4 = the plain tracer with packet traversal of the primary rays (13 % slower).  Identical pixels */
     RT_OPT_BUILDER = 6,     /* hierarchy over the Morton-sorted primitives: 0 = auto (PLOC up to 1024 primitives, Karras above), 1 = Karras, 2 = PLOC */
     RT_OPT_FORCE_RADIX = 7, /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
     RT_OPT_ORDER = 8,       /* work order of the shared-memory tracer on whole frames: 0 = most expensive patches of the previous frame of this size first (default; first frame bottom-up), 1 = always bottom-up.  Scheduling only: identical pixels */
@@ -79,7 +79,7 @@ enum {
     RT_OPT_COMPACTION = 12, /* ray compaction in the shared-memory tracer: 0 = every lane follows its own pixel's chain to the end (default), 1 = rays of the second and later generations that have to traverse the hierarchy are parked in a per-CTA shared-memory queue (ballot + popc slot assignment) and traced 32 at a time by full warps.  Measured SLOWER on every BASELINE view (full warps, but rays of unrelated patches: the traversal loses the coherence an 8x4 patch has), hence opt-in.  Scheduling only: identical pixels */
     RT_OPT_PACKET = 13, /* persistent tracer of big scenes: 0 = the 32 primary rays of an 8x4 patch walk the hierarchy as ONE packet (warp-uniform node, one stack per warp, broadcast node loads; default), 1 = every lane traverses for itself.  Identical pixels */
     RT_OPT_BIG_STACK = 14, /* persistent tracer of big scenes, per-lane traversal stack: 0 = local memory (default), 1 = first 16 entries in shared memory.  Identical pixels */
-    RT_OPT_WIDE_BVH = 15,  /* plain tracer of big scenes: 0 = walks the binary LBVH (default), 1 = walks a 4-wide view of it (one 128-byte node per visit holding the boxes of the grandchildren; rebuilt after every rt_set_scene, 128 bytes per primitive) -- measured 37 % slower on the million-triangle terrain, hence opt-in.  Identical pixels */
+    RT_OPT_WIDE_BVH = 15,  /* plain tracer of big scenes: 0 = walks the binary LBVH (default), 1 = walks a 4-wide view of it (one 128-byte node per visit holding the boxes of the grandchildren; rebuilt after every rt_set_scene, 128 bytes per primitive) -- measured 22 % slower on the million-triangle terrain, hence opt-in.  Identical pixels */
     RT_OPT_N = 16
 };
 

@@ -753,8 +753,8 @@ static int render_impl(rt_context* ctx, const rt_frame* frame, const rt_shard* s
             for (int i = 0; i < RT_LGB_LIGHTS; i++) sc.lg_offsets[i] = sc.lg_entries[i] = nullptr;
         unsigned int* const errw = ctx->d_tile_counter + RT_DEVICE_ERROR_WORD;
         sc.err = errw;
-        /* RT_OPT_WIDE_BVH 1: the plain tracer walks the 4-wide view of the hierarchy (measured 1.60 ms against the binary
-         * walk's 1.17 ms on the terrain at 3840x2160, profiles/r02_big_probe.jsonl: opt-in) */
+        /* RT_OPT_WIDE_BVH 1: the plain tracer walks the 4-wide view of the hierarchy (measured 1.42 ms against the binary
+         * walk's 1.16 ms on the terrain at 3840x2160, profiles/r02_big_probe.jsonl: opt-in) */
         if (!brute && impl != 3 && ctx->opt[RT_OPT_WIDE_BVH] == 1 && sc.n_bvh_prims > 1) {
             const size_t need = (size_t)RT_WIDE_F4 * (size_t)(sc.n_bvh_prims - 1);
             if (need > ctx->cap_wide) {

@@ -47,6 +47,7 @@ __device__ __forceinline__ bool rb_traverse_loop(const RtSceneDev& sc, const RtR
     int node = sc.root;
     int deep[RT_STACK_SIZE];
     int sp = 0;
+    bool overflow = false;                       /* reported by one atomic BEHIND the loop (trace_common.cuh) */
     const float4* __restrict__ nodes = sc.nodes;
     while (true) {
         if (node >= 0) {
@@ -71,7 +72,7 @@ __device__ __forceinline__ bool rb_traverse_loop(const RtSceneDev& sc, const RtR
                     deep[sp - SS] = c1;
                     sp++;
                 } else {
-                    atomicOr(err, 1u);           /* deeper than any hierarchy the host lets through: say so */
+                    overflow = true;             /* deeper than any hierarchy the host lets through: say so */
                 }
                 node = c0;
                 continue;
@@ -94,6 +95,7 @@ __device__ __forceinline__ bool rb_traverse_loop(const RtSceneDev& sc, const RtR
         sp--;
         node = sp < SS ? stk[32 * sp] : deep[sp - SS];
     }
+    if (overflow) atomicOr(err, 1u);
     return false;
 }
 

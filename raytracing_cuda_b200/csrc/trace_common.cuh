@@ -91,6 +91,9 @@ __device__ __forceinline__ bool rt_traverse_loop(const RtSceneDev& sc, const RtR
     int node = sc.root;
     int stack[RT_STACK_SIZE];
     int sp = 0;
+    /* a push beyond the stack is reported, never silent (rt_get_device_errors) -- by ONE atomic behind the loop: the
+     * same atomic inside it, never executed, cost the terrain frame 41 % (1.15 -> 1.62 ms) */
+    bool overflow = false;
     const float4* __restrict__ nodes = sc.nodes;
     while (true) {
         if (node >= 0) {
@@ -109,6 +112,7 @@ __device__ __forceinline__ bool rt_traverse_loop(const RtSceneDev& sc, const RtR
             if (h0 && h1) {
                 if (t1 < t0) { int tmp = c0; c0 = c1; c1 = tmp; }
                 if (sp < RT_STACK_SIZE) stack[sp++] = c1;
+                else overflow = true;
                 node = c0;
                 continue;
             }
@@ -129,6 +133,7 @@ __device__ __forceinline__ bool rt_traverse_loop(const RtSceneDev& sc, const RtR
         if (sp == 0) break;
         node = stack[--sp];
     }
+    if (overflow && sc.err) atomicOr(sc.err, 1u);
     return false;
 }
 
@@ -151,6 +156,7 @@ __device__ __forceinline__ bool rt_traverse_wide_loop(const RtSceneDev& sc, cons
     int node = sc.root;
     int stack[RT_STACK_SIZE];
     int sp = 0;
+    bool overflow = false;                       /* reported behind the loop, see rt_traverse_loop */
     const float4* __restrict__ wide = sc.wide;
     while (true) {
         if (node >= 0) {
@@ -207,8 +213,8 @@ __device__ __forceinline__ bool rt_traverse_wide_loop(const RtSceneDev& sc, cons
                     if (t3 < inf) stack[sp++] = c3;            /* farthest first: the nearest pops first */
                     if (t2 < inf) stack[sp++] = c2;
                     if (t1 < inf) stack[sp++] = c1;
-                } else if (sc.err) {
-                    atomicOr(sc.err, 1u);                       /* never silently: rt_get_device_errors */
+                } else {
+                    overflow = true;
                 }
                 node = c0;
                 continue;
@@ -228,6 +234,7 @@ __device__ __forceinline__ bool rt_traverse_wide_loop(const RtSceneDev& sc, cons
         if (sp == 0) break;
         node = stack[--sp];
     }
+    if (overflow && sc.err) atomicOr(sc.err, 1u);
     return false;
 }
 

@@ -105,6 +105,7 @@ __device__ __forceinline__ void rt_packet_closest(const RtSceneDev& sc, bool liv
     const float4* __restrict__ nodes = sc.nodes;
     int node = sc.root;                           /* warp-uniform from here on */
     int sp = 0;
+    bool overflow = false;                        /* reported by one atomic BEHIND the loop (trace_common.cuh) */
     for (;;) {
         if (node >= 0) {
             const float4 n0 = __ldg(nodes + 4 * node);
@@ -125,8 +126,8 @@ __device__ __forceinline__ void rt_packet_closest(const RtSceneDev& sc, bool liv
                 if (sp < RT_PACKET_STACK) {
                     if (lane == 0) wstk[sp] = one_first ? c0 : c1;
                     sp++;
-                } else if (lane == 0) {
-                    atomicOr(err, 1u);
+                } else {
+                    overflow = true;
                 }
                 node = one_first ? c1 : c0;
                 continue;
@@ -145,6 +146,7 @@ __device__ __forceinline__ void rt_packet_closest(const RtSceneDev& sc, bool liv
         node = wstk[sp];
         __syncwarp();                             /* ... and read before the slot is pushed over */
     }
+    if (overflow && lane == 0) atomicOr(err, 1u);
 }
 
 /* RtGlobalScene whose primary-ray hit is handed in (packet traversal) */
