@@ -67,9 +67,12 @@ def test_fxaa_vs_reference_goldens_and_reference_kernel(impl):
             assert (got == ref).all(), (name, impl, float((got == ref).mean()))
 
 
-@pytest.mark.parametrize("shape", [(2, 4), (3, 8), (33, 64), (34, 68), (97, 131), (108, 192), (720, 1280), (1080, 1920)])
+@pytest.mark.parametrize("shape", [(2, 4), (3, 8), (33, 64), (34, 68), (97, 131), (108, 192), (720, 1280), (1080, 1920),
+                                   (1088, 2240), (1440, 2560), (2160, 3840)])
 def test_fxaa_tma_equals_smem_equals_oracle(shape):
-    """Ragged sizes: tiny images, sizes around the 64x32 tile, widths not divisible by 4 (TMA falls back)."""
+    """Ragged sizes: tiny images, sizes around the 64x32 tile, widths not divisible by 4 (TMA falls back).  Up to
+    1,184 tiles (148 SMs x 8) the TMA kernel runs one tile per CTA (1080x1920: 1,020), beyond that CTAs loop over their
+    tiles with two stages (1088x2240: 1,190 tiles, just over; 1440x2560; 2160x3840)."""
     rng = np.random.default_rng(shape[0] * 7919 + shape[1])
     h, w = shape
     img = rng.integers(0, 1 << 24, size=(h, w), dtype=np.uint32)
