@@ -8,10 +8,14 @@
  * kernel.cu:318-319) only ever feed border pixels, so a clean version needs none.
  *
  * HBM-bound: 4 B read + 4 B written per pixel.  Two implementations:
- *   rt_fxaa_tma_kernel  : persistent CTAs, 64x32-pixel tiles (+1 halo) staged into shared
- *                         memory by TMA (cp.async.bulk.tensor.2d, 72x34 box, zero OOB fill),
- *                         double-buffered on two mbarriers; luminance computed once per
- *                         staged texel; coalesced 128-byte row stores.
+ *   rt_fxaa_tma_kernel  : 64x32-pixel tiles (+1 halo) staged into shared memory by TMA
+ *                         (cp.async.bulk.tensor.2d, 72x34 box, zero OOB fill) on mbarriers;
+ *                         luminance computed once per staged texel; coalesced 128-byte row
+ *                         stores.  Two shapes: one tile per CTA (frames of up to 148 x 8
+ *                         tiles: the whole grid is resident at once) or persistent CTAs
+ *                         looping over their tiles with the next load in flight.  With a peer
+ *                         frame as the output the kernel carries the hand-shake with the
+ *                         frame's owner itself (RtPeerSync).
  *   rt_fxaa_smem_kernel : plain shared-memory tile, any width, any shard tile size.
  *
  * Arithmetic is spelled with explicit rounding intrinsics in the fused shape the

@@ -4,23 +4,28 @@
  * RT_SMALL_MAX_PRIMS).  Same per-pixel arithmetic as trace.cu (trace_pixel.cuh), so the
  * two kernels agree bit for bit; only WHICH primitives get tested differs.
  *
- *   - rt_cull_tiles_kernel (binning pre-pass, one warp per 64x16-pixel bin): primary rays do
- *     not traverse the hierarchy at all.  The warp culls the primitives against the bin's
- *     frustum (4 planes through the eye, 32 primitives per step, back-facing triangles
- *     dropped -- they fail `det < 0.001`, kernel.cu:104) into a short, index-ordered
- *     candidate list in HBM (ballot compaction, 64 B per bin).  For a screen-tile shard it
- *     also marks which 16x8 work tiles hold pixels to trace (own tiles + 1-pixel FXAA apron)
- *     and appends them to a compact work list;
+ *   - rt_cull_tiles_kernel (binning pre-pass, one warp per 64x16-pixel bin, one CTA per 4x2
+ *     block of bins): primary rays do not traverse the hierarchy at all.  The CTA culls every
+ *     primitive against the frustum of its block (4 planes through the eye, back-facing
+ *     triangles dropped -- they fail `det < 0.001`, kernel.cu:104), each warp the survivors
+ *     against its bin, into a short, index-ordered candidate list in HBM (ballot compaction,
+ *     64 B per bin); the same against the frustum mirrored in the sea plane (mirror bins).  For
+ *     a screen-tile shard it also marks which 16x8 work tiles hold pixels to trace (own tiles +
+ *     1-pixel FXAA apron) and appends them to a compact work list.  CTAs behind the screen bins
+ *     fill the light bins when scene or lights have changed;
  *   - rt_trace_small_kernel: persistent CTAs (4 per SM); the LBVH nodes, leaf records,
  *     materials and planes are staged into shared memory once per CTA (the reference keeps
  *     its 133 objects in __constant__, kernel.cu:14).  After that every WARP is autonomous:
- *     it fetches single 8x4 patches from an atomic counter, walking the frame bottom-up so
- *     that the expensive patches (mirror chains in the lower half) start early and the frame
- *     ends on cheap sky patches; no CTA barrier in the loop.  Every pixel tests just its bin's list for its primary ray;
- *   - shadow and mirror rays traverse the shared-memory LBVH with a per-thread stack of
+ *     it fetches single 8x4 patches from an atomic counter, the previous frame's most
+ *     expensive patches first (order history; without one: bottom-up, so that the mirror
+ *     chains in the lower half start early and the frame ends on cheap sky patches); no CTA
+ *     barrier in the loop.  A primary ray tests just its bin's list, a shadow ray the <= 7
+ *     occluders of its light's direction bin, the ray a primary ray sends off the sea plane its
+ *     bin's mirror list;
+ *   - the remaining bounces traverse the shared-memory LBVH with a per-thread stack of
  *     16-bit entries in shared memory (no local memory, sentinel at the bottom), child links
  *     pre-scaled to byte offsets so that a node fetch is one add + four LDS.128;
- *   - ray compaction: a ray of the second or a later generation that has to TRAVERSE the hierarchy (no
+ *   - ray compaction (RT_OPT_COMPACTION 1; measured slower, off by default): a ray of the second or a later generation that has to TRAVERSE the hierarchy (no
  *     candidate list covers it) is not traced by the lane that spawned it.  The lane parks the ray -- origin,
  *     direction, pixel, generation and the colours waiting for it -- in a queue in the CTA's shared memory
  *     (ballot + popc slot assignment) and its warp goes on to the next patch; any warp of the CTA that finds 32
@@ -474,6 +479,7 @@ rs_cull_block(const RtSceneDev& sc, const RtFrameDev& f, unsigned short* __restr
         rs_tile_corners(f, x0, y0, x1, y1, corner);
         const RsFrustum fb = rs_frustum_from_corners(corner);
         const RsFrustum fmb = rs_mirror_frustum(mir, corner);
+        static_assert(RT_SMALL_MAX_PRIMS <= 256, "one primitive per thread of the 256-thread CTA");
         const int j = threadIdx.x;                /* n <= RT_SMALL_MAX_PRIMS = the CTA's threads */
         bool kp = false, km = false;
         if (j < n) {
