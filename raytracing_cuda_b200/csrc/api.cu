@@ -484,6 +484,8 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
         RT_CHECK(ctx, regrow(&b.node_other, c));
         RT_CHECK(ctx, regrow(&b.flags, c));
         RT_CHECK(ctx, regrow(&b.node_aux, c * 12));
+        RT_CHECK(ctx, cudaMemsetAsync(b.node_aux, 0, sizeof(float) * c * 12, ctx->stream));   /* empty arrival slots */
+        b.refit_epoch = 0;
         RT_CHECK(ctx, regrow(&b.nodes, c * 16));
         RT_CHECK(ctx, regrow(&b.prims, c * 3));
         ctx->cap_bvh = n_bvh;
@@ -511,6 +513,12 @@ int rt_set_scene(rt_context* ctx, const rtb_Object* objects, int n_objects, cons
     const bool timing = ctx->opt[RT_OPT_TIMING] != 0;
     if (timing) cudaEventRecord(ctx->ev[4], ctx->stream);
     /* material / plane-only changes still run the (cheap) setup + refit: one code path */
+    b.refit_epoch = (b.refit_epoch + 1u) & 0xFFFFFu;
+    if (b.refit_epoch == 0u) {             /* the stamp wrapped: no slot may still carry this value from 2^20 refits ago */
+        if (b.node_aux && ctx->cap_bvh > 0)
+            RT_CHECK(ctx, cudaMemsetAsync(b.node_aux, 0, sizeof(float) * (size_t)ctx->cap_bvh * 12, ctx->stream));
+        b.refit_epoch = 1u;
+    }
     RT_CHECK(ctx, rt_build_bvh(&b, mode == 0 ? 0 : 1, ctx->opt[RT_OPT_FORCE_RADIX], ctx->opt[RT_OPT_BUILDER], ctx->stream));
     if (timing) { cudaEventRecord(ctx->ev[5], ctx->stream); ctx->build_timed = true; }
     (void)bvh_geometry_changed;

@@ -555,11 +555,33 @@ __device__ __forceinline__ void rt_refit_leaf(int j, int n, const unsigned int* 
     *depth_out = (int)height;                /* only the thread that reached the root gets here */
 }
 
+/* 128-bit exchange with global memory, and a 128-bit atomic read (compare-and-swap of a value with itself) */
+__device__ __forceinline__ uint4 rt_exch128(uint4* p, const uint4 v) {
+    uint4 o;
+    asm volatile("{\n.reg .b128 a, b;\nmov.b128 a, {%4, %5, %6, %7};\natom.global.exch.b128 b, [%8], a;\n"
+                 "mov.b128 {%0, %1, %2, %3}, b;\n}"
+                 : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w) : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "l"(p) : "memory");
+    return o;
+}
+__device__ __forceinline__ uint4 rt_read128(uint4* p) {
+    uint4 o;
+    asm volatile("{\n.reg .b128 z, b;\nmov.b128 z, {%4, %4, %4, %4};\natom.global.cas.b128 b, [%5], z, z;\n"
+                 "mov.b128 {%0, %1, %2, %3}, b;\n}"
+                 : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w) : "r"(0u), "l"(p) : "memory");
+    return o;
+}
+
 /* Full-size refit.  A Karras node covers a contiguous range of sorted leaves (node_other: its other end), so a
  * block of RT_REFIT_THREADS consecutive leaves owns every node whose range lies inside its own: those (255 of 256)
  * are joined through shared memory -- both arrivals park their box there, block-scope fence, shared atomic --
- * and only the nodes that straddle blocks take the global protocol of rt_refit_leaf (device-scope fence + L2
- * atomic + 12 scalar stores per arrival, which held a 1M-leaf refit at 192 us).  node_other[i] < 0 (PLOC
+ * and only the nodes that straddle blocks take the global protocol.  There the child's box TRAVELS IN THE ARRIVAL
+ * itself: a node has two 16-byte slots in `node_aux`, (lo.xyz, stamp) and (hi.xyz, stamp); an arrival exchanges its
+ * halves into them with two 128-bit atomics.  Whoever finds slot 0 without this refit's stamp is first and leaves; the
+ * second has the sibling's lo in hand, and its hi as soon as the sibling's second exchange has landed (it normally
+ * has: else the slot is re-read until it carries the sibling's stamp).  No fence, no flag word, no re-read of the
+ * sibling's box through memory -- one round trip per level where the fence + counter + six loads made three (the
+ * round-1 protocol, which held the ~16,000 straddling nodes' serial chain at 2.6 us per level).  stamp = epoch << 12 |
+ * height << 1 | which child; older epochs count as empty (RtBuildBuffers.refit_epoch).  node_other[i] < 0 (PLOC
  * topology: ranges unknown) sends a node to the global protocol. */
 #ifndef RT_REFIT_THREADS
 #define RT_REFIT_THREADS 256
@@ -571,7 +593,8 @@ rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
                 const unsigned int* __restrict__ bounds, const int2* __restrict__ children,
                 const int* __restrict__ node_parent, const int* __restrict__ leaf_parent,
                 const int* __restrict__ node_other, unsigned int* __restrict__ flags, float* __restrict__ nodes,
-                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out) {
+                float* __restrict__ node_aux, float4* __restrict__ prims, int* __restrict__ depth_out,
+                unsigned int epoch) {
     __shared__ unsigned int s_flags[RT_REFIT_THREADS];
     __shared__ float s_box[RT_REFIT_THREADS][12];    /* per block-owned node: both children's exact (lo, hi) */
     const int b0 = blockIdx.x * blockDim.x, b1 = min(b0 + (int)blockDim.x, n);
@@ -635,20 +658,23 @@ rt_refit_kernel(const unsigned int* __restrict__ sorted_vals, int n,
             lo = make_float3(fminf(lo.x, ob[0]), fminf(lo.y, ob[1]), fminf(lo.z, ob[2]));
             hi = make_float3(fmaxf(hi.x, ob[3]), fmaxf(hi.y, ob[4]), fmaxf(hi.z, ob[5]));
         } else {
-            float* aux = node_aux + 12 * (size_t)node;
-            rt_store_child_box<false>(rec, aux, which, lo, hi);
-            if (which == 0) __stcg(rec + 12, __int_as_float(ch.x));
-            else            __stcg(rec + 13, __int_as_float(ch.y));
-            __threadfence();
-            /* bit 0..7: arrivals, bits 8..: height of the first arrival's subtree */
-            const unsigned int old = atomicAdd(&flags[node], 1u + (height << 8));
-            if (old == 0u) return;                           /* first arrival: the sibling will carry on */
-            height = max(height, old >> 8) + 1u;
-            const float* oa = aux + 6 * (which ^ 1);
-            const float olx = __ldcg(oa + 0), oly = __ldcg(oa + 1), olz = __ldcg(oa + 2);
-            const float ohx = __ldcg(oa + 3), ohy = __ldcg(oa + 4), ohz = __ldcg(oa + 5);
-            lo = make_float3(fminf(lo.x, olx), fminf(lo.y, oly), fminf(lo.z, olz));
-            hi = make_float3(fmaxf(hi.x, ohx), fmaxf(hi.y, ohy), fmaxf(hi.z, ohz));
+            /* traversal record of this child, as above (plain stores, read by nobody before the kernel ends) */
+            const float grow = 1.0f + 4.76837158203125e-07f;   /* 1 + 2^-21 */
+            const float cx = 0.5f * (lo.x + hi.x), cy = 0.5f * (lo.y + hi.y), cz = 0.5f * (lo.z + hi.z);
+            const float ex = fmaxf(hi.x - cx, cx - lo.x) * grow, ey = fmaxf(hi.y - cy, cy - lo.y) * grow,
+                        ez = fmaxf(hi.z - cz, cz - lo.z) * grow;
+            float2* r2 = (float2*)(rec + 6 * which);
+            r2[0] = make_float2(cx, cy); r2[1] = make_float2(cz, ex); r2[2] = make_float2(ey, ez);
+            rec[12 + which] = __int_as_float(which == 0 ? ch.x : ch.y);
+            uint4* slot = (uint4*)(node_aux + 12 * (size_t)node);      /* 48-byte stride: 16-byte aligned */
+            const unsigned int stamp = (epoch << 12) | (height << 1) | (unsigned int)which;
+            const uint4 o0 = rt_exch128(slot, make_uint4(__float_as_uint(lo.x), __float_as_uint(lo.y), __float_as_uint(lo.z), stamp));
+            uint4 o1 = rt_exch128(slot + 1, make_uint4(__float_as_uint(hi.x), __float_as_uint(hi.y), __float_as_uint(hi.z), stamp));
+            if ((o0.w >> 12) != epoch) return;               /* first arrival: the sibling will carry on */
+            while ((o1.w >> 12) != epoch || (o1.w & 1u) == (unsigned int)which) o1 = rt_read128(slot + 1);
+            height = max(height, (o0.w >> 1) & 0x7FFu) + 1u;
+            lo = make_float3(fminf(lo.x, __uint_as_float(o0.x)), fminf(lo.y, __uint_as_float(o0.y)), fminf(lo.z, __uint_as_float(o0.z)));
+            hi = make_float3(fmaxf(hi.x, __uint_as_float(o1.x)), fmaxf(hi.y, __uint_as_float(o1.y)), fmaxf(hi.z, __uint_as_float(o1.z)));
         }
         child = node;
         node = parent;
@@ -922,14 +948,10 @@ extern "C" cudaError_t rt_build_bvh(const RtBuildBuffers* b, int mode, int force
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    if (n >= 2) {
-        cudaError_t e = cudaMemsetAsync(b->flags, 0, sizeof(unsigned int) * (size_t)(n - 1), stream);
-        if (e != cudaSuccess) return e;
-    }
     RT_LAUNCHED(1);
     rt_refit_kernel<<<(n + RT_REFIT_THREADS - 1) / RT_REFIT_THREADS, RT_REFIT_THREADS, 0, stream>>>(b->vals, n, b->bvh_src, b->recs, b->prim_lo, b->prim_hi, b->bounds,
                                                       b->children, b->node_parent, b->leaf_parent, b->node_other, b->flags,
-                                                      b->nodes, b->node_aux, b->prims, b->depth);
+                                                      b->nodes, b->node_aux, b->prims, b->depth, b->refit_epoch);
     return cudaGetLastError();
 }
 

@@ -159,6 +159,9 @@ struct RtBuildBuffers {
      * previous operation on the stream is this context's own FXAA / copy kernel (bvh_build.cu, by-value refit) */
     const float* objs_host;
     int after_own_post;
+    /* stamp of the current refit in the arrival slots of `node_aux` (rt_refit_kernel): a slot whose stamp is older
+     * is empty, so the slots are cleared when they are allocated and when the 20-bit stamp wraps, not per refit */
+    unsigned int refit_epoch;
 };
 
 /* owner of the tile containing pixel (x,y) */
