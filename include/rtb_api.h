@@ -242,7 +242,7 @@ int  rt_sort_pairs(rt_context* ctx, unsigned int* keys_dev, unsigned int* vals_d
  * (key, val) pairs in DEVICE memory for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid it): it calls no cudaMalloc, cudaFree or allocating library routine -- the
  * scratch rt_sort_pairs allocates per call (two temporary arrays + digit histograms) lives in a file-scope device
- * array of RT_SORT_STATIC_MAX keys' capacity (8.25 MiB per GPU that loads the library, held until the process exits).
+ * array of RT_SORT_STATIC_MAX keys' capacity (8.5 MiB per GPU that loads the library, held until the process exits).
  * n > RT_SORT_STATIC_MAX is rejected with RT_ERR_ARG and a message in rt_last_error.  Asynchronous on the context's
  * stream (rt_sort_pairs synchronises before it frees; this one does not).  Every call on a GPU shares the one array,
  * which keeps the last call's contents (nothing in it has to start at zero: every pass overwrites what it reads):

@@ -201,8 +201,11 @@ __global__ void rt_morton_kernel(const float4* __restrict__ prim_lo, const float
 /* ------------------------------------------------------------------ sort */
 
 #define RS_THREADS 256
-#define RS_KEYS_PER_THREAD 16
-#define RS_TILE (RS_THREADS * RS_KEYS_PER_THREAD)   /* 4096 keys per block */
+#ifndef RS_KEYS_PER_THREAD
+#define RS_KEYS_PER_THREAD 8          /* 2,048 keys per block: a 1M-key sort has 490 blocks (16: 245 blocks, 1.65 waves of
+                                         long serial ranking loops -- 118 us for the four passes against 101 with 8) */
+#endif
+#define RS_TILE (RS_THREADS * RS_KEYS_PER_THREAD)
 #define RS_WARPS (RS_THREADS / 32)
 
 /* per-block digit histogram -> hist[digit * n_blocks + block] */
@@ -256,8 +259,8 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(unsigned int* __restrict__
     if (lane == 0) hist[(size_t)256 * n_blocks + b] = carry;
 }
 
-/* stable ranked scatter.  Warp w owns the contiguous chunk [w*512, (w+1)*512) of the block's
- * tile and walks it in 16 steps of 32 keys, so rank order == memory order. */
+/* stable ranked scatter.  Warp w owns the contiguous chunk [w*32*RS_KEYS_PER_THREAD, (w+1)*32*RS_KEYS_PER_THREAD) of the block's
+ * tile and walks it in RS_KEYS_PER_THREAD steps of 32 keys, so rank order == memory order. */
 __global__ void __launch_bounds__(RS_THREADS)
 rs_scatter_kernel(const unsigned int* __restrict__ keys_in, const unsigned int* __restrict__ vals_in,
                   unsigned int* __restrict__ keys_out, unsigned int* __restrict__ vals_out, int n, int shift,
@@ -385,7 +388,7 @@ extern "C" int rt_radix_hist_entries(int n) { return 256 * ((n + RS_TILE - 1) / 
 
 /* ---- the same sort with its scratch in a file-scope device array: allocates nothing (rt_sort_pairs_static, api.cu).
  * Layout in uints: [tmp keys, RT_SORT_STATIC_MAX][tmp values, RT_SORT_STATIC_MAX][histogram rows + bin totals].
- * 8.25 MiB that every GPU which loads the library holds until the process exits.  Nothing in it has to start at
+ * 8.5 MiB that every GPU which loads the library holds until the process exits.  Nothing in it has to start at
  * zero: each of the four passes writes every histogram row, every bin total and all n temporary keys / values before
  * it reads them, so the previous call's contents are never seen and no clear is needed.  All calls share the array:
  * two sorts that overlap on one GPU (different streams, different contexts, different threads) race on it. */
