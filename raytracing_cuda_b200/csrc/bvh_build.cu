@@ -215,33 +215,40 @@ rs_hist_kernel(const unsigned int* __restrict__ keys, int n, int shift, unsigned
     s_h[threadIdx.x] = 0;
     __syncthreads();
     const int base = blockIdx.x * RS_TILE;
-    for (int i = threadIdx.x; i < RS_TILE; i += RS_THREADS) {
-        const int g = base + i;
-        if (g < n) atomicAdd(&s_h[(keys[g] >> shift) & 255u], 1u);
+    /* all of a thread's keys in flight before the first shared-memory atomic (one round trip, not RS_KEYS_PER_THREAD) */
+    unsigned int k[RS_KEYS_PER_THREAD];
+#pragma unroll
+    for (int s = 0; s < RS_KEYS_PER_THREAD; s++) {
+        const int g = base + s * RS_THREADS + threadIdx.x;
+        k[s] = g < n ? __ldg(keys + g) : 0u;
     }
+#pragma unroll
+    for (int s = 0; s < RS_KEYS_PER_THREAD; s++)
+        if (base + s * RS_THREADS + (int)threadIdx.x < n) atomicAdd(&s_h[(k[s] >> shift) & 255u], 1u);
     __syncthreads();
     hist[threadIdx.x * n_blocks + blockIdx.x] = s_h[threadIdx.x];
 }
 
 /* exclusive scan of every bin's row hist[bin][0 .. n_blocks) in place, one WARP per bin (32 blocks of 8 warps),
  * bin totals to hist[256 n_blocks + bin]; the scatter kernel adds the exclusive scan of the 256 totals itself.
- * Four independent 32-wide loads are in flight per step.  (History: a flat single-CTA scan with four barriers per
+ * RS_SCAN_LOADS independent 32-wide loads are in flight per step.  (History: a flat single-CTA scan with four barriers per
  * 1024 counters took 61 us for the 62,720 counters of a 1M-key sort; one CTA with 8 bins per warp and two walks
  * over every row 21 us -- 128 dependent L2 round trips per warp.) */
+#define RS_SCAN_LOADS 4                /* 32-wide loads in flight per step (16, a whole 1M-key row in one step, is slower: 31 vs 21 us) */
 __global__ void __launch_bounds__(256) rs_scan_kernel(unsigned int* __restrict__ hist, int n_blocks) {
     const int lane = threadIdx.x & 31;
     const int b = blockIdx.x * 8 + (threadIdx.x >> 5);
     unsigned int* __restrict__ row = hist + (size_t)b * n_blocks;
     unsigned int carry = 0;
-    for (int j0 = 0; j0 < n_blocks; j0 += 128) {
-        unsigned int v[4], s[4];
+    for (int j0 = 0; j0 < n_blocks; j0 += 32 * RS_SCAN_LOADS) {
+        unsigned int v[RS_SCAN_LOADS], s[RS_SCAN_LOADS];
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
+        for (int q = 0; q < RS_SCAN_LOADS; q++) {
             const int j = j0 + 32 * q + lane;
             v[q] = j < n_blocks ? row[j] : 0u;
         }
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
+        for (int q = 0; q < RS_SCAN_LOADS; q++) {
             s[q] = v[q];
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -250,7 +257,7 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(unsigned int* __restrict__
             }
         }
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
+        for (int q = 0; q < RS_SCAN_LOADS; q++) {
             const int j = j0 + 32 * q + lane;
             if (j < n_blocks) row[j] = carry + s[q] - v[q];
             carry += __shfl_sync(0xFFFFFFFFu, s[q], 31);
@@ -273,12 +280,18 @@ rs_scatter_kernel(const unsigned int* __restrict__ keys_in, const unsigned int* 
 
     const int chunk = blockIdx.x * RS_TILE + warp * (32 * RS_KEYS_PER_THREAD);
     unsigned int key[RS_KEYS_PER_THREAD], val[RS_KEYS_PER_THREAD], rank[RS_KEYS_PER_THREAD];
+    /* every load of the thread in flight before the ranking loop (its ballots and barriers would pin each load to
+     * its own step) */
+#pragma unroll
+    for (int s = 0; s < RS_KEYS_PER_THREAD; s++) {
+        const int g = chunk + s * 32 + lane;
+        key[s] = g < n ? __ldg(keys_in + g) : 0xFFFFFFFFu;
+        val[s] = g < n ? __ldg(vals_in + g) : 0u;
+    }
 #pragma unroll
     for (int s = 0; s < RS_KEYS_PER_THREAD; s++) {
         const int g = chunk + s * 32 + lane;
         const bool valid = g < n;
-        key[s] = valid ? keys_in[g] : 0xFFFFFFFFu;
-        val[s] = valid ? vals_in[g] : 0u;
         const unsigned int digit = (key[s] >> shift) & 255u;
         const unsigned int vmask = __ballot_sync(0xFFFFFFFFu, valid);
         const unsigned int peers = __match_any_sync(0xFFFFFFFFu, digit) & vmask;
@@ -449,6 +462,9 @@ __global__ void rt_karras_kernel(const unsigned int* __restrict__ keys, int n, i
     if (i == 0) node_parent[0] = -1;
     const int d = (rt_delta(keys, n, i, i + 1) - rt_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
     const int dmin = rt_delta(keys, n, i, i - d);
+    /* (Probing two steps of each search per round trip -- 3 or 4 independent loads, decisions in order -- was
+     * measured: 45 instead of 33 us for a million leaves; the kernel is bound by the probes of ALL nodes, not by the
+     * long searches near the root.) */
     int lmax = 2;
     while (rt_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
     int l = 0;

@@ -248,6 +248,65 @@ def test_refit_after_motion_equals_rebuild():
     assert (a == b).all() and (ida == idb).all()
 
 
+def _karras_children(keys):
+    """Karras 2012, one probe at a time, on the host: children of every internal node over sorted `keys` (ties broken
+    by index), encoded like the device's (>= 0 node, < 0 ~leaf)."""
+    n = len(keys)
+    keys = [int(k) for k in keys]
+
+    def delta(i, j):
+        if j < 0 or j >= n:
+            return -1
+        a, b = keys[i], keys[j]
+        if a == b:
+            return 32 + (32 - (i ^ j).bit_length())
+        return 32 - (a ^ b).bit_length()
+
+    out = np.zeros((n - 1, 2), dtype=np.int32)
+    for i in range(n - 1):
+        d = 1 if delta(i, i + 1) - delta(i, i - 1) >= 0 else -1
+        dmin = delta(i, i - d)
+        lmax = 2
+        while delta(i, i + lmax * d) > dmin:
+            lmax <<= 1
+        l, t = 0, lmax >> 1
+        while t >= 1:
+            if delta(i, i + (l + t) * d) > dmin:
+                l += t
+            t >>= 1
+        j = i + l * d
+        dnode = delta(i, j)
+        s, t = 0, (l + 1) >> 1
+        while True:
+            if delta(i, i + (s + t) * d) > dnode:
+                s += t
+            if t == 1:
+                break
+            t = (t + 1) >> 1
+        gamma = i + s * d + min(d, 0)
+        lo, hi = min(i, j), max(i, j)
+        out[i, 0] = ~gamma if lo == gamma else gamma
+        out[i, 1] = ~(gamma + 1) if hi == gamma + 1 else gamma + 1
+    return out
+
+
+@pytest.mark.parametrize("cells", [24, 61])
+def test_karras_topology_equals_host_karras(cells):
+    """The device's Karras kernel against the algorithm restated on the host, node for node -- terrains above the PLOC
+    limit (Karras is then the builder), whose Morton codes repeat (flat cells share a code at 10 bits per axis)."""
+    r = gu.renderer()
+    objs = rt.terrain_objects(cells)
+    s = rt.Scene()
+    r.set_scene(objs[:40], s.lights)                   # force a fresh build
+    r.set_scene(objs, s.lights)
+    n = r.bvh_info()["prims"]
+    assert n > 1024
+    _check_bvh(r, n)
+    nodes, ids, keys = r.bvh_download()
+    got = nodes[:, 12:14].copy().view(np.int32)
+    assert (got == _karras_children(keys)).all()
+
+
 def test_terrain_bvh_equals_bruteforce():
     """Config 4's generator at a size the brute-force kernel finishes quickly: 2*96*96+3 objects."""
     r = gu.renderer()
