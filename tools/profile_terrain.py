@@ -24,6 +24,9 @@ s.set_antialiasing(True)
 f = s.frame(w, h)
 objs = rt.terrain_objects(cells)
 r.set_option(_lib.RT_OPT_TIMING, 1)
+r.set_option(_lib.RT_OPT_SHADOW_BINS, 2)                                  # light grid with the first frame
+r.set_option(_lib.RT_OPT_WIDE_BVH, int(os.environ.get("RTB_WIDE", "0")))  # 1: the 4-wide view of the hierarchy
+r.set_option(_lib.RT_OPT_TRACE_IMPL, int(os.environ.get("RTB_IMPL", "0")))
 r.set_scene(objs, s.lights)
 out = torch.empty(w * h, dtype=torch.int32, device="cuda")
 r.set_option(_lib.RT_OPT_COUNTERS, 1)
