@@ -229,23 +229,38 @@ rs_hist_kernel(const unsigned int* __restrict__ keys, int n, int shift, unsigned
     hist[threadIdx.x * n_blocks + blockIdx.x] = s_h[threadIdx.x];
 }
 
-/* exclusive scan of every bin's row hist[bin][0 .. n_blocks) in place, one WARP per bin (32 blocks of 8 warps),
- * bin totals to hist[256 n_blocks + bin]; the scatter kernel adds the exclusive scan of the 256 totals itself.
- * RS_SCAN_LOADS independent 32-wide loads are in flight per step.  (History: a flat single-CTA scan with four barriers per
- * 1024 counters took 61 us for the 62,720 counters of a 1M-key sort; one CTA with 8 bins per warp and two walks
- * over every row 21 us -- 128 dependent L2 round trips per warp.) */
-#define RS_SCAN_LOADS 4                /* 32-wide loads in flight per step (16, a whole 1M-key row in one step, is slower: 31 vs 21 us) */
+/* exclusive scan of every bin's row hist[bin][0 .. n_blocks) in place, bin totals to hist[256 n_blocks + bin]; the
+ * scatter kernel adds the exclusive scan of the 256 totals itself.  RS_SCAN_WARPS warps share a bin: each sums its
+ * contiguous quarter of the row, the quarters' sums meet in shared memory, then each scans its quarter from its
+ * offset (the re-read hits L1) -- two short round trips for a 1M-key sort's 490 counters per row where one warp per
+ * bin made four.  (History: a flat single-CTA scan with four barriers per 1024 counters took 61 us for the 62,720
+ * counters of a 1M-key sort; one CTA with 8 bins per warp and two walks over every row 21 us; one warp per bin
+ * 5.4 us per pass.) */
+#define RS_SCAN_LOADS 4                /* 32-wide loads in flight per step */
+#define RS_SCAN_WARPS 4                /* warps per bin */
 __global__ void __launch_bounds__(256) rs_scan_kernel(unsigned int* __restrict__ hist, int n_blocks) {
-    const int lane = threadIdx.x & 31;
-    const int b = blockIdx.x * 8 + (threadIdx.x >> 5);
+    __shared__ unsigned int s_part[256 / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b = blockIdx.x * (8 / RS_SCAN_WARPS) + warp / RS_SCAN_WARPS, q4 = warp % RS_SCAN_WARPS;
     unsigned int* __restrict__ row = hist + (size_t)b * n_blocks;
+    /* this warp's part of the row: [j_lo, j_hi), a multiple of 32 long except at the end */
+    const int seg = ((n_blocks + RS_SCAN_WARPS - 1) / RS_SCAN_WARPS + 31) & ~31;
+    const int j_lo = min(q4 * seg, n_blocks), j_hi = min(j_lo + seg, n_blocks);
+    unsigned int sum = 0;
+    for (int j = j_lo + lane; j < j_hi; j += 32) sum += row[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+    if (lane == 0) s_part[warp] = sum;
+    __syncthreads();
     unsigned int carry = 0;
-    for (int j0 = 0; j0 < n_blocks; j0 += 32 * RS_SCAN_LOADS) {
+    for (int w = 0; w < RS_SCAN_WARPS; w++)
+        if (w < q4) carry += s_part[warp - q4 + w];
+    for (int j0 = j_lo; j0 < j_hi; j0 += 32 * RS_SCAN_LOADS) {
         unsigned int v[RS_SCAN_LOADS], s[RS_SCAN_LOADS];
 #pragma unroll
         for (int q = 0; q < RS_SCAN_LOADS; q++) {
             const int j = j0 + 32 * q + lane;
-            v[q] = j < n_blocks ? row[j] : 0u;
+            v[q] = j < j_hi ? row[j] : 0u;
         }
 #pragma unroll
         for (int q = 0; q < RS_SCAN_LOADS; q++) {
@@ -259,11 +274,11 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(unsigned int* __restrict__
 #pragma unroll
         for (int q = 0; q < RS_SCAN_LOADS; q++) {
             const int j = j0 + 32 * q + lane;
-            if (j < n_blocks) row[j] = carry + s[q] - v[q];
+            if (j < j_hi) row[j] = carry + s[q] - v[q];
             carry += __shfl_sync(0xFFFFFFFFu, s[q], 31);
         }
     }
-    if (lane == 0) hist[(size_t)256 * n_blocks + b] = carry;
+    if (q4 == RS_SCAN_WARPS - 1 && lane == 0) hist[(size_t)256 * n_blocks + b] = carry;
 }
 
 /* stable ranked scatter.  Warp w owns the contiguous chunk [w*32*RS_KEYS_PER_THREAD, (w+1)*32*RS_KEYS_PER_THREAD) of the block's
@@ -388,7 +403,7 @@ extern "C" cudaError_t rt_radix_sort_pairs(unsigned int* keys, unsigned int* val
     for (int pass = 0; pass < 4; pass++) {
         const int shift = pass * 8;
         rs_hist_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, n, shift, hist, n_blocks);
-        rs_scan_kernel<<<32, 256, 0, stream>>>(hist, n_blocks);
+        rs_scan_kernel<<<256 * RS_SCAN_WARPS / 8, 256, 0, stream>>>(hist, n_blocks);
         rs_scatter_kernel<<<n_blocks, RS_THREADS, 0, stream>>>(ki, vi, ko, vo, n, shift, hist, n_blocks);
         RT_LAUNCHED(3);
         unsigned int* t = ki; ki = ko; ko = t;

