@@ -73,7 +73,7 @@ enum {
     RT_OPT_BUILDER = 6,     /* hierarchy over the Morton-sorted primitives: 0 = auto (PLOC up to 1024 primitives, Karras above), 1 = Karras, 2 = PLOC */
     RT_OPT_FORCE_RADIX = 7, /* 1 = use the multi-pass radix sort even for tiny scenes (tests) */
     RT_OPT_ORDER = 8,       /* work order of the shared-memory tracer on whole frames: 0 = most expensive patches of the previous frame of this size first (default; first frame bottom-up), 1 = always bottom-up.  Scheduling only: identical pixels */
-    RT_OPT_SHADOW_BINS = 9, /* shadow rays: 0 = per-light direction bins (default; small scenes: rebuilt by every frame's pre-pass; big scenes: a CSR grid built once a second frame finds scene and lights unchanged), 1 = traverse the hierarchy, 2 = like 0, big scenes build the grid at once.  Which primitives get tested only: identical pixels */
+    RT_OPT_SHADOW_BINS = 9, /* shadow rays: 0 = per-light direction bins (default; small scenes: built by the pre-pass of the first frame after a change of scene or lights, see RT_OPT_LIGHT_BINS_REUSE; big scenes: a CSR grid built once a second frame finds scene and lights unchanged), 1 = traverse the hierarchy, 2 = like 0, big scenes build the grid at once.  Which primitives get tested only: identical pixels */
     RT_OPT_MIRROR_BINS = 10, /* rays that primary rays send off plane 0 (the sea) in the shared-memory tracer: 0 = candidate lists of the bin's mirrored frustum (default), 1 = traverse the hierarchy.  Which primitives get tested only: identical pixels */
     RT_OPT_LIGHT_BINS_REUSE = 11, /* light bins of the shared-memory tracer: 0 = rebuilt only when the scene or the lights changed since they were built (default; they do not depend on the camera), 1 = rebuilt by every frame's pre-pass.  Identical pixels */
     RT_OPT_COMPACTION = 12, /* ray compaction in the shared-memory tracer: 0 = every lane follows its own pixel's chain to the end (default), 1 = rays of the second and later generations that have to traverse the hierarchy are parked in a per-CTA shared-memory queue (ballot + popc slot assignment) and traced 32 at a time by full warps.  Measured SLOWER on every BASELINE view (full warps, but rays of unrelated patches: the traversal loses the coherence an 8x4 patch has), hence opt-in.  Scheduling only: identical pixels */
